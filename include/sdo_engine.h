@@ -1,0 +1,195 @@
+/*
+ * sdo_engine.h -- C ABI of the B200 OLAP-index engine (libsdo_engine.so).
+ *
+ * This is the drop-in boundary for the one call the Sparkline accelerator makes into its
+ * OLAP index: DruidRDD.compute -> mQry.executeQuery(client)
+ *   (/root/reference/src/main/scala/org/sparklinedata/druid/DruidRDD.scala:180,
+ *    QuerySpec.executeQuery, DruidQuerySpec.scala:598-599,
+ *    DruidQueryServerClient.executeQueryAsStream, client/DruidClient.scala:448-451).
+ * Everything behind that call in the reference (HTTP to a Druid broker/historical, the Druid
+ * scan/filter/group-by engines, JSON result streaming) is replaced by these entry points.
+ * A JNI shim binds them 1:1; tests and bench bind them with ctypes.
+ *
+ * Conventions: plain pointers and sizes only; no exceptions cross the ABI; every function
+ * returns an sdo_status (0 = OK) unless stated; strings are UTF-8, NUL-terminated unless a
+ * length is passed; all returned pointers stay owned by the engine/result they came from.
+ * Threading: one engine handle may be used from many threads at once; sdo_query_execute is
+ * re-entrant (each call runs on its own CUDA stream with its own scratch), as many Spark tasks
+ * share one executor JVM (reference pool: 100 connections, DruidPlanner.scala:83-90).
+ */
+#ifndef SDO_ENGINE_H
+#define SDO_ENGINE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct sdo_engine sdo_engine;
+typedef struct sdo_result sdo_result;
+typedef struct sdo_partial sdo_partial;
+
+/* Status codes.  Any non-zero status maps to DruidDataSourceException on the Scala side
+ * (/root/reference/src/main/scala/org/sparklinedata/druid/DruidDataSourceException.scala),
+ * except SDO_UNSUPPORTED, which tells the caller to leave the plan un-rewritten (javascript,
+ * spatial, search, select specs: SURVEY.md 8b "Errors"), and SDO_CANCELLED, which the caller
+ * swallows as DruidRDD does (DruidRDD.scala:181-186). */
+typedef enum {
+  SDO_OK = 0,
+  SDO_ERROR = 1,
+  SDO_UNSUPPORTED = 2,
+  SDO_INVALID = 3,
+  SDO_NOT_FOUND = 4,
+  SDO_CANCELLED = 5,
+  SDO_NO_DEVICE = 6,
+  SDO_OUT_OF_MEMORY = 7
+} sdo_status;
+
+/* ---- engine lifetime ---------------------------------------------------------------------
+ * Replaces the per-task DruidQueryServerClient construction (DruidRDD.scala:175-177) and the
+ * connection pool set-up in DruidPlanner.apply (DruidPlanner.scala:54-58).
+ * device >= 0: CUDA device ordinal; queries run there.  device < 0: planning-only engine (spec
+ * parsing, segment metadata, sdo_query_explain); sdo_query_execute then fails with
+ * SDO_NO_DEVICE -- there is no CPU execution path. */
+int sdo_engine_create(int device, sdo_engine** out);
+void sdo_engine_destroy(sdo_engine* e);
+/* Last error message of the calling thread ("" if none).  Replaces the message carried by
+ * DruidDataSourceException (client/DruidClient.scala:206-224,266-283). */
+const char* sdo_last_error(void);
+/* Engine build/version string; "0.9.1-b200" style so that DruidDataSource.supportsBoundFilter
+ * (metadata/DruidDataSource.scala:94-97, needs >= 0.9.0) holds. */
+const char* sdo_version(void);
+
+/* ---- load path ----------------------------------------------------------------------------
+ * New (the reference delegates ingestion to a Druid index task, client/DruidOverlordClient.scala:
+ * 51-129; the segment schema follows src/test/resources/tpch_index_task.json.template).
+ * sdo_datasource_create takes options as JSON:
+ *   {"segmentGranularity":"MONTH"|"DAY"|"YEAR"|"ALL", "queryGranularity":"DAY"|"NONE"|"HOUR"|...}
+ * (defaults MONTH / DAY, as tpch_index_task.json.template:175-176). */
+int sdo_datasource_create(sdo_engine* e, const char* name, const char* options_json);
+int sdo_datasource_drop(sdo_engine* e, const char* name);
+
+typedef enum { SDO_COL_TIME = 0, SDO_COL_DIM = 1, SDO_COL_METRIC = 2 } sdo_col_kind;
+typedef enum {
+  SDO_T_INT64 = 0,   /* data: int64[n_rows]   (time in epoch ms; integer dimension; long metric) */
+  SDO_T_FLOAT64 = 1, /* data: double[n_rows]  (double metric) */
+  SDO_T_STRING = 2,  /* data: int64 offsets[n_rows+1] into bytes (string dimension, row-wise) */
+  SDO_T_CODES = 3,   /* data: int32 codes[n_rows] into a caller dictionary (dict_offsets[n_dict+1], bytes) */
+  SDO_T_INT32 = 4    /* data: int32[n_rows]   (integer dimension) */
+} sdo_col_type;
+/* Spark type of a dimension's source column; decides what approx_count_distinct hashes
+ * (XxHash64 of int vs long vs UTF-8 bytes), SURVEY.md 7 "hard parts". */
+typedef enum { SDO_SRC_STRING = 0, SDO_SRC_INT32 = 1, SDO_SRC_INT64 = 2 } sdo_src_type;
+
+typedef struct {
+  const char* name;
+  int kind;                    /* sdo_col_kind */
+  int type;                    /* sdo_col_type */
+  const void* data;
+  const char* bytes;           /* STRING: row bytes; CODES: dictionary bytes */
+  const int64_t* dict_offsets; /* CODES only */
+  int64_t n_dict;              /* CODES only */
+  int src_type;                /* sdo_src_type (dimensions) */
+} sdo_column;
+
+/* Append n_rows rows (any time order, any time range) to a datasource: the engine truncates
+ * time to the query granularity, sorts by time, cuts month segments, dictionary-encodes the
+ * dimensions (ids 1/2/4 bytes wide by cardinality) and moves the columns into HBM.  Every call
+ * creates one new partition ("shard") per touched segment interval; `partition_num` is recorded
+ * in the segment metadata (DruidSegmentInfo.shardSpec.partitionNum,
+ * metadata/DruidMetadataCache.scala:64-76).  Column buffers are borrowed for the call only. */
+int sdo_segment_load(sdo_engine* e, const char* datasource, int64_t n_rows, int n_cols,
+                     const sdo_column* cols, int partition_num);
+
+/* ---- metadata -----------------------------------------------------------------------------
+ * Replace DruidClient.metadata / timeBoundary / dataSourceInfo / serverStatus
+ * (client/DruidClient.scala:337-364,402-415,495-499).  JSON shapes follow MetadataResponse and
+ * DruidSegmentInfo (client/DruidMessages.scala:25-53, metadata/DruidMetadataCache.scala:64-76).
+ * The returned string is owned by the calling thread's slot and valid until its next call. */
+int sdo_datasource_metadata(sdo_engine* e, const char* name, const char** json_out);
+int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_out);
+
+/* ---- query --------------------------------------------------------------------------------
+ * sdo_query_execute replaces QuerySpec.executeQuery (DruidQuerySpec.scala:598-599): the JSON is
+ * exactly what DruidClient.executeQueryAsStream renders (client/DruidClient.scala:328-331) with
+ * Utils.jsonFormat (Utils.scala:38-105).  queryType in {groupBy, timeseries, topN}. */
+int sdo_query_execute(sdo_engine* e, const char* query_json, size_t len, sdo_result** out);
+/* Plan only (no device work): returns a JSON description of the spans, compiled filter,
+ * key layout, strategy and algorithmic bytes.  No reference counterpart beyond
+ * EXPLAIN DRUID REWRITE (sparklinedata/commands/DruidMetadataCommands.scala:49). */
+int sdo_query_explain(sdo_engine* e, const char* query_json, size_t len, const char** json_out);
+/* Cancel a running query by context.queryId from another thread.  Replaces
+ * CancellableHolder / TaskCancelHandler (client/DruidClient.scala:82-103, DruidRDD.scala:428-491). */
+int sdo_query_cancel(sdo_engine* e, const char* query_id);
+
+/* ---- result -------------------------------------------------------------------------------
+ * Replaces the ResultRow stream (client/DruidMessages.scala:67-153) and the iterators
+ * (sources/druid/DruidQueryResultIterator.scala:58-90, DruidTopNResultIterator.scala:32-74).
+ * Columnar, in pinned host memory; column order = [timestamp if granularity != all], dimensions
+ * (outputName), aggregations (name), post-aggregations (name)  (DruidQuerySpec.scala:614-627). */
+typedef enum {
+  SDO_RES_INT64 = 0,   /* values: int64[n_rows] */
+  SDO_RES_FLOAT64 = 1, /* values: double[n_rows] */
+  SDO_RES_STRING = 2,  /* values: uint32 ids[n_rows] into (dict_offsets, dict_bytes) */
+  SDO_RES_DIM_INT64 = 3, /* integer-valued dimension: values int64[n_rows]; its Druid value is the decimal string */
+  SDO_RES_TIMESTAMP = 4  /* bucket start, epoch ms, int64[n_rows] */
+} sdo_res_type;
+
+typedef struct {
+  const char* name;
+  int type;                    /* sdo_res_type */
+  const void* values;
+  const int64_t* dict_offsets; /* STRING */
+  const char* dict_bytes;      /* STRING */
+  int64_t n_dict;              /* STRING */
+} sdo_result_column;
+
+int64_t sdo_result_num_rows(const sdo_result* r);
+int sdo_result_num_columns(const sdo_result* r);
+int sdo_result_column_get(const sdo_result* r, int i, sdo_result_column* out);
+/* HyperLogLog++ registers (p = 9: 512 bytes per row) behind cardinality column `i`, so the
+ * Scala side can merge partitions or run Spark's own estimator; NULL for other columns. */
+const uint8_t* sdo_result_hll_registers(const sdo_result* r, int i);
+/* Per-query execution facts as JSON: strategy, kernel/total times (CUDA events), rows scanned,
+ * algorithmic bytes, launches.  Feeds DruidQueryExecutionView (DruidRDD.scala:194-216). */
+const char* sdo_result_stats_json(const sdo_result* r);
+/* Release a result.  Replaces closing the HTTP entity (client/DruidClient.scala:160-166). */
+void sdo_result_free(sdo_result* r);
+
+/* ---- sharded execution (one engine per GPU, partial aggregates merged by the host layer) ---
+ * Replaces per-historical partial queries + Spark re-aggregation (DruidRDD.scala:244-269,
+ * sources/druid/DruidStrategy.scala:353-359, sources/druid/PostAggregate.scala:39-60).
+ * sdo_query_partial runs the scan/aggregate on this engine's segments and leaves the partial
+ * aggregate state on the device; the host layer merges the exposed device buffers across ranks
+ * (NCCL sum/min/max on dense tables; hash-partitioned all-to-all for sparse ones), then
+ * sdo_partial_finish turns the merged state into a result. */
+typedef struct {
+  int dense;            /* 1: fixed-layout table indexed by packed key; 0: (key, value) rows */
+  int64_t n_keys;       /* dense: key-space size; sparse: number of local groups */
+  int n_slots;          /* 8-byte aggregate slots per key */
+  void* keys;           /* sparse: device uint64[n_keys] packed keys; dense: NULL */
+  void* slots;          /* device [n_keys * n_slots] 8-byte slots, slot-major per key */
+  const int* slot_ops;  /* host int[n_slots]: 0 = int64 sum, 1 = float64 sum, 2 = int64 min, 3 = int64 max */
+  void* hll;            /* device uint8[n_keys * n_hll * 512] registers or NULL */
+  int n_hll;
+} sdo_partial_view;
+
+int sdo_query_partial(sdo_engine* e, const char* query_json, size_t len, sdo_partial** out);
+int sdo_partial_view_get(sdo_partial* p, sdo_partial_view* out);
+/* Sparse path: split local groups by owner = mix(key) % n_ranks into n_ranks contiguous runs
+ * (counts_out[n_ranks], host), reordering keys/slots in place on the device. */
+int sdo_partial_partition(sdo_partial* p, int n_ranks, int64_t* counts_out);
+/* Sparse path: replace the local state by the merge of `n` received (key, slots) rows. */
+int sdo_partial_merge_rows(sdo_partial* p, const void* keys_dev, const void* slots_dev, int64_t n);
+/* The CUDA stream (cudaStream_t) the partial's device work was queued on; the host layer must
+ * order its collectives after it. */
+void* sdo_partial_stream(sdo_partial* p);
+int sdo_partial_finish(sdo_partial* p, sdo_result** out);
+void sdo_partial_free(sdo_partial* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDO_ENGINE_H */

@@ -1,0 +1,930 @@
+#include "engine.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "../../include/sdo_engine.h"
+#include "xxh64.hpp"
+
+namespace sdo {
+
+static double now_ms() {
+  return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// Spark HyperLogLogPlusPlusHelper.query for p = 9 (relativeSD = 0.05), restated: raw estimate
+// alpha*m^2 / sum(2^-M[j]), linear counting below the p = 9 threshold (400), rounded to a long.
+// The empirical bias-correction tables of HLL++ (used by Spark when E < 5m) are not available
+// offline; in that band (roughly 400 < E < 2560) the estimate is the uncorrected E and is
+// reported as such -- the registers themselves (sdo_result_hll_registers) are exact.
+double hll_estimate(const uint8_t* regs) {
+  const double m = HLL_M;
+  double zinv = 0, V = 0;
+  for (int j = 0; j < HLL_M; j++) {
+    zinv += 1.0 / (double)(1ull << regs[j]);
+    if (regs[j] == 0) V += 1;
+  }
+  const double alpha_m2 = (0.7213 / (1.0 + 1.079 / m)) * m * m;
+  const double E = alpha_m2 / zinv;
+  double est = E;
+  if (V > 0) {
+    double H = m * std::log(m / V);
+    if (H <= 400.0) est = H;
+  }
+  return std::floor(est + 0.5);  // Math.round
+}
+
+Engine::Engine(int device) : device_(device), store_(device) {
+  if (device_ >= 0) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) throw NoDevice(std::string("no CUDA device available: ") + cudaGetErrorString(e));
+    if (device_ >= n) throw NoDevice("CUDA device " + std::to_string(device_) + " does not exist (" + std::to_string(n) + " visible)");
+    SDO_CUDA(cudaSetDevice(device_));
+    cudaDeviceProp prop;
+    SDO_CUDA(cudaGetDeviceProperties(&prop, device_));
+    sm_count_ = prop.multiProcessorCount;
+    if (prop.major < 10) throw NoDevice(std::string("device '") + prop.name + "' is not sm_100 class; this library is built for sm_100a only");
+    cudaMemPool_t pool;
+    SDO_CUDA(cudaDeviceGetDefaultMemPool(&pool, device_));
+    uint64_t thr = UINT64_MAX;
+    SDO_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+  }
+}
+
+Engine::~Engine() {
+  if (device_ >= 0) {
+    cudaSetDevice(device_);
+    cudaDeviceSynchronize();
+    for (QueryCtx* c : free_ctx_) {
+      if (c->stream) cudaStreamDestroy(c->stream);
+      for (auto& e : c->ev)
+        if (e) cudaEventDestroy(e);
+      if (c->pinned_in) cudaFreeHost(c->pinned_in);
+      if (c->pinned_out) cudaFreeHost(c->pinned_out);
+      if (c->counters) cudaFree(c->counters);
+      delete c;
+    }
+  }
+}
+
+QueryCtx* Engine::acquire_ctx() {
+  {
+    std::lock_guard<std::mutex> lk(ctx_mu_);
+    if (!free_ctx_.empty()) {
+      QueryCtx* c = free_ctx_.back();
+      free_ctx_.pop_back();
+      return c;
+    }
+  }
+  QueryCtx* c = new QueryCtx();
+  SDO_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  for (auto& e : c->ev) SDO_CUDA(cudaEventCreate(&e));
+  SDO_CUDA(cudaMalloc((void**)&c->counters, 64));
+  ensure_pinned(&c->pinned_in, &c->pinned_in_bytes, 1 << 20);
+  ensure_pinned(&c->pinned_out, &c->pinned_out_bytes, 4 << 20);
+  return c;
+}
+void Engine::release_ctx(QueryCtx* c) {
+  std::lock_guard<std::mutex> lk(ctx_mu_);
+  free_ctx_.push_back(c);
+}
+void Engine::ensure_pinned(void** p, size_t* cur, size_t need) {
+  if (*cur >= need) return;
+  if (*p) cudaFreeHost(*p);
+  *p = nullptr;
+  size_t n = std::max(need, *cur * 2);
+  SDO_CUDA(cudaMallocHost(p, n));
+  *cur = n;
+}
+
+void Engine::cancel(const std::string& qid) {
+  std::lock_guard<std::mutex> lk(cancel_mu_);
+  cancelled_.insert(qid);
+  if (cancelled_.size() > 4096) cancelled_.erase(cancelled_.begin());
+}
+void Engine::check_cancel(const std::string& qid) {
+  if (qid.empty()) return;
+  std::lock_guard<std::mutex> lk(cancel_mu_);
+  auto it = cancelled_.find(qid);
+  if (it != cancelled_.end()) {
+    cancelled_.erase(it);
+    throw Cancelled("query '" + qid + "' was cancelled");
+  }
+}
+
+const uint16_t* Engine::ensure_hll_lut(DataSource& ds, int di, cudaStream_t st) {
+  std::lock_guard<std::mutex> lk(lut_mu_);
+  DimMeta& dm = ds.dims[di];
+  if (dm.hll_lut && dm.hll_lut_card == dm.cardinality) return (const uint16_t*)dm.hll_lut;
+  if (dm.hll_lut) { cudaFree(dm.hll_lut); dm.hll_lut = nullptr; }
+  const Dictionary& d = *dm.dict;
+  void *dbytes = nullptr, *doffs = nullptr, *lut = nullptr;
+  SDO_CUDA(cudaMalloc(&dbytes, std::max<size_t>(d.bytes.size(), 16)));
+  SDO_CUDA(cudaMalloc(&doffs, d.offsets.size() * 8));
+  SDO_CUDA(cudaMalloc(&lut, std::max<size_t>((size_t)d.size() * 2, 16)));
+  SDO_CUDA(cudaMemcpyAsync(dbytes, d.bytes.data(), d.bytes.size(), cudaMemcpyHostToDevice, st));
+  SDO_CUDA(cudaMemcpyAsync(doffs, d.offsets.data(), d.offsets.size() * 8, cudaMemcpyHostToDevice, st));
+  launch_hll_lut_strings((const char*)dbytes, (const int64_t*)doffs, d.size(), (uint16_t*)lut, st);
+  SDO_CUDA(cudaStreamSynchronize(st));
+  cudaFree(dbytes);
+  cudaFree(doffs);
+  dm.hll_lut = lut;
+  dm.hll_lut_card = dm.cardinality;
+  return (const uint16_t*)lut;
+}
+
+static uint64_t pow2_ceil(uint64_t v) {
+  uint64_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
+  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+  SDO_CUDA(cudaSetDevice(device_));
+  cudaStream_t s = ctx->stream;
+  DataSource& ds = *plan.ds;
+  const size_t n_cols = plan.columns.size();
+  const size_t n_segs = plan.seg_index.size();
+  const size_t n_spans = plan.spans.size();
+
+  // ---- per-query device blob: spans + sentinel | coarse index | segment pointer table | bitsets ----
+  size_t off_spans = 0;
+  size_t off_coarse = off_spans + (n_spans + 1) * sizeof(DevSpan);
+  size_t off_segptr = round_up(off_coarse + plan.coarse.size() * 4, 16);
+  size_t off = round_up(off_segptr + std::max<size_t>(1, n_segs * n_cols) * 8, 16);
+  std::vector<size_t> off_bits(plan.leaves.size(), 0);
+  for (size_t i = 0; i < plan.leaves.size(); i++)
+    if (plan.leaves[i].leaf.kind == LEAF_BITSET) {
+      off_bits[i] = off;
+      off = round_up(off + plan.leaves[i].bitset.size() * 4, 16);
+    }
+  const size_t blob_bytes = off;
+  ensure_pinned(&ctx->pinned_in, &ctx->pinned_in_bytes, blob_bytes);
+  char* h = (char*)ctx->pinned_in;
+  memcpy(h + off_spans, plan.spans.data(), n_spans * sizeof(DevSpan));
+  DevSpan sentinel{};
+  sentinel.unit_begin = plan.n_units;
+  memcpy(h + off_spans + n_spans * sizeof(DevSpan), &sentinel, sizeof(DevSpan));
+  memcpy(h + off_coarse, plan.coarse.data(), plan.coarse.size() * 4);
+  const void** sp = (const void**)(h + off_segptr);
+  for (size_t si = 0; si < n_segs; si++) {
+    const Segment& sg = *ds.segments[plan.seg_index[si]];
+    for (size_t c = 0; c < n_cols; c++) {
+      const PlanColumn& pc = plan.columns[c];
+      const void* p = pc.is_metric ? sg.metric_data[pc.index] : sg.dim_data[pc.index];
+      if (!p) throw Unsupported("segment " + format_iso_instant(sg.start_ms) + " has no data for column '" + (pc.is_metric ? ds.metrics[pc.index].name : ds.dims[pc.index].name) + "'");
+      if (!pc.is_metric && sg.dim_width[pc.index] != pc.width) throw std::runtime_error("internal: segment id width differs from datasource width");
+      sp[si * n_cols + c] = p;
+    }
+  }
+  for (size_t i = 0; i < plan.leaves.size(); i++)
+    if (plan.leaves[i].leaf.kind == LEAF_BITSET) memcpy(h + off_bits[i], plan.leaves[i].bitset.data(), plan.leaves[i].bitset.size() * 4);
+
+  SDO_CUDA(cudaEventRecord(ctx->ev[0], s));
+  SDO_CUDA(cudaMallocAsync(&st->blob, blob_bytes, s));
+  SDO_CUDA(cudaMemcpyAsync(st->blob, h, blob_bytes, cudaMemcpyHostToDevice, s));
+  st->h2d_bytes += blob_bytes;
+
+  ScanParams& p = st->params;
+  memset(&p, 0, sizeof p);
+  char* d = (char*)st->blob;
+  p.spans = (const DevSpan*)(d + off_spans);
+  p.n_spans = (uint32_t)n_spans;
+  p.n_units = plan.n_units;
+  p.units_per_chunk = 8;
+  p.n_cols = (uint32_t)n_cols;
+  p.segptr = (const void* const*)(d + off_segptr);
+  p.n_leaves = (int)plan.leaves.size();
+  for (size_t i = 0; i < plan.leaves.size(); i++) {
+    p.leaves[i] = plan.leaves[i].leaf;
+    if (p.leaves[i].kind == LEAF_BITSET) p.leaves[i].bits = (const uint32_t*)(d + off_bits[i]);
+  }
+  p.n_ops = (int)plan.op_code.size();
+  for (size_t i = 0; i < plan.op_code.size(); i++) { p.op_code[i] = plan.op_code[i]; p.op_arg[i] = plan.op_arg[i]; }
+  p.n_dims = (int)plan.dev_dims.size();
+  for (size_t i = 0; i < plan.dev_dims.size(); i++) p.dims[i] = plan.dev_dims[i];
+  p.n_aggs = (int)plan.dev_aggs.size();
+  for (size_t i = 0; i < plan.dev_aggs.size(); i++) {
+    p.aggs[i] = plan.dev_aggs[i];
+    if (p.aggs[i].op == AGG_HLL && p.aggs[i].hll_mode == HLL_LUT) p.aggs[i].hll_lut = ensure_hll_lut(ds, plan.hll_ds_dim[i], s);
+  }
+  p.n_slots = plan.n_slots;
+  p.n_hll = plan.n_hll;
+  p.n_keys = plan.n_keys;
+  for (int i = 0; i < plan.n_slots; i++) { p.slot_op[i] = plan.slot_op[i]; p.slot_init[i] = plan.slot_init[i]; }
+  p.counters = ctx->counters;
+  SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, 64, s));
+
+  int strat = plan.strategy;
+  st->strategy = strat;
+  const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;
+
+  if (strat == STRAT_HASH) {
+    // size the table from an exact count of passing rows when a filter can shrink it
+    uint64_t rows_upper = (uint64_t)plan.rows_scanned;
+    if (p.n_ops > 0) {
+      ScanParams c = p;
+      c.n_dims = 0;
+      c.n_aggs = 0;
+      c.n_keys = 1;
+      c.n_slots = 1;
+      c.n_hll = 0;
+      size_t smem = scan_smem_bytes(STRAT_LANE, 1, 1);
+      int grid = scan_grid_size(STRAT_LANE, smem, sm_count_);
+      unsigned long long* part = nullptr;
+      SDO_CUDA(cudaMallocAsync((void**)&part, (size_t)(grid + 1) * 8, s));
+      c.table = part;
+      launch_scan(STRAT_LANE, c, grid, smem, s);
+      launch_reduce_partials(part, grid, 1, 1, c, part + grid, s);
+      unsigned long long cnt = 0;
+      SDO_CUDA(cudaMemcpyAsync(&cnt, part + grid, 8, cudaMemcpyDeviceToHost, s));
+      SDO_CUDA(cudaStreamSynchronize(s));
+      SDO_CUDA(cudaFreeAsync(part, s));
+      SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, 64, s));
+      st->launches += 2;
+      st->d2h_bytes += 8;
+      rows_upper = cnt;
+    }
+    uint64_t groups_upper = std::min<uint64_t>(plan.n_keys, rows_upper);
+    uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, groups_upper + groups_upper / 2));
+    st->table_rows = cap;
+    SDO_CUDA(cudaMallocAsync((void**)&st->hkeys, cap * 8, s));
+    SDO_CUDA(cudaMallocAsync((void**)&st->table, cap * (uint64_t)plan.n_slots * 8, s));
+    launch_fill_u64(st->hkeys, cap, HASH_EMPTY, s);
+    launch_fill_slots(st->table, cap, plan.n_slots, nullptr, p, s);
+    st->launches += 2;
+    p.hkeys = st->hkeys;
+    p.hmask = cap - 1;
+    p.table = st->table;
+  } else {
+    st->table_rows = plan.n_keys;
+    SDO_CUDA(cudaMallocAsync((void**)&st->table, std::max<uint64_t>(cells, 1) * 8, s));
+    if (strat != STRAT_LANE) {
+      launch_fill_slots(st->table, plan.n_keys, plan.n_slots, nullptr, p, s);
+      st->launches += 1;
+      p.table = st->table;
+    }
+  }
+  if (plan.n_hll) {
+    size_t hb = (size_t)st->table_rows * plan.n_hll * HLL_M;
+    if (hb > opt_.hll_max_bytes) throw Unsupported("cardinality aggregation needs " + std::to_string(hb) + " bytes of registers");
+    SDO_CUDA(cudaMallocAsync((void**)&st->hll, hb, s));
+    SDO_CUDA(cudaMemsetAsync(st->hll, 0, hb, s));
+    p.hll = st->hll;
+  }
+
+  size_t smem = scan_smem_bytes(strat, plan.n_keys, plan.n_slots);
+  int grid = scan_grid_size(strat, smem, sm_count_);
+  const uint32_t n_chunks = (plan.n_units + p.units_per_chunk - 1) / p.units_per_chunk;
+  grid = (int)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid, n_chunks));
+  if (strat == STRAT_LANE) {
+    SDO_CUDA(cudaMallocAsync((void**)&st->partials, (size_t)grid * std::max<uint64_t>(cells, 1) * 8, s));
+    p.table = st->partials;
+  }
+  SDO_CUDA(cudaEventRecord(ctx->ev[1], s));
+  launch_scan(strat, p, grid, smem, s);
+  SDO_CUDA(cudaEventRecord(ctx->ev[2], s));
+  st->launches += 1;
+  if (strat == STRAT_LANE) {
+    launch_reduce_partials(st->partials, grid, (uint32_t)cells, plan.n_slots, p, st->table, s);
+    st->launches += 1;
+    p.table = st->table;
+  }
+}
+
+// Gather the occupied groups of a large dense table or a hash table into row arrays.
+void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
+  cudaStream_t s = ctx->stream;
+  const int ns = plan.n_slots;
+  unsigned long long* counter = (unsigned long long*)(ctx->counters + 4);
+  unsigned long long* src = nullptr;
+  // upper bound on rows: table rows (dense) or capacity (hash); allocate exactly after a count
+  // pass would cost another launch, so size by min(table rows, rows scanned)
+  uint64_t cap_rows = std::min<uint64_t>(st->table_rows, (uint64_t)std::max<int64_t>(plan.rows_scanned, 1));
+  SDO_CUDA(cudaMallocAsync((void**)&st->rows_keys, std::max<uint64_t>(cap_rows, 1) * 8, s));
+  SDO_CUDA(cudaMallocAsync((void**)&st->rows_slots, std::max<uint64_t>(cap_rows, 1) * ns * 8, s));
+  if (plan.n_hll) SDO_CUDA(cudaMallocAsync((void**)&src, std::max<uint64_t>(cap_rows, 1) * 8, s));
+  SDO_CUDA(cudaMemsetAsync(counter, 0, 8, s));
+  if (st->strategy == STRAT_HASH) launch_compact_hash(st->hkeys, st->table, st->table_rows, ns, st->rows_keys, st->rows_slots, src, counter, s);
+  else launch_compact_dense(st->table, st->table_rows, ns, st->rows_keys, st->rows_slots, src, counter, s);
+  st->launches += 1;
+  struct { unsigned int c[4]; unsigned long long n; } host;
+  SDO_CUDA(cudaMemcpyAsync(&host, ctx->counters, 24, cudaMemcpyDeviceToHost, s));
+  SDO_CUDA(cudaStreamSynchronize(s));
+  st->d2h_bytes += 24;
+  if (host.c[1]) throw std::runtime_error("internal: hash table overflow");
+  st->n_rows = host.n;
+  if (plan.n_hll) {
+    SDO_CUDA(cudaMallocAsync((void**)&st->rows_hll, std::max<uint64_t>(st->n_rows, 1) * plan.n_hll * HLL_M, s));
+    launch_gather_hll(st->hll, src, st->n_rows, plan.n_hll, st->rows_hll, s);
+    st->launches += 1;
+    SDO_CUDA(cudaFreeAsync(src, s));
+  }
+  st->rows_valid = true;
+}
+
+void Engine::free_state(QueryCtx* ctx, ScanState* st) {
+  if (device_ < 0) return;
+  cudaStream_t s = ctx->stream;
+  void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll};
+  for (void* p : ptrs)
+    if (p) cudaFreeAsync(p, s);
+  st->blob = nullptr; st->table = nullptr; st->hkeys = nullptr; st->hll = nullptr; st->partials = nullptr;
+  st->rows_keys = nullptr; st->rows_slots = nullptr; st->rows_hll = nullptr;
+}
+
+namespace {
+
+struct HostRows {
+  uint64_t n = 0;
+  int ns = 1;
+  std::vector<uint64_t> keys, slots;
+  std::vector<uint8_t> hll;
+};
+
+inline double ord_to_f64(int64_t raw) {
+  if (raw == INT64_MAX) return INFINITY;   // empty min
+  if (raw == INT64_MIN) return -INFINITY;  // empty max
+  int64_t bits = raw ^ ((raw >> 63) & 0x7FFFFFFFFFFFFFFFll);
+  double d;
+  memcpy(&d, &bits, 8);
+  return d;
+}
+
+struct Assembler {
+  const Plan& plan;
+  const HostRows& rows;
+  std::vector<std::vector<int64_t>> agg_i;  // per agg (int outputs)
+  std::vector<std::vector<double>> agg_f;   // per agg (float outputs)
+  std::vector<std::vector<double>> post;    // per post-agg
+
+  double agg_value(size_t a, uint64_t r) const { return plan.aggs[a].out_float ? agg_f[a][r] : (double)agg_i[a][r]; }
+  int find_agg(const std::string& n) const {
+    for (size_t i = 0; i < plan.aggs.size(); i++)
+      if (plan.aggs[i].name == n) return (int)i;
+    return -1;
+  }
+  int find_post(const std::string& n) const {
+    for (size_t i = 0; i < plan.spec.post_aggregations.size(); i++)
+      if (plan.spec.post_aggregations[i].name == n) return (int)i;
+    return -1;
+  }
+  bool named_value(const std::string& n, uint64_t r, double* v, size_t post_limit) const {
+    int a = find_agg(n);
+    if (a >= 0) { *v = agg_value((size_t)a, r); return true; }
+    int p = find_post(n);
+    if (p >= 0 && (size_t)p < post_limit) { *v = post[(size_t)p][r]; return true; }
+    return false;
+  }
+  // PostAggregationSpec semantics: DruidQuerySpec.scala:379-430 (Druid arithmetic: x / 0 = 0)
+  double eval_post(const PostAggSpec& ps, uint64_t r, size_t post_limit) const {
+    switch (ps.kind) {
+      case PostAggSpec::Constant: return ps.value;
+      case PostAggSpec::FieldAccess: case PostAggSpec::HyperUniqueCardinality: {
+        double v;
+        if (!named_value(ps.field, r, &v, post_limit)) throw Invalid("postAggregation refers to unknown field '" + ps.field + "'");
+        return v;
+      }
+      case PostAggSpec::Arithmetic: {
+        double acc = eval_post(ps.fields[0], r, post_limit);
+        for (size_t i = 1; i < ps.fields.size(); i++) {
+          double x = eval_post(ps.fields[i], r, post_limit);
+          if (ps.fn == "+") acc += x;
+          else if (ps.fn == "-") acc -= x;
+          else if (ps.fn == "*") acc *= x;
+          else if (ps.fn == "/") acc = x == 0.0 ? 0.0 : acc / x;
+          else acc = acc / x;
+        }
+        return acc;
+      }
+    }
+    return 0;
+  }
+  bool eval_having(const HavingNode& h, uint64_t r) const {
+    switch (h.kind) {
+      case HavingNode::And: for (auto& c : h.specs) if (!eval_having(c, r)) return false; return true;
+      case HavingNode::Or: for (auto& c : h.specs) if (eval_having(c, r)) return true; return false;
+      case HavingNode::Not: return !eval_having(h.specs.at(0), r);
+      default: break;
+    }
+    double v;
+    if (!named_value(h.aggregation, r, &v, post.size())) throw Invalid("having refers to unknown aggregation '" + h.aggregation + "'");
+    if (h.kind == HavingNode::GreaterThan) return v > h.value;
+    if (h.kind == HavingNode::LessThan) return v < h.value;
+    return v == h.value;
+  }
+};
+
+}  // namespace
+
+Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms) {
+  cudaStream_t s = ctx ? ctx->stream : nullptr;
+  const int ns = plan.n_slots;
+  HostRows rows;
+  rows.ns = ns;
+  bool device_topk = false;
+  float ms_h2d = 0, ms_scan = 0, ms_dev = 0;
+
+  if (!plan.always_false) {
+    const bool dense = st->strategy != STRAT_HASH && !st->rows_valid;
+    if (dense && st->table_rows <= 65536 && (uint64_t)st->table_rows * std::max(1, plan.n_hll) * HLL_M <= (64u << 20)) {
+      // small dense table: bring it back whole and drop empty groups on the host
+      const size_t tb = (size_t)st->table_rows * ns * 8;
+      const size_t hb = plan.n_hll ? (size_t)st->table_rows * plan.n_hll * HLL_M : 0;
+      ensure_pinned(&ctx->pinned_out, &ctx->pinned_out_bytes, tb + hb);
+      SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
+      SDO_CUDA(cudaMemcpyAsync(ctx->pinned_out, st->table, tb, cudaMemcpyDeviceToHost, s));
+      if (hb) SDO_CUDA(cudaMemcpyAsync((char*)ctx->pinned_out + tb, st->hll, hb, cudaMemcpyDeviceToHost, s));
+      SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
+      SDO_CUDA(cudaStreamSynchronize(s));
+      st->d2h_bytes += tb + hb;
+      const uint64_t* t = (const uint64_t*)ctx->pinned_out;
+      const uint8_t* hr = (const uint8_t*)ctx->pinned_out + tb;
+      for (uint64_t k = 0; k < st->table_rows; k++) {
+        if (t[k * ns] == 0) continue;
+        rows.keys.push_back(k);
+        rows.slots.insert(rows.slots.end(), t + k * ns, t + (k + 1) * ns);
+        if (hb) rows.hll.insert(rows.hll.end(), hr + k * plan.n_hll * HLL_M, hr + (k + 1) * plan.n_hll * HLL_M);
+      }
+      rows.n = rows.keys.size();
+    } else {
+      if (!st->rows_valid) compact_rows(ctx, plan, st);
+      uint64_t n = st->n_rows;
+      // device top-k when only a few rows of a large result are wanted
+      int topk_slot = -1, topk_f64 = 0, topk_desc = 1;
+      int64_t k_want = 0;
+      if (!plan.spec.has_having && n > 65536) {
+        const QuerySpec& q = plan.spec;
+        std::string col;
+        bool desc = true;
+        if (q.type == QuerySpec::TopN && q.metric.kind == TopNMetric::Numeric) { col = q.metric.metric; desc = !q.metric.inverted; k_want = q.threshold; }
+        else if (q.type == QuerySpec::GroupBy && q.limit.present && q.limit.columns.size() == 1) { col = q.limit.columns[0].dimension; desc = !q.limit.columns[0].ascending; k_want = q.limit.limit; }
+        if (!col.empty() && k_want > 0 && k_want <= 1024) {
+          for (auto& a : plan.aggs)
+            if (a.name == col && a.hll_index < 0 && !a.const_times_count && !(a.kind == AggregationSpec::Count && a.slot == 0 && false)) {
+              topk_slot = a.slot;
+              topk_f64 = (a.kind == AggregationSpec::DoubleSum) ? 1 : 0;  // min/max doubles are already order-preserving ints
+              topk_desc = desc ? 1 : 0;
+            }
+        }
+      }
+      SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
+      if (topk_slot >= 0 && !plan.n_hll) {
+        int k = (int)k_want;
+        size_t se = topk_scratch_elems(n, k);
+        unsigned long long *sa = nullptr, *sb = nullptr, *oi = nullptr, *gk = nullptr, *gs = nullptr;
+        SDO_CUDA(cudaMallocAsync((void**)&sa, se * 8, s));
+        SDO_CUDA(cudaMallocAsync((void**)&sb, se * 8, s));
+        SDO_CUDA(cudaMallocAsync((void**)&oi, (size_t)k * 8, s));
+        SDO_CUDA(cudaMallocAsync((void**)&gk, (size_t)k * 8, s));
+        SDO_CUDA(cudaMallocAsync((void**)&gs, (size_t)k * ns * 8, s));
+        launch_topk(st->rows_keys, st->rows_slots, n, ns, topk_slot, topk_f64, topk_desc, k, sa, sb, oi, s);
+        launch_gather_rows(st->rows_keys, st->rows_slots, oi, (uint64_t)k, ns, gk, gs, s);
+        st->launches += 2;
+        rows.keys.assign((size_t)k, 0);
+        rows.slots.assign((size_t)k * ns, 0);
+        SDO_CUDA(cudaMemcpyAsync(rows.keys.data(), gk, (size_t)k * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaMemcpyAsync(rows.slots.data(), gs, (size_t)k * ns * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
+        SDO_CUDA(cudaStreamSynchronize(s));
+        st->d2h_bytes += (size_t)k * (ns + 1) * 8;
+        for (void* p : {(void*)sa, (void*)sb, (void*)oi, (void*)gk, (void*)gs}) SDO_CUDA(cudaFreeAsync(p, s));
+        // drop padding (fewer than k groups cannot happen here since n > 65536 >= k, kept for safety)
+        size_t w = 0;
+        for (size_t i = 0; i < (size_t)k; i++)
+          if (rows.keys[i] != ~0ull) {
+            rows.keys[w] = rows.keys[i];
+            memmove(&rows.slots[w * ns], &rows.slots[i * ns], (size_t)ns * 8);
+            w++;
+          }
+        rows.keys.resize(w);
+        rows.slots.resize(w * ns);
+        rows.n = w;
+        device_topk = true;
+      } else {
+        rows.keys.assign((size_t)n, 0);
+        rows.slots.assign((size_t)n * ns, 0);
+        if (n) {
+          SDO_CUDA(cudaMemcpyAsync(rows.keys.data(), st->rows_keys, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
+          SDO_CUDA(cudaMemcpyAsync(rows.slots.data(), st->rows_slots, (size_t)n * ns * 8, cudaMemcpyDeviceToHost, s));
+          if (plan.n_hll) {
+            rows.hll.assign((size_t)n * plan.n_hll * HLL_M, 0);
+            SDO_CUDA(cudaMemcpyAsync(rows.hll.data(), st->rows_hll, rows.hll.size(), cudaMemcpyDeviceToHost, s));
+          }
+        }
+        SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
+        SDO_CUDA(cudaStreamSynchronize(s));
+        st->d2h_bytes += (size_t)n * (ns + 1) * 8 + rows.hll.size();
+        rows.n = n;
+      }
+    }
+    cudaEventElapsedTime(&ms_h2d, ctx->ev[0], ctx->ev[1]);
+    cudaEventElapsedTime(&ms_scan, ctx->ev[1], ctx->ev[2]);
+    cudaEventElapsedTime(&ms_dev, ctx->ev[0], ctx->ev[4]);
+    st->scan_ms = ms_scan;
+  }
+
+  // ---- host assembly -------------------------------------------------------------------------------
+  const QuerySpec& q = plan.spec;
+  const uint64_t n = rows.n;
+  Assembler as{plan, rows, {}, {}, {}};
+  as.agg_i.resize(plan.aggs.size());
+  as.agg_f.resize(plan.aggs.size());
+  for (size_t a = 0; a < plan.aggs.size(); a++) {
+    const PlanAgg& pa = plan.aggs[a];
+    if (pa.out_float) as.agg_f[a].resize(n);
+    else as.agg_i[a].resize(n);
+    for (uint64_t r = 0; r < n; r++) {
+      if (pa.hll_index >= 0) {
+        as.agg_f[a][r] = hll_estimate(&rows.hll[(r * plan.n_hll + pa.hll_index) * HLL_M]);
+        continue;
+      }
+      uint64_t raw = rows.slots[r * ns + pa.slot];
+      if (pa.const_times_count) as.agg_i[a][r] = (int64_t)raw * pa.const_value;
+      else if (pa.slot_is_f64_ord) as.agg_f[a][r] = ord_to_f64((int64_t)raw);
+      else if (pa.out_float) { double d; memcpy(&d, &raw, 8); as.agg_f[a][r] = d; }
+      else as.agg_i[a][r] = (int64_t)raw;
+    }
+  }
+  as.post.resize(q.post_aggregations.size());
+  for (size_t pi = 0; pi < q.post_aggregations.size(); pi++) {
+    as.post[pi].resize(n);
+    for (uint64_t r = 0; r < n; r++) as.post[pi][r] = as.eval_post(q.post_aggregations[pi], r, pi);
+  }
+
+  // decode keys
+  std::vector<uint32_t> tk(plan.has_time_key ? n : 0);
+  std::vector<std::vector<uint32_t>> dim_ids(plan.dims.size());
+  for (size_t d = 0; d < plan.dims.size(); d++)
+    if (!plan.dims[d].is_time) dim_ids[d].resize(n);
+  for (uint64_t r = 0; r < n; r++) {
+    uint64_t k = rows.keys[r];
+    if (plan.has_time_key) tk[r] = (uint32_t)(k / plan.tk_stride);
+    for (size_t d = 0; d < plan.dims.size(); d++) {
+      const PlanDim& pd = plan.dims[d];
+      if (pd.is_time) continue;
+      dim_ids[d][r] = (uint32_t)((k / pd.stride) % pd.card);
+    }
+  }
+
+  // having, ordering, limit
+  std::vector<uint64_t> order(n);
+  std::iota(order.begin(), order.end(), 0);
+  if (q.has_having) {
+    size_t w = 0;
+    for (uint64_t r = 0; r < n; r++)
+      if (as.eval_having(q.having, r)) order[w++] = r;
+    order.resize(w);
+  }
+  int64_t limit = -1;
+  auto dim_cmp = [&](size_t d, uint64_t a, uint64_t b) -> int {
+    const PlanDim& pd = plan.dims[d];
+    if (pd.is_time) {
+      const std::string& x = plan.time_keys[tk[a]].formatted[pd.time_fmt];
+      const std::string& y = plan.time_keys[tk[b]].formatted[pd.time_fmt];
+      return utf8_cmp(x.data(), x.size(), y.data(), y.size());
+    }
+    return dim_ids[d][a] < dim_ids[d][b] ? -1 : (dim_ids[d][a] > dim_ids[d][b] ? 1 : 0);
+  };
+  auto key_less = [&](uint64_t a, uint64_t b) { return rows.keys[a] < rows.keys[b]; };
+  if (q.type == QuerySpec::TopN) {
+    // TopNMetricSpec: numeric = descending, inverted = ascending, lexicographic by dimension value
+    // (QuerySpecTransforms.scala:281-298)
+    limit = q.threshold;
+    if (q.metric.kind == TopNMetric::Numeric) {
+      std::vector<double> v(n);
+      for (uint64_t r : order)
+        if (!as.named_value(q.metric.metric, r, &v[r], as.post.size())) throw Invalid("topN metric '" + q.metric.metric + "' is not an aggregation");
+      const bool desc = !q.metric.inverted;
+      std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+        if (v[a] != v[b]) return desc ? v[a] > v[b] : v[a] < v[b];
+        return key_less(a, b);
+      });
+    } else {
+      const bool desc = q.metric.inverted;
+      if (!q.metric.previous_stop.empty()) {
+        const std::string& ps = q.metric.previous_stop;
+        size_t w = 0;
+        for (uint64_t r : order) {
+          std::string val;
+          const PlanDim& pd = plan.dims[0];
+          if (pd.is_time) val = plan.time_keys[tk[r]].formatted[pd.time_fmt];
+          else if (plan.ds->dims[pd.ds_dim].enc == DimEncoding::Dict) val = plan.ds->dims[pd.ds_dim].dict->get(dim_ids[0][r]);
+          else val = std::to_string(dim_ids[0][r]);
+          int c = utf8_cmp(val.data(), val.size(), ps.data(), ps.size());
+          if (desc ? c < 0 : c > 0) order[w++] = r;
+        }
+        order.resize(w);
+      }
+      std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+        int c = dim_cmp(0, a, b);
+        if (c) return desc ? c > 0 : c < 0;
+        return key_less(a, b);
+      });
+    }
+  } else if (q.type == QuerySpec::GroupBy && q.limit.present) {
+    // LimitSpec / OrderByColumnSpec (DruidQuerySpec.scala:437-456); sort without limit = Int.MaxValue
+    limit = q.limit.limit;
+    struct Ord { int dim; int agg; int post; bool asc; bool ts; };
+    std::vector<Ord> ords;
+    for (auto& c : q.limit.columns) {
+      Ord o{-1, -1, -1, c.ascending, false};
+      for (size_t d = 0; d < plan.dims.size(); d++)
+        if (plan.dims[d].output_name == c.dimension) o.dim = (int)d;
+      if (o.dim < 0) o.agg = as.find_agg(c.dimension);
+      if (o.dim < 0 && o.agg < 0) o.post = as.find_post(c.dimension);
+      if (o.dim < 0 && o.agg < 0 && o.post < 0) {
+        if (c.dimension == "timestamp" || c.dimension == "__time") o.ts = true;
+        else throw Invalid("limitSpec orders by unknown column '" + c.dimension + "'");
+      }
+      ords.push_back(o);
+    }
+    if (!device_topk || ords.size() != 1) {
+      std::sort(order.begin(), order.end(), [&](uint64_t a, uint64_t b) {
+        for (auto& o : ords) {
+          int c = 0;
+          if (o.dim >= 0) c = dim_cmp((size_t)o.dim, a, b);
+          else if (o.ts) {
+            int64_t x = plan.time_keys[tk[a]].bucket, y = plan.time_keys[tk[b]].bucket;
+            c = x < y ? -1 : (x > y ? 1 : 0);
+          } else {
+            double x, y;
+            if (o.agg >= 0) {
+              if (!plan.aggs[o.agg].out_float) {
+                int64_t xi = as.agg_i[o.agg][a], yi = as.agg_i[o.agg][b];
+                c = xi < yi ? -1 : (xi > yi ? 1 : 0);
+                if (c) return o.asc ? c < 0 : c > 0;
+                continue;
+              }
+              x = as.agg_f[o.agg][a]; y = as.agg_f[o.agg][b];
+            } else { x = as.post[o.post][a]; y = as.post[o.post][b]; }
+            c = x < y ? -1 : (x > y ? 1 : 0);
+          }
+          if (c) return o.asc ? c < 0 : c > 0;
+        }
+        return key_less(a, b);
+      });
+    }
+  } else if (n <= (4u << 20)) {
+    std::sort(order.begin(), order.end(), key_less);  // deterministic output for small results
+  }
+  if (limit >= 0 && (uint64_t)limit < order.size()) order.resize((size_t)limit);
+
+  // ---- columns (DruidQuerySpec.scala:614-627: dimensions, aggregations, post-aggregations) --------
+  std::unique_ptr<Result> res(new Result());
+  const uint64_t m = order.size();
+  res->n_rows = (int64_t)m;
+  if (plan.has_bucket) {
+    ResultColumn c;
+    c.name = "timestamp";
+    c.type = SDO_RES_TIMESTAMP;
+    c.i64.resize(m);
+    for (uint64_t i = 0; i < m; i++) c.i64[i] = plan.time_keys[tk[order[i]]].bucket;
+    res->columns.push_back(std::move(c));
+  }
+  for (size_t d = 0; d < plan.dims.size(); d++) {
+    const PlanDim& pd = plan.dims[d];
+    ResultColumn c;
+    c.name = pd.output_name;
+    if (pd.is_time) {
+      c.type = SDO_RES_STRING;
+      c.dict = std::make_shared<Dictionary>();
+      std::map<std::string, uint32_t> seen;
+      c.ids.resize(m);
+      for (uint64_t i = 0; i < m; i++) {
+        const std::string& v = plan.time_keys[tk[order[i]]].formatted[pd.time_fmt];
+        auto it = seen.find(v);
+        if (it == seen.end()) {
+          it = seen.emplace(v, (uint32_t)c.dict->size()).first;
+          c.dict->push(v.data(), v.size());
+        }
+        c.ids[i] = it->second;
+      }
+    } else if (plan.ds->dims[pd.ds_dim].enc == DimEncoding::Dict) {
+      c.type = SDO_RES_STRING;
+      c.dict = plan.ds->dims[pd.ds_dim].dict;
+      c.ids.resize(m);
+      for (uint64_t i = 0; i < m; i++) c.ids[i] = dim_ids[d][order[i]];
+    } else {
+      c.type = SDO_RES_DIM_INT64;
+      c.i64.resize(m);
+      for (uint64_t i = 0; i < m; i++) c.i64[i] = (int64_t)dim_ids[d][order[i]];
+    }
+    res->columns.push_back(std::move(c));
+  }
+  for (size_t a = 0; a < plan.aggs.size(); a++) {
+    const PlanAgg& pa = plan.aggs[a];
+    ResultColumn c;
+    c.name = pa.name;
+    if (pa.out_float) {
+      c.type = SDO_RES_FLOAT64;
+      c.f64.resize(m);
+      for (uint64_t i = 0; i < m; i++) c.f64[i] = as.agg_f[a][order[i]];
+      if (pa.hll_index >= 0) {
+        c.hll.resize(m * HLL_M);
+        for (uint64_t i = 0; i < m; i++) memcpy(&c.hll[i * HLL_M], &rows.hll[(order[i] * plan.n_hll + pa.hll_index) * HLL_M], HLL_M);
+      }
+    } else {
+      c.type = SDO_RES_INT64;
+      c.i64.resize(m);
+      for (uint64_t i = 0; i < m; i++) c.i64[i] = as.agg_i[a][order[i]];
+    }
+    res->columns.push_back(std::move(c));
+  }
+  for (size_t pi = 0; pi < q.post_aggregations.size(); pi++) {
+    ResultColumn c;
+    c.name = q.post_aggregations[pi].name;
+    c.type = SDO_RES_FLOAT64;
+    c.f64.resize(m);
+    for (uint64_t i = 0; i < m; i++) c.f64[i] = as.post[pi][order[i]];
+    res->columns.push_back(std::move(c));
+  }
+
+  // ---- stats (DruidQueryExecutionView analogue, DruidRDD.scala:194-216) ------------------------------
+  char buf[1024];
+  snprintf(buf, sizeof buf,
+           "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
+           "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
+           "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":%s,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu}",
+           plan.always_false ? "none" : strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row,
+           (long long)plan.algorithmic_bytes, (unsigned long long)n, (unsigned long long)m, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms,
+           st->launches, st->h2d_bytes, st->d2h_bytes, device_topk ? "true" : "false", plan.spans.size(), plan.seg_index.size(),
+           (unsigned long long)plan.n_keys);
+  res->stats = buf;
+  return res.release();
+}
+
+Result* Engine::execute(const char* json, size_t len) {
+  const double t0 = now_ms();
+  QuerySpec spec = parse_query_spec(json, len);
+  check_cancel(spec.query_id);
+  auto ds = store_.get(spec.data_source);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  Plan plan = make_plan(spec, ds, opt_);
+  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+  QueryCtx* ctx = acquire_ctx();
+  ScanState st;
+  Result* r = nullptr;
+  try {
+    if (!plan.always_false) run_scan(ctx, plan, &st);
+    check_cancel(spec.query_id);
+    r = finalize(ctx, plan, &st, t0);
+  } catch (...) {
+    cudaStreamSynchronize(ctx->stream);
+    free_state(ctx, &st);
+    release_ctx(ctx);
+    throw;
+  }
+  free_state(ctx, &st);
+  release_ctx(ctx);
+  return r;
+}
+
+std::string Engine::explain(const char* json, size_t len) {
+  QuerySpec spec = parse_query_spec(json, len);
+  auto ds = store_.get(spec.data_source);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  Plan plan = make_plan(spec, ds, opt_);
+  return explain_json(plan);
+}
+
+// ---- sharded execution ---------------------------------------------------------------------------------
+Partial* Engine::partial(const char* json, size_t len) {
+  QuerySpec spec = parse_query_spec(json, len);
+  auto ds = store_.get(spec.data_source);
+  std::unique_ptr<Partial> p(new Partial());
+  p->engine = this;
+  p->ds = ds;
+  ds->mu.lock_shared();
+  try {
+    p->plan = make_plan(spec, ds, opt_);
+    if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+    p->ctx = acquire_ctx();
+    // every rank must produce the same table layout even when its own shard has no matching rows:
+    // scan zero units, so the tables are initialised and nothing is added
+    if (p->plan.always_false) {
+      p->plan.spans.clear();
+      p->plan.n_units = 0;
+      p->plan.coarse.assign(2, 0);
+      p->plan.rows_scanned = 0;
+      p->plan.always_false = false;
+    }
+    run_scan(p->ctx, p->plan, &p->st);
+    if (p->st.strategy == STRAT_HASH) compact_rows(p->ctx, p->plan, &p->st);
+    for (int i = 0; i < p->plan.n_slots; i++) p->slot_ops.push_back(p->plan.slot_op[i]);
+  } catch (...) {
+    if (p->ctx) {
+      cudaStreamSynchronize(p->ctx->stream);
+      free_state(p->ctx, &p->st);
+      release_ctx(p->ctx);
+    }
+    ds->mu.unlock_shared();
+    throw;
+  }
+  return p.release();
+}
+
+void Engine::partial_view(Partial* p, void* out_) {
+  sdo_partial_view* v = (sdo_partial_view*)out_;
+  memset(v, 0, sizeof *v);
+  v->n_slots = p->plan.n_slots;
+  v->slot_ops = p->slot_ops.data();
+  v->n_hll = p->plan.n_hll;
+  if (p->st.strategy == STRAT_HASH || p->st.rows_valid) {
+    v->dense = 0;
+    v->n_keys = (int64_t)p->st.n_rows;
+    v->keys = p->st.rows_keys;
+    v->slots = p->st.rows_slots;
+    v->hll = p->st.rows_hll;
+  } else {
+    v->dense = 1;
+    v->n_keys = (int64_t)p->st.table_rows;
+    v->keys = nullptr;
+    v->slots = p->st.table;
+    v->hll = p->st.hll;
+  }
+}
+
+void Engine::partial_partition(Partial* p, int n_ranks, int64_t* counts_out) {
+  if (!p->st.rows_valid) throw Invalid("sdo_partial_partition applies to sparse partials only");
+  if (n_ranks < 1 || n_ranks > 64) throw Invalid("n_ranks out of range");
+  SDO_CUDA(cudaSetDevice(device_));
+  cudaStream_t s = p->ctx->stream;
+  const int ns = p->plan.n_slots;
+  const uint64_t n = p->st.n_rows;
+  unsigned long long *counts = nullptr, *ok = nullptr, *os = nullptr;
+  SDO_CUDA(cudaMallocAsync((void**)&counts, 2 * 64 * 8, s));
+  SDO_CUDA(cudaMemsetAsync(counts, 0, 2 * 64 * 8, s));
+  launch_partition_rows(p->st.rows_keys, p->st.rows_slots, n, ns, n_ranks, nullptr, nullptr, counts, nullptr, s);
+  unsigned long long h[64] = {0}, cur[64] = {0};
+  SDO_CUDA(cudaMemcpyAsync(h, counts, (size_t)n_ranks * 8, cudaMemcpyDeviceToHost, s));
+  SDO_CUDA(cudaStreamSynchronize(s));
+  unsigned long long run = 0;
+  for (int r = 0; r < n_ranks; r++) { cur[r] = run; run += h[r]; counts_out[r] = (int64_t)h[r]; }
+  SDO_CUDA(cudaMemcpyAsync(counts + 64, cur, (size_t)n_ranks * 8, cudaMemcpyHostToDevice, s));
+  SDO_CUDA(cudaMallocAsync((void**)&ok, std::max<uint64_t>(n, 1) * 8, s));
+  SDO_CUDA(cudaMallocAsync((void**)&os, std::max<uint64_t>(n, 1) * ns * 8, s));
+  launch_partition_rows(p->st.rows_keys, p->st.rows_slots, n, ns, n_ranks, ok, os, counts, counts + 64, s);
+  SDO_CUDA(cudaStreamSynchronize(s));
+  SDO_CUDA(cudaFreeAsync(p->st.rows_keys, s));
+  SDO_CUDA(cudaFreeAsync(p->st.rows_slots, s));
+  SDO_CUDA(cudaFreeAsync(counts, s));
+  p->st.rows_keys = ok;
+  p->st.rows_slots = os;
+}
+
+void Engine::partial_merge_rows(Partial* p, const void* keys, const void* slots, int64_t n) {
+  if (!p->st.rows_valid) throw Invalid("sdo_partial_merge_rows applies to sparse partials only");
+  if (p->plan.n_hll) throw Unsupported("cardinality aggregations cannot be merged on the sparse path");
+  SDO_CUDA(cudaSetDevice(device_));
+  cudaStream_t s = p->ctx->stream;
+  ScanState& st = p->st;
+  const int ns = p->plan.n_slots;
+  // fresh table sized for the received rows
+  for (void* q : {(void*)st.table, (void*)st.hkeys, (void*)st.rows_keys, (void*)st.rows_slots})
+    if (q) SDO_CUDA(cudaFreeAsync(q, s));
+  st.table = nullptr; st.hkeys = nullptr; st.rows_keys = nullptr; st.rows_slots = nullptr;
+  uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, (uint64_t)n + (uint64_t)n / 2));
+  SDO_CUDA(cudaMallocAsync((void**)&st.hkeys, cap * 8, s));
+  SDO_CUDA(cudaMallocAsync((void**)&st.table, cap * (uint64_t)ns * 8, s));
+  st.params.hkeys = st.hkeys;
+  st.params.hmask = cap - 1;
+  st.params.table = st.table;
+  st.table_rows = cap;
+  st.strategy = STRAT_HASH;
+  SDO_CUDA(cudaMemsetAsync(p->ctx->counters, 0, 64, s));
+  launch_fill_u64(st.hkeys, cap, HASH_EMPTY, s);
+  launch_fill_slots(st.table, cap, ns, nullptr, st.params, s);
+  launch_merge_rows((const unsigned long long*)keys, (const unsigned long long*)slots, (uint64_t)n, st.params, s);
+  st.launches += 3;
+  st.rows_valid = false;
+  // rows_scanned bounds the compaction buffer
+  p->plan.rows_scanned = std::max<int64_t>(p->plan.rows_scanned, n);
+  compact_rows(p->ctx, p->plan, &st);
+}
+
+Result* Engine::partial_finish(Partial* p) {
+  SDO_CUDA(cudaSetDevice(device_));
+  Result* r = finalize(p->ctx, p->plan, &p->st, now_ms());
+  p->finished = true;
+  return r;
+}
+
+void Engine::partial_free(Partial* p) {
+  if (!p) return;
+  if (p->ctx) {
+    cudaSetDevice(device_);
+    cudaStreamSynchronize(p->ctx->stream);
+    free_state(p->ctx, &p->st);
+    release_ctx(p->ctx);
+  }
+  p->ds->mu.unlock_shared();
+  delete p;
+}
+
+}  // namespace sdo

@@ -1,0 +1,118 @@
+// Engine: owns the segment store and runs query plans on one GPU.
+// Replaces the execution behind DruidRDD.compute (DruidRDD.scala:152-242): where the reference
+// posts the query to a broker/historical and streams JSON rows back, the engine launches the scan
+// kernels on its HBM-resident segments and returns a columnar result.
+#pragma once
+#include <atomic>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "plan.hpp"
+#include "store.hpp"
+
+namespace sdo {
+
+struct ResultColumn {
+  std::string name;
+  int type = 0;  // sdo_res_type
+  std::vector<int64_t> i64;
+  std::vector<double> f64;
+  std::vector<uint32_t> ids;
+  std::shared_ptr<Dictionary> dict;  // STRING
+  std::vector<uint8_t> hll;          // cardinality columns: n_rows * 512 registers
+};
+
+struct Result {
+  int64_t n_rows = 0;
+  std::vector<ResultColumn> columns;
+  std::string stats;
+};
+
+// one in-flight query's device resources
+struct QueryCtx {
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  void* pinned_in = nullptr;
+  size_t pinned_in_bytes = 0;
+  void* pinned_out = nullptr;
+  size_t pinned_out_bytes = 0;
+  unsigned int* counters = nullptr;  // device: [0] chunk ticket [1] overflow; +8 bytes: u64 compaction counter
+};
+
+// device state of a finished scan (before finalisation / merging)
+struct ScanState {
+  ScanParams params{};
+  int strategy = 0;
+  uint64_t table_rows = 0;   // dense: n_keys; hash: capacity
+  unsigned long long* table = nullptr;
+  unsigned long long* hkeys = nullptr;
+  uint8_t* hll = nullptr;
+  void* blob = nullptr;      // per-query device blob (spans, coarse index, segptr, bitsets)
+  unsigned long long* partials = nullptr;
+  int launches = 0;
+  size_t h2d_bytes = 0, d2h_bytes = 0;
+  float scan_ms = 0;
+  // sparse rows after compaction / merging (multi-GPU)
+  unsigned long long* rows_keys = nullptr;
+  unsigned long long* rows_slots = nullptr;
+  uint8_t* rows_hll = nullptr;
+  uint64_t n_rows = 0;
+  bool rows_valid = false;
+};
+
+class Engine;
+struct Partial {
+  Engine* engine = nullptr;
+  std::shared_ptr<DataSource> ds;
+  Plan plan;
+  ScanState st;
+  QueryCtx* ctx = nullptr;
+  std::vector<int> slot_ops;
+  bool finished = false;
+};
+
+class Engine {
+ public:
+  explicit Engine(int device);
+  ~Engine();
+  Store& store() { return store_; }
+  int device() const { return device_; }
+  Result* execute(const char* json, size_t len);
+  std::string explain(const char* json, size_t len);
+  void cancel(const std::string& query_id);
+  Partial* partial(const char* json, size_t len);
+  void partial_view(Partial* p, void* view_out);
+  void partial_partition(Partial* p, int n_ranks, int64_t* counts_out);
+  void partial_merge_rows(Partial* p, const void* keys, const void* slots, int64_t n);
+  Result* partial_finish(Partial* p);
+  void partial_free(Partial* p);
+
+ private:
+  int device_;
+  int sm_count_ = 148;
+  Store store_;
+  PlanOptions opt_;
+  std::mutex ctx_mu_;
+  std::vector<QueryCtx*> free_ctx_;
+  std::mutex cancel_mu_;
+  std::set<std::string> cancelled_;
+  std::mutex lut_mu_;
+
+  QueryCtx* acquire_ctx();
+  void release_ctx(QueryCtx* c);
+  void ensure_pinned(void** p, size_t* cur, size_t need);
+  void check_cancel(const std::string& qid);
+  void run_scan(QueryCtx* ctx, Plan& plan, ScanState* st);
+  void compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st);
+  Result* finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
+  void free_state(QueryCtx* ctx, ScanState* st);
+  const uint16_t* ensure_hll_lut(DataSource& ds, int di, cudaStream_t st);
+};
+
+double hll_estimate(const uint8_t* regs);
+
+}  // namespace sdo

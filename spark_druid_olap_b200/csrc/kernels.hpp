@@ -1,0 +1,150 @@
+// Device-side contract of the scan / filter / aggregate kernels (kernels.cu) and their launchers.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+
+namespace sdo {
+
+constexpr int MAX_LEAVES = 12;
+constexpr int MAX_OPS = 32;
+constexpr int MAX_DIMS = 8;
+constexpr int MAX_AGGS = 16;
+constexpr int MAX_SLOTS = MAX_AGGS + 1;
+constexpr int SCAN_THREADS = 256;
+constexpr int ROWS_PER_THREAD = 4;
+constexpr int UNIT_ROWS = SCAN_THREADS * ROWS_PER_THREAD;  // 1024 rows: one pass of a block
+constexpr uint64_t HASH_EMPTY = 0xFFFFFFFFFFFFFFFFull;
+
+// A span is a run of rows of one segment that shares its time-derived key part; interval pruning
+// and time bucketing are resolved to spans on the host, so kernels never read a time column.
+struct DevSpan {
+  uint32_t seg;         // index into segptr rows
+  uint32_t row_begin;   // first row (inclusive), segment-relative
+  uint32_t row_end;     // last row (exclusive)
+  uint32_t unit_begin;  // units (of UNIT_ROWS rows, from row_begin & ~3) before this span
+  uint64_t key_base;    // time-derived key component
+};
+
+enum LeafKind : int32_t { LEAF_RANGE = 0, LEAF_BITSET = 1 };
+struct DevLeaf {
+  int32_t col;    // column slot in segptr row
+  int32_t width;  // id bytes: 1, 2, 4
+  int32_t kind;
+  uint32_t lo, hi;       // RANGE: lo <= id < hi
+  const uint32_t* bits;  // BITSET over ids
+};
+enum FilterOp : uint8_t { FOP_LEAF = 0, FOP_AND = 1, FOP_OR = 2, FOP_NOT = 3, FOP_TRUE = 4, FOP_FALSE = 5 };
+
+struct DevDim {
+  int32_t col;
+  int32_t width;
+  uint64_t stride;
+};
+
+// how a row value reaches its 8-byte slot
+enum AggOp : int32_t {
+  AGG_SUM_I64 = 0,      // int64 metric
+  AGG_SUM_F64 = 1,      // float64 metric
+  AGG_MIN_I64 = 2,
+  AGG_MAX_I64 = 3,
+  AGG_MIN_F64 = 4,      // kept as order-preserving int64
+  AGG_MAX_F64 = 5,
+  AGG_SUM_F64_I64 = 6,  // doubleSum over an int64 metric
+  AGG_SUM_I64_F64 = 7,  // longSum over a float64 metric (truncating cast per row, as Druid)
+  AGG_COUNT_IF = 8,     // filtered count: adds 1 where the aggregator's own filter matches
+  AGG_HLL = 9,          // cardinality: HLL++ registers, no slot
+  AGG_MIN_F64_I64 = 10,
+  AGG_MAX_F64_I64 = 11,
+  AGG_MIN_I64_F64 = 12,
+  AGG_MAX_I64_F64 = 13,
+};
+// how two partial slots merge (PostAggregate.scala:39-60: count/sum -> sum, min -> min, max -> max)
+enum SlotOp : int32_t { SLOT_SUM_I64 = 0, SLOT_SUM_F64 = 1, SLOT_MIN_I64 = 2, SLOT_MAX_I64 = 3 };
+
+enum HllMode : int32_t { HLL_DIRECT_INT = 0, HLL_DIRECT_LONG = 1, HLL_LUT = 2 };
+struct DevAgg {
+  int32_t op;
+  int32_t col;        // metric column slot (or dimension slot for HLL)
+  int32_t slot;       // 8-byte slot index within the group row (slot 0 = row count)
+  int32_t leaf;       // filtered aggregation: leaf index, else -1
+  int32_t width;      // HLL: id width
+  int32_t hll_index;  // HLL: which register set of the group
+  int32_t hll_mode;
+  int32_t pad;
+  const uint16_t* hll_lut;  // HLL_LUT: id -> (idx << 6 | rho)
+};
+
+enum Strategy : int32_t {
+  STRAT_LANE = 0,   // lane-private shared-memory accumulators (tiny key spaces)
+  STRAT_BLOCK = 1,  // block-shared shared-memory table with shared atomics
+  STRAT_HASH = 2,   // open-addressing global hash table (atomicCAS)
+  STRAT_GLOBAL = 3, // direct-indexed global table (dense key space too big for shared memory)
+};
+
+struct ScanParams {
+  const DevSpan* spans;  // n_spans + 1 entries (sentinel carries unit_begin = n_units)
+  uint32_t n_spans;
+  uint32_t n_units;
+  uint32_t units_per_chunk;
+  uint32_t n_cols;
+  const void* const* segptr;  // [segment][n_cols] column base pointers
+  int32_t n_leaves, n_ops;
+  DevLeaf leaves[MAX_LEAVES];
+  uint8_t op_code[MAX_OPS];
+  uint8_t op_arg[MAX_OPS];
+  int32_t n_dims;
+  DevDim dims[MAX_DIMS];
+  int32_t n_aggs;
+  DevAgg aggs[MAX_AGGS];
+  int32_t n_slots;  // per group, slot 0 = row count
+  int32_t n_hll;
+  uint64_t n_keys;  // dense key-space size (LANE / BLOCK / GLOBAL)
+  int32_t slot_op[MAX_SLOTS];
+  uint64_t slot_init[MAX_SLOTS];
+  unsigned long long* table;    // LANE: partials [grid][n_keys*n_slots]; BLOCK/GLOBAL: [n_keys*n_slots]; HASH: [cap*n_slots]
+  uint8_t* hll;                 // [n_keys or cap][n_hll][512]
+  unsigned long long* hkeys;    // HASH: [cap]
+  uint64_t hmask;               // HASH: cap - 1
+  unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
+};
+
+// ---- launchers (host) ---------------------------------------------------------------------------
+// loader helpers
+void launch_encode_dim(const void* src, bool src64, const int32_t* perm, int64_t r0, int64_t n, const uint32_t* lut,
+                       void* dst, int dst_width, cudaStream_t st);
+void launch_reencode(const void* src, int src_width, void* dst, int dst_width, int64_t n, const uint32_t* lut, cudaStream_t st);
+void launch_gather64(const void* src, const int32_t* perm, int64_t r0, int64_t n, void* dst, cudaStream_t st);
+// HLL lookup table of a string dictionary: lut[i] = hll_pack(xxh64(bytes of entry i))
+void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n, uint16_t* lut, cudaStream_t st);
+
+// scan
+size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots);
+int scan_grid_size(int strategy, size_t smem_bytes, int sm_count);
+void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem_bytes, cudaStream_t st);
+void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, const uint64_t* slot_init_dev_or_null,
+                       const ScanParams& p, cudaStream_t st);
+void launch_fill_u64(unsigned long long* dst, uint64_t n, unsigned long long v, cudaStream_t st);
+void launch_reduce_partials(const unsigned long long* partials, int n_blocks, uint32_t n, int n_slots, const ScanParams& p,
+                            unsigned long long* out, cudaStream_t st);
+// compaction of non-empty groups: dense tables (keyed by slot 0 > 0) and hash tables
+void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int n_slots, unsigned long long* out_keys,
+                          unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st);
+void launch_compact_hash(const unsigned long long* hkeys, const unsigned long long* table, uint64_t cap, int n_slots,
+                         unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
+                         unsigned long long* counter, cudaStream_t st);
+void launch_gather_hll(const uint8_t* hll, const unsigned long long* src, uint64_t n, int n_hll, uint8_t* out, cudaStream_t st);
+// top-k of (metric, key) rows: ord = order-preserving u64 of the metric (descending = larger first)
+void launch_topk(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int slot, int slot_is_f64,
+                 int descending, int k, unsigned long long* scratch_a, unsigned long long* scratch_b, unsigned long long* out_idx,
+                 cudaStream_t st);
+size_t topk_scratch_elems(uint64_t n, int k);
+void launch_gather_rows(const unsigned long long* keys, const unsigned long long* slots, const unsigned long long* idx, uint64_t k, int ns,
+                        unsigned long long* out_keys, unsigned long long* out_slots, cudaStream_t st);
+// sparse multi-GPU merge helpers
+void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
+                           unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,
+                           unsigned long long* cursors_dev, cudaStream_t st);
+void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
+
+}  // namespace sdo

@@ -1,0 +1,540 @@
+#include "store.hpp"
+
+#include <algorithm>
+#include <cstring>
+#include <numeric>
+#include <unordered_map>
+
+#include "kernels.hpp"
+
+namespace sdo {
+
+int utf8_cmp(const char* a, size_t na, const char* b, size_t nb) {
+  int c = memcmp(a, b, std::min(na, nb));  // memcmp compares as unsigned char
+  if (c) return c;
+  return na < nb ? -1 : (na > nb ? 1 : 0);
+}
+int64_t Dictionary::lower_bound(const std::string& s) const {
+  int64_t lo = 0, hi = size();
+  while (lo < hi) {
+    int64_t mid = (lo + hi) / 2;
+    if (utf8_cmp(data(mid), len(mid), s.data(), s.size()) < 0) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+int64_t Dictionary::upper_bound(const std::string& s) const {
+  int64_t lo = 0, hi = size();
+  while (lo < hi) {
+    int64_t mid = (lo + hi) / 2;
+    if (utf8_cmp(data(mid), len(mid), s.data(), s.size()) <= 0) lo = mid + 1;
+    else hi = mid;
+  }
+  return lo;
+}
+int64_t Dictionary::find(const std::string& s) const {
+  int64_t i = lower_bound(s);
+  if (i < size() && len(i) == s.size() && !memcmp(data(i), s.data(), s.size())) return i;
+  return -1;
+}
+
+int DataSource::dim_index(const std::string& n) const {
+  for (size_t i = 0; i < dims.size(); i++)
+    if (dims[i].name == n) return (int)i;
+  return -1;
+}
+int DataSource::metric_index(const std::string& n) const {
+  for (size_t i = 0; i < metrics.size(); i++)
+    if (metrics[i].name == n) return (int)i;
+  return -1;
+}
+
+static std::string upper(std::string s) {
+  for (auto& c : s) c = (char)toupper((unsigned char)c);
+  return s;
+}
+
+int64_t truncate_time(const std::string& gran, int64_t t) {
+  if (gran == "NONE") return t;
+  if (gran == "ALL") return t;
+  Granularity g = simple_granularity(gran);
+  return bucket_start(g, t);
+}
+int64_t segment_start(const std::string& gran, int64_t t) {
+  if (gran == "ALL") return INT64_MIN / 2;
+  Granularity g = simple_granularity(gran);
+  return bucket_start(g, t);
+}
+int64_t segment_end(const std::string& gran, int64_t start) {
+  if (gran == "ALL") return INT64_MAX / 2;
+  Granularity g = simple_granularity(gran);
+  if (g.months) {
+    Civil c = civil_from_ms(start, 0);
+    int64_t midx = c.year * 12 + (c.month - 1) + g.months;
+    return days_from_civil(floordiv(midx, 12), (int)floormod(midx, 12) + 1, 1) * MS_DAY;
+  }
+  return start + g.period_ms;
+}
+
+Store::~Store() {
+  for (auto& kv : sources_) {
+    for (auto& s : kv.second->segments) free_segment(*s);
+    for (auto& d : kv.second->dims)
+      if (d.hll_lut) cudaFree(d.hll_lut);
+  }
+}
+
+void Store::free_segment(Segment& s) {
+  if (device_ < 0) return;
+  for (void* p : s.dim_data)
+    if (p) cudaFree(p);
+  for (void* p : s.metric_data)
+    if (p) cudaFree(p);
+  s.dim_data.clear();
+  s.metric_data.clear();
+}
+
+void Store::create(const std::string& name, const std::string& options_json) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (sources_.count(name)) throw Invalid("datasource '" + name + "' already exists");
+  auto ds = std::make_shared<DataSource>();
+  ds->name = name;
+  if (!options_json.empty()) {
+    Json o;
+    try {
+      o = json_parse(options_json.data(), options_json.size());
+    } catch (const JsonError& e) {
+      throw Invalid(e.what());
+    }
+    ds->segment_granularity = upper(o.get_str("segmentGranularity", "MONTH"));
+    ds->query_granularity = upper(o.get_str("queryGranularity", "DAY"));
+  }
+  // validate names early
+  segment_start(ds->segment_granularity, 0);
+  truncate_time(ds->query_granularity, 0);
+  sources_[name] = ds;
+}
+
+void Store::drop(const std::string& name) {
+  std::shared_ptr<DataSource> ds;
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    auto it = sources_.find(name);
+    if (it == sources_.end()) throw NotFound("unknown datasource '" + name + "'");
+    ds = it->second;
+    sources_.erase(it);
+  }
+  std::unique_lock<std::shared_mutex> lk(ds->mu);  // waits for running queries
+  if (device_ >= 0) SDO_CUDA(cudaSetDevice(device_));
+  for (auto& s : ds->segments) free_segment(*s);
+  ds->segments.clear();
+  for (auto& d : ds->dims)
+    if (d.hll_lut) { cudaFree(d.hll_lut); d.hll_lut = nullptr; }
+}
+
+std::shared_ptr<DataSource> Store::get(const std::string& name) const {
+  std::lock_guard<std::mutex> lk(mu_);
+  auto it = sources_.find(name);
+  if (it == sources_.end()) throw NotFound("unknown datasource '" + name + "'");
+  return it->second;
+}
+
+static int width_for(int64_t card) { return card <= 256 ? 1 : (card <= 65536 ? 2 : 4); }
+
+namespace {
+struct DevBuf {
+  void* p = nullptr;
+  explicit DevBuf(size_t n) { SDO_CUDA(cudaMalloc(&p, std::max<size_t>(n, 256))); }
+  ~DevBuf() { if (p) cudaFree(p); }
+  DevBuf(const DevBuf&) = delete;
+  DevBuf& operator=(const DevBuf&) = delete;
+};
+// segment column arrays are padded so that 16-byte vector loads past n_rows stay in bounds
+size_t padded_bytes(int64_t n_rows, int width) { return round_up((size_t)n_rows * width + 64, 256); }
+}  // namespace
+
+void Store::load(const std::string& name, int64_t n_rows, const std::vector<LoadColumn>& cols, int partition) {
+  auto ds = get(name);
+  std::unique_lock<std::shared_mutex> lk(ds->mu);
+  if (n_rows < 0 || n_rows > 2147483647ll) throw Invalid("sdo_segment_load: n_rows must be in [0, 2^31)");
+  if (n_rows == 0) return;
+  const bool dev = device_ >= 0;
+  if (dev) SDO_CUDA(cudaSetDevice(device_));
+
+  // ---- time: truncate, order, cut -----------------------------------------------------------
+  const LoadColumn* tc = nullptr;
+  for (auto& c : cols)
+    if (c.kind == 0) {
+      if (tc) throw Invalid("more than one time column");
+      tc = &c;
+    }
+  if (!tc || tc->type != 0 || !tc->data) throw Invalid("sdo_segment_load needs one SDO_COL_TIME column of type SDO_T_INT64");
+  const int64_t* traw = (const int64_t*)tc->data;
+  std::vector<int64_t> tt((size_t)n_rows);
+  bool sorted = true;
+  {
+    const std::string& qg = ds->query_granularity;
+    if (qg == "NONE" || qg == "ALL") {
+      memcpy(tt.data(), traw, (size_t)n_rows * 8);
+    } else {
+      Granularity g = simple_granularity(qg);
+      // fast path for fixed periods aligned to the epoch (DAY, HOUR, ...)
+      if (!g.months && g.period_ms > 0 && g.period_ms % (7 * MS_DAY) != 0) {
+        const int64_t p = g.period_ms;
+        for (int64_t i = 0; i < n_rows; i++) tt[i] = traw[i] - floormod(traw[i], p);
+      } else {
+        for (int64_t i = 0; i < n_rows; i++) tt[i] = bucket_start(g, traw[i]);
+      }
+    }
+    for (int64_t i = 1; i < n_rows; i++)
+      if (tt[i] < tt[i - 1]) { sorted = false; break; }
+  }
+  std::vector<int32_t> perm;
+  if (!sorted) {
+    perm.resize((size_t)n_rows);
+    std::iota(perm.begin(), perm.end(), 0);
+    std::stable_sort(perm.begin(), perm.end(), [&](int32_t a, int32_t b) { return tt[a] < tt[b]; });
+    std::vector<int64_t> t2((size_t)n_rows);
+    for (int64_t i = 0; i < n_rows; i++) t2[i] = tt[perm[i]];
+    tt.swap(t2);
+  }
+  struct Cut { int64_t r0, r1, start_ms; };
+  std::vector<Cut> cuts;
+  {
+    int64_t r0 = 0;
+    int64_t cur = segment_start(ds->segment_granularity, tt[0]);
+    int64_t cur_end = segment_end(ds->segment_granularity, cur);
+    for (int64_t i = 1; i < n_rows; i++) {
+      if (tt[i] >= cur_end) {
+        cuts.push_back({r0, i, cur});
+        r0 = i;
+        cur = segment_start(ds->segment_granularity, tt[i]);
+        cur_end = segment_end(ds->segment_granularity, cur);
+      }
+    }
+    cuts.push_back({r0, n_rows, cur});
+  }
+
+  // ---- dimensions: dictionaries, widths -------------------------------------------------------
+  struct DimLoad {
+    int di;
+    const LoadColumn* col;
+    std::vector<int32_t> owned_codes;   // STRING input converted to codes
+    std::vector<uint32_t> code_to_id;   // Dict
+  };
+  std::vector<DimLoad> dloads;
+  auto reencode_existing = [&](int di, const std::vector<uint32_t>* lut, int new_width) {
+    DimMeta& dm = ds->dims[di];
+    (void)dm;
+    if (!dev) {
+      for (auto& s : ds->segments)
+        if ((int)s->dim_width.size() > di) s->dim_width[di] = new_width;
+      return;
+    }
+    std::unique_ptr<DevBuf> dl;
+    if (lut) {
+      dl.reset(new DevBuf(lut->size() * 4));
+      SDO_CUDA(cudaMemcpy(dl->p, lut->data(), lut->size() * 4, cudaMemcpyHostToDevice));
+    }
+    for (auto& s : ds->segments) {
+      if ((int)s->dim_data.size() <= di || !s->dim_data[di]) continue;
+      int ow = s->dim_width[di];
+      void* nb = nullptr;
+      SDO_CUDA(cudaMalloc(&nb, padded_bytes(s->n_rows, new_width)));
+      SDO_CUDA(cudaMemset(nb, 0, padded_bytes(s->n_rows, new_width)));
+      launch_reencode(s->dim_data[di], ow, nb, new_width, s->n_rows, dl ? (const uint32_t*)dl->p : nullptr, 0);
+      SDO_CUDA(cudaDeviceSynchronize());
+      s->device_bytes += padded_bytes(s->n_rows, new_width);
+      s->device_bytes -= padded_bytes(s->n_rows, ow);
+      cudaFree(s->dim_data[di]);
+      s->dim_data[di] = nb;
+      s->dim_width[di] = new_width;
+    }
+  };
+
+  for (auto& c : cols) {
+    if (c.kind != 1) continue;
+    if (!c.data) throw Invalid("dimension '" + c.name + "' has no data");
+    int di = ds->dim_index(c.name);
+    bool is_int = (c.type == 0 || c.type == 4);
+    if (c.type != 0 && c.type != 2 && c.type != 3 && c.type != 4) throw Invalid("dimension '" + c.name + "': bad column type");
+    if (ds->metric_index(c.name) >= 0) throw Invalid("'" + c.name + "' is already a metric");
+    if (di < 0) {
+      DimMeta dm;
+      dm.name = c.name;
+      dm.enc = is_int ? DimEncoding::Direct : DimEncoding::Dict;
+      dm.src_type = c.src_type;
+      if (is_int && dm.src_type == 0) dm.src_type = (c.type == 4) ? 1 : 2;
+      ds->dims.push_back(std::move(dm));
+      di = (int)ds->dims.size() - 1;
+    }
+    DimMeta& dm = ds->dims[di];
+    if ((dm.enc == DimEncoding::Direct) != is_int) throw Invalid("dimension '" + c.name + "' changes between integer and string encoding");
+    DimLoad dl;
+    dl.di = di;
+    dl.col = &c;
+    if (is_int) {
+      int64_t mn = INT64_MAX, mx = INT64_MIN;
+      if (c.type == 0) {
+        const int64_t* v = (const int64_t*)c.data;
+        for (int64_t i = 0; i < n_rows; i++) { mn = std::min(mn, v[i]); mx = std::max(mx, v[i]); }
+      } else {
+        const int32_t* v = (const int32_t*)c.data;
+        for (int64_t i = 0; i < n_rows; i++) { mn = std::min<int64_t>(mn, v[i]); mx = std::max<int64_t>(mx, v[i]); }
+      }
+      if (mn < 0 || mx >= 4294967295ll) throw Unsupported("integer dimension '" + c.name + "' has values outside [0, 2^32-2]");
+      dm.cardinality = std::max(dm.cardinality, mx + 1);
+      int w = width_for(dm.cardinality);
+      if (w > dm.width) { reencode_existing(di, nullptr, w); dm.width = w; }
+    } else {
+      // batch dictionary
+      Dictionary bd;
+      if (c.type == 3) {
+        if (!c.dict_offsets || (!c.bytes && c.n_dict > 0 && c.dict_offsets[c.n_dict] > 0)) throw Invalid("dimension '" + c.name + "': CODES column needs dict_offsets and bytes");
+        for (int64_t k = 0; k < c.n_dict; k++) bd.push(c.bytes + c.dict_offsets[k], (size_t)(c.dict_offsets[k + 1] - c.dict_offsets[k]));
+        const int32_t* codes = (const int32_t*)c.data;
+        for (int64_t i = 0; i < n_rows; i++)
+          if (codes[i] < 0 || codes[i] >= c.n_dict) throw Invalid("dimension '" + c.name + "': code out of dictionary range");
+      } else {
+        const int64_t* off = (const int64_t*)c.data;
+        std::unordered_map<std::string, int32_t> seen;
+        dl.owned_codes.resize((size_t)n_rows);
+        for (int64_t i = 0; i < n_rows; i++) {
+          std::string s(c.bytes + off[i], (size_t)(off[i + 1] - off[i]));
+          auto it = seen.find(s);
+          if (it == seen.end()) {
+            it = seen.emplace(s, (int32_t)bd.size()).first;
+            bd.push(s.data(), s.size());
+          }
+          dl.owned_codes[i] = it->second;
+        }
+      }
+      // merged, sorted, de-duplicated dictionary
+      const Dictionary& od = *dm.dict;
+      int64_t nb = bd.size(), no = od.size();
+      std::vector<int64_t> border((size_t)nb);
+      std::iota(border.begin(), border.end(), 0);
+      std::sort(border.begin(), border.end(), [&](int64_t a, int64_t b) { return utf8_cmp(bd.data(a), bd.len(a), bd.data(b), bd.len(b)) < 0; });
+      Dictionary merged;
+      std::vector<uint32_t> old_to_new((size_t)no);
+      dl.code_to_id.assign((size_t)nb, 0);
+      int64_t i = 0, j = 0;
+      while (i < no || j < nb) {
+        int cmp;
+        if (i >= no) cmp = 1;
+        else if (j >= nb) cmp = -1;
+        else cmp = utf8_cmp(od.data(i), od.len(i), bd.data(border[j]), bd.len(border[j]));
+        uint32_t id = (uint32_t)merged.size();
+        if (cmp < 0) { merged.push(od.data(i), od.len(i)); old_to_new[i++] = id; }
+        else if (cmp > 0) {
+          const char* p = bd.data(border[j]);
+          size_t n = bd.len(border[j]);
+          merged.push(p, n);
+          dl.code_to_id[border[j++]] = id;
+          // duplicates inside the batch dictionary map to the same id
+          while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) dl.code_to_id[border[j++]] = id;
+        } else {
+          merged.push(od.data(i), od.len(i));
+          old_to_new[i++] = id;
+          const char* p = merged.data(id);
+          size_t n = merged.len(id);
+          while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) dl.code_to_id[border[j++]] = id;
+        }
+      }
+      bool changed = merged.size() != no;
+      int w = std::max(dm.width, width_for(merged.size()));
+      if (changed && no > 0) {
+        bool identity = true;
+        for (int64_t k = 0; k < no; k++)
+          if (old_to_new[k] != (uint32_t)k) { identity = false; break; }
+        if (!identity || w != dm.width) reencode_existing(di, identity ? nullptr : &old_to_new, w);
+        if (dm.hll_lut) { cudaFree(dm.hll_lut); dm.hll_lut = nullptr; dm.hll_lut_card = 0; }
+      }
+      dm.dict = std::make_shared<Dictionary>(std::move(merged));
+      dm.cardinality = dm.dict->size();
+      dm.width = w;
+    }
+    dloads.push_back(std::move(dl));
+  }
+
+  // ---- metrics ----------------------------------------------------------------------------------
+  struct MetLoad { int mi; const LoadColumn* col; };
+  std::vector<MetLoad> mloads;
+  for (auto& c : cols) {
+    if (c.kind != 2) continue;
+    if (!c.data) throw Invalid("metric '" + c.name + "' has no data");
+    if (c.type != 0 && c.type != 1) throw Invalid("metric '" + c.name + "' must be SDO_T_INT64 or SDO_T_FLOAT64");
+    if (ds->dim_index(c.name) >= 0) throw Invalid("'" + c.name + "' is already a dimension");
+    int mi = ds->metric_index(c.name);
+    if (mi < 0) {
+      MetricMeta mm;
+      mm.name = c.name;
+      mm.is_float = c.type == 1;
+      ds->metrics.push_back(mm);
+      mi = (int)ds->metrics.size() - 1;
+    }
+    MetricMeta& mm = ds->metrics[mi];
+    if (mm.is_float != (c.type == 1)) throw Invalid("metric '" + c.name + "' changes type between loads");
+    if (!mm.is_float) {
+      const int64_t* v = (const int64_t*)c.data;
+      int64_t first = mm.seen ? mm.const_value : v[0];
+      bool cst = mm.constant;
+      for (int64_t i = 0; cst && i < n_rows; i++) cst = v[i] == first;
+      mm.constant = cst;
+      mm.const_value = first;
+    } else {
+      mm.constant = false;
+    }
+    mm.seen = true;
+    mloads.push_back({mi, &c});
+  }
+
+  // ---- build segments ---------------------------------------------------------------------------
+  std::vector<std::unique_ptr<Segment>> segs;
+  for (auto& ct : cuts) {
+    std::unique_ptr<Segment> s(new Segment());
+    s->start_ms = ct.start_ms;
+    s->end_ms = segment_end(ds->segment_granularity, ct.start_ms);
+    s->partition = partition;
+    s->n_rows = ct.r1 - ct.r0;
+    s->dim_data.assign(ds->dims.size(), nullptr);
+    s->dim_width.assign(ds->dims.size(), 0);
+    s->metric_data.assign(ds->metrics.size(), nullptr);
+    for (int64_t r = ct.r0; r < ct.r1; r++) {
+      if (r == ct.r0 || tt[r] != tt[r - 1]) {
+        s->time_vals.push_back(tt[r]);
+        s->time_rows.push_back(r - ct.r0);
+      }
+    }
+    s->time_rows.push_back(s->n_rows);
+    segs.push_back(std::move(s));
+  }
+
+  if (dev) {
+    std::unique_ptr<DevBuf> dperm;
+    if (!sorted) {
+      dperm.reset(new DevBuf((size_t)n_rows * 4));
+      SDO_CUDA(cudaMemcpy(dperm->p, perm.data(), (size_t)n_rows * 4, cudaMemcpyHostToDevice));
+    }
+    for (auto& dl : dloads) {
+      DimMeta& dm = ds->dims[dl.di];
+      bool src64 = dl.col->type == 0;
+      const void* src = dl.owned_codes.empty() ? dl.col->data : (const void*)dl.owned_codes.data();
+      size_t esz = src64 ? 8 : 4;
+      DevBuf raw((size_t)n_rows * esz);
+      SDO_CUDA(cudaMemcpy(raw.p, src, (size_t)n_rows * esz, cudaMemcpyHostToDevice));
+      std::unique_ptr<DevBuf> dlut;
+      if (dm.enc == DimEncoding::Dict) {
+        dlut.reset(new DevBuf(dl.code_to_id.size() * 4));
+        SDO_CUDA(cudaMemcpy(dlut->p, dl.code_to_id.data(), dl.code_to_id.size() * 4, cudaMemcpyHostToDevice));
+      }
+      for (size_t k = 0; k < cuts.size(); k++) {
+        Segment& s = *segs[k];
+        size_t nb = padded_bytes(s.n_rows, dm.width);
+        SDO_CUDA(cudaMalloc(&s.dim_data[dl.di], nb));
+        SDO_CUDA(cudaMemset(s.dim_data[dl.di], 0, nb));
+        s.dim_width[dl.di] = dm.width;
+        s.device_bytes += nb;
+        launch_encode_dim(raw.p, src64, dperm ? (const int32_t*)dperm->p : nullptr, cuts[k].r0, s.n_rows,
+                          dlut ? (const uint32_t*)dlut->p : nullptr, s.dim_data[dl.di], dm.width, 0);
+      }
+      SDO_CUDA(cudaDeviceSynchronize());
+    }
+    for (auto& ml : mloads) {
+      DevBuf raw((size_t)n_rows * 8);
+      SDO_CUDA(cudaMemcpy(raw.p, ml.col->data, (size_t)n_rows * 8, cudaMemcpyHostToDevice));
+      for (size_t k = 0; k < cuts.size(); k++) {
+        Segment& s = *segs[k];
+        size_t nb = padded_bytes(s.n_rows, 8);
+        SDO_CUDA(cudaMalloc(&s.metric_data[ml.mi], nb));
+        SDO_CUDA(cudaMemset(s.metric_data[ml.mi], 0, nb));
+        s.device_bytes += nb;
+        launch_gather64(raw.p, dperm ? (const int32_t*)dperm->p : nullptr, cuts[k].r0, s.n_rows, s.metric_data[ml.mi], 0);
+      }
+      SDO_CUDA(cudaDeviceSynchronize());
+    }
+  } else {
+    for (auto& dl : dloads)
+      for (auto& s : segs) s->dim_width[dl.di] = ds->dims[dl.di].width;
+  }
+
+  for (auto& s : segs) {
+    ds->n_rows += s->n_rows;
+    auto pos = std::upper_bound(ds->segments.begin(), ds->segments.end(), s, [](const std::unique_ptr<Segment>& a, const std::unique_ptr<Segment>& b) {
+      return a->start_ms != b->start_ms ? a->start_ms < b->start_ms : a->partition < b->partition;
+    });
+    ds->segments.insert(pos, std::move(s));
+  }
+  // older segments may lack columns that arrived later
+  for (auto& s : ds->segments) {
+    s->dim_data.resize(ds->dims.size(), nullptr);
+    s->dim_width.resize(ds->dims.size(), 0);
+    s->metric_data.resize(ds->metrics.size(), nullptr);
+  }
+}
+
+// ---- metadata -----------------------------------------------------------------------------------
+
+std::string Store::metadata_json(const std::string& name) const {
+  auto ds = get(name);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  // MetadataResponse shape: client/DruidMessages.scala:25-53 -> {id, intervals, columns{name->{type,size,cardinality}}, size, numRows}
+  std::string o = "{";
+  o += "\"id\":";
+  json_escape(o, "merged");
+  o += ",\"intervals\":[";
+  int64_t lo = INT64_MAX, hi = INT64_MIN;
+  size_t bytes = 0;
+  for (auto& s : ds->segments) {
+    if (s->time_vals.empty()) continue;
+    lo = std::min(lo, s->time_vals.front());
+    hi = std::max(hi, s->time_vals.back());
+    bytes += s->device_bytes;
+  }
+  if (lo <= hi) {
+    o += "\"" + format_iso_instant(lo) + "/" + format_iso_instant(hi + 1) + "\"";
+  }
+  o += "],\"columns\":{";
+  o += "\"__time\":{\"type\":\"LONG\",\"size\":0,\"cardinality\":null}";
+  for (auto& d : ds->dims) {
+    o += ",";
+    json_escape(o, d.name);
+    o += ":{\"type\":\"STRING\",\"size\":" + std::to_string((long long)ds->n_rows * d.width) + ",\"cardinality\":" + std::to_string((long long)d.cardinality) + "}";
+  }
+  for (auto& m : ds->metrics) {
+    o += ",";
+    json_escape(o, m.name);
+    o += std::string(":{\"type\":\"") + (m.is_float ? "FLOAT" : "LONG") + "\",\"size\":" + std::to_string((long long)ds->n_rows * 8) + ",\"cardinality\":null}";
+  }
+  o += "},\"size\":" + std::to_string((unsigned long long)bytes) + ",\"numRows\":" + std::to_string((long long)ds->n_rows);
+  o += ",\"queryGranularity\":";
+  json_escape(o, ds->query_granularity);
+  o += ",\"segmentGranularity\":";
+  json_escape(o, ds->segment_granularity);
+  if (lo <= hi) o += ",\"timeBoundary\":{\"minTime\":\"" + format_iso_instant(lo) + "\",\"maxTime\":\"" + format_iso_instant(hi) + "\"}";
+  o += "}";
+  return o;
+}
+
+std::string Store::segments_json(const std::string& name) const {
+  auto ds = get(name);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  // DruidSegmentInfo shape: metadata/DruidMetadataCache.scala:64-76 {identifier, interval, version, size, shardSpec}
+  std::string o = "[";
+  bool first = true;
+  for (auto& s : ds->segments) {
+    if (!first) o += ",";
+    first = false;
+    std::string itv = format_iso_instant(s->start_ms) + "/" + format_iso_instant(s->end_ms);
+    o += "{\"identifier\":";
+    json_escape(o, ds->name + "_" + itv + "_v1_" + std::to_string(s->partition));
+    o += ",\"interval\":\"" + itv + "\",\"version\":\"v1\",\"size\":" + std::to_string((unsigned long long)s->device_bytes);
+    o += ",\"numRows\":" + std::to_string((long long)s->n_rows);
+    o += ",\"shardSpec\":{\"type\":\"linear\",\"partitionNum\":" + std::to_string(s->partition) + "}";
+    o += ",\"server\":\"gpu:" + std::to_string(device_) + "\"}";
+  }
+  o += "]";
+  return o;
+}
+
+}  // namespace sdo

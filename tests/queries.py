@@ -1,0 +1,193 @@
+"""Query corpus: the shapes the reference plans / benchmarks, built with the spec mirror.
+Sources: tools/TpchBenchMark.scala:135-292 (benchmark SQL and the specs it plans to),
+docs/benchmark/druid/queries/*.json (serialised specs), client/test/TPCHQueries.scala:30-140 (raw
+specs with granularity / limit / post-aggregations), FilterCTest.scala:28-50 (in / not / null)."""
+from spark_druid_olap_b200.specs import *  # noqa: F401,F403
+
+DS = "tpch"
+ALL_TIME = ["1992-01-01T00:00:00.000Z/1999-01-01T00:00:00.000Z"]
+
+
+def agg(t, name, field):
+    return FunctionAggregationSpec(t, name, field)
+
+
+def ctx(strategy=None, qid="q"):
+    return QuerySpecContext(qid, gpuStrategy=strategy) if strategy else None
+
+
+def q1_style(strategy=None):
+    """BASELINE config 1: group by l_returnflag, l_linestatus, l_shipdate <= 1998-09-02, sum/avg/count."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("l_returnflag"), DefaultDimensionSpec("l_linestatus")], None, None, "all", None,
+        [agg("count", "count_order", "count"), agg("doubleSum", "sum_qty", "l_quantity"),
+         agg("doubleSum", "sum_base_price", "l_extendedprice"), agg("doubleSum", "sum_disc", "l_discount")],
+        [ArithmeticPostAggregationSpec("avg_qty", "/", [FieldAccessPostAggregationSpec("sum_qty"), FieldAccessPostAggregationSpec("count_order")]),
+         ArithmeticPostAggregationSpec("avg_price", "/", [FieldAccessPostAggregationSpec("sum_base_price"), FieldAccessPostAggregationSpec("count_order")]),
+         ArithmeticPostAggregationSpec("avg_disc", "/", [FieldAccessPostAggregationSpec("sum_disc"), FieldAccessPostAggregationSpec("count_order")])],
+        ["1992-01-01T00:00:00.000Z/1998-09-02T00:00:00.001Z"], ctx(strategy))
+
+
+def basic_agg(strategy=None):
+    """docs/benchmark/druid/queries/q1.json / basicAgg.json shape (count, doubleSum, doubleMax, longSum, HLL, post-agg)."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("l_returnflag"), DefaultDimensionSpec("l_linestatus")], None, None, "all", None,
+        [agg("count", "alias-1", "count"), agg("doubleSum", "alias-2", "l_extendedprice"), agg("doubleMax", "alias-3", "ps_supplycost"),
+         agg("longSum", "alias-5", "ps_availqty"), agg("longSum", "alias-6", "count"),
+         CardinalityAggregationSpec("alias-7", ["o_orderkey"])],
+        [ArithmeticPostAggregationSpec("alias-4", "/", [FieldAccessPostAggregationSpec("alias-5"), FieldAccessPostAggregationSpec("alias-6")])],
+        ALL_TIME, ctx(strategy))
+
+
+def ship_date_range(strategy=None):
+    """shipDteRange.json: interval (1995-12-01, 1997-09-02], count by flag/status."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("l_returnflag", "f"), DefaultDimensionSpec("l_linestatus", "s")], None, None, "all", None,
+        [agg("count", "count_order", "count")], None, ["1995-12-01T00:00:00.001Z/1997-09-02T00:00:00.001Z"], ctx(strategy))
+
+
+def _nations():
+    return Or(And(SelectorFilterSpec("s_nation", "FRANCE"), SelectorFilterSpec("c_nation", "GERMANY")),
+              And(SelectorFilterSpec("c_nation", "FRANCE"), SelectorFilterSpec("s_nation", "GERMANY")))
+
+
+def proj_filt_range(strategy=None):
+    """projFiltRange.json: p_type selector AND nation pairs, ship-date interval, group by s_nation."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("s_nation")], None, None, "all",
+        And(SelectorFilterSpec("p_type", "ECONOMY ANODIZED STEEL"), _nations()),
+        [agg("count", "alias-1", "count"), agg("doubleSum", "alias-2", "l_extendedprice"), agg("doubleMax", "alias-3", "ps_supplycost"),
+         agg("longSum", "alias-5", "ps_availqty")], None,
+        ["1995-12-01T00:00:00.001Z/1997-09-02T00:00:00.001Z"], ctx(strategy))
+
+
+def q3(limit=None, strategy=None):
+    """TPCH Q3 shape (q3.json with the javascript date test as the `bound` the newer planner emits,
+    FilterPlanningTest.scala:67-81); limit=10 gives BASELINE config 2's Q3L."""
+    ls = LimitSpec(limit, [OrderByColumnSpec("revenue", "descending")]) if limit else None
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("o_orderkey"), DefaultDimensionSpec("o_orderdate"), DefaultDimensionSpec("o_shippriority")], ls, None, "all",
+        And(SelectorFilterSpec("c_mktsegment", "BUILDING"), BoundFilterSpec("o_orderdate", upper="1995-03-15", upperStrict=True)),
+        [agg("doubleSum", "revenue", "l_extendedprice")], None,
+        ["1995-03-15T00:00:00.001Z/1999-01-01T00:00:00.000Z"], ctx(strategy))
+
+
+def _q5_filter():
+    return And(SelectorFilterSpec("s_region", "ASIA"),
+               BoundFilterSpec("o_orderdate", lower="1994-01-01", lowerStrict=False, upper="1995-01-01", upperStrict=True))
+
+
+def q5(strategy=None):
+    return GroupByQuerySpec(DS, [DefaultDimensionSpec("s_nation")], None, None, "all", _q5_filter(),
+                            [agg("doubleSum", "revenue", "l_extendedprice")], None, ALL_TIME, ctx(strategy))
+
+
+def q5_topn(threshold=10, strategy=None):
+    """BASELINE config 2's Q5T: TopN s_nation by revenue."""
+    return TopNQuerySpec(DS, ALL_TIME, "all", _q5_filter(), [agg("doubleSum", "revenue", "l_extendedprice")], None,
+                         DefaultDimensionSpec("s_nation"), threshold, NumericTopNMetricSpec("revenue"), ctx(strategy))
+
+
+def q7(strategy=None):
+    """q7.json: nation pairs, dims s_nation, c_nation, year of ship date (timeFormat on __time)."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("s_nation"), DefaultDimensionSpec("c_nation"),
+             ExtractionDimensionSpec("__time", "l_year", TimeFormatExtractionFunctionSpec("yyyy"))], None, None, "all", _nations(),
+        [agg("doubleSum", "alias-1", "l_extendedprice")], None, ALL_TIME, ctx(strategy))
+
+
+def q8(strategy=None):
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("order_year", "o_year")], None, None, "all",
+        And(SelectorFilterSpec("c_region", "AMERICA"), SelectorFilterSpec("p_type", "ECONOMY ANODIZED STEEL"),
+            BoundFilterSpec("o_orderdate", lower="1995-01-01", lowerStrict=False, upper="1996-12-31", upperStrict=False)),
+        [agg("doubleSum", "price", "l_extendedprice")], None, ALL_TIME, ctx(strategy))
+
+
+def timeseries(period="P1D", with_sum=True, strategy=None, intervals=None):
+    """BASELINE config 3: Timeseries at day / month granularity with HLL count-distinct of o_custkey."""
+    aggs = [agg("count", "rows", "count"), CardinalityAggregationSpec("custs", ["o_custkey"])]
+    if with_sum:
+        aggs.append(agg("doubleSum", "price", "l_extendedprice"))
+    return TimeSeriesQuerySpec(DS, intervals or ALL_TIME, PeriodGranularitySpec(period), None, aggs, None, ctx(strategy))
+
+
+def by_orderkey(strategy=None):
+    """BASELINE config 4: group by o_orderkey (~1.5M x SF groups)."""
+    return GroupByQuerySpec(DS, [DefaultDimensionSpec("o_orderkey")], None, None, "all", None,
+                            [agg("count", "n", "count"), agg("doubleSum", "price", "l_extendedprice")], None, ALL_TIME, ctx(strategy))
+
+
+def q1_month_grain(strategy=None):
+    """TPCHQueries.q1MonthGrain shape: P1M granularity + dims + timeFormat dim + limit ordered by dims."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("l_returnflag"), DefaultDimensionSpec("l_linestatus"),
+             ExtractionDimensionSpec("__time", "month", TimeFormatExtractionFunctionSpec("yyyy-MMM", "UTC"))],
+        LimitSpec(10, [OrderByColumnSpec("l_returnflag"), OrderByColumnSpec("l_linestatus"), OrderByColumnSpec("month")]), None,
+        PeriodGranularitySpec("P1M"), None,
+        [agg("longSum", "count", "count"), agg("doubleSum", "sum_quantity", "l_quantity"), agg("doubleSum", "sum_base_price", "l_extendedprice"),
+         agg("doubleSum", "l_discount", "l_discount"), agg("doubleSum", "l_tax", "l_tax"), CardinalityAggregationSpec("count_order", ["o_orderkey"])],
+        [ArithmeticPostAggregationSpec("sum_disc_price", "-", [FieldAccessPostAggregationSpec("sum_base_price"), FieldAccessPostAggregationSpec("l_discount")]),
+         ArithmeticPostAggregationSpec("avg_qty", "/", [FieldAccessPostAggregationSpec("sum_quantity"), FieldAccessPostAggregationSpec("count")])],
+        ["1993-01-01T00:00:00.000/1993-03-01T00:00:00.000"], ctx(strategy))
+
+
+def filter_cases():
+    """(name, FilterSpec) pairs covering selector / bound / in / regex / contains / not / null."""
+    return [
+        ("in2", ExtractionFilterSpec("c_mktsegment", ["MACHINERY", "HOUSEHOLD"])),                       # FilterPlanningTest "in"
+        ("in_many", ExtractionFilterSpec("p_type", ["ECONOMY ANODIZED STEEL", "PROMO PLATED TIN", "SMALL BRUSHED COPPER", "nope"])),
+        ("not_in", NotFilterSpec("not", ExtractionFilterSpec("l_shipmode", ["AIR", "RAIL"]))),
+        ("is_null", SelectorFilterSpec("l_shipmode", "")),
+        ("is_not_null", NotFilterSpec("not", SelectorFilterSpec("l_shipmode", ""))),
+        ("ts_null_guard", And(NotFilterSpec("not", SelectorFilterSpec("__time", "")), SelectorFilterSpec("l_returnflag", "R"))),
+        ("bound_ge", And(NotFilterSpec("not", SelectorFilterSpec("o_orderdate", "")),                    # FilterPlanningTest "timestamp4"
+                         BoundFilterSpec("o_orderdate", "1995-12-30", False, None, None, False))),
+        ("bound_between_strict", BoundFilterSpec("s_nation", "CANADA", True, "JAPAN", True, False)),
+        ("bound_int_lex", BoundFilterSpec("p_size", "2", False, "35", True, False)),                    # lexicographic on an integer dimension
+        ("bound_int_num", BoundFilterSpec("p_size", "2", False, "35", True, True)),                     # alphaNumeric
+        ("selector_int", SelectorFilterSpec("l_linenumber", "3")),
+        ("selector_int_noncanonical", SelectorFilterSpec("l_linenumber", "03")),
+        ("selector_absent_value", SelectorFilterSpec("s_nation", "ATLANTIS")),
+        ("regex", RegexFilterSpec("p_type", "^(ECONOMY|PROMO) .* (TIN|STEEL)$")),
+        ("contains", StringContainsSpec("p_type", "BRUSHED")),
+        ("or_mix", Or(SelectorFilterSpec("l_returnflag", "A"), And(SelectorFilterSpec("l_linestatus", "O"), StringContainsSpec("l_shipmode", "AI")))),
+        ("unknown_dim_null", SelectorFilterSpec("no_such_dim", "")),
+        ("unknown_dim_value", SelectorFilterSpec("no_such_dim", "x")),
+    ]
+
+
+def with_filter(f, strategy=None):
+    return GroupByQuerySpec(DS, [DefaultDimensionSpec("l_shipmode"), DefaultDimensionSpec("l_returnflag")], None, None, "all", f,
+                            [agg("count", "n", "count"), agg("longSum", "qty", "ps_availqty"), agg("doubleSum", "price", "l_extendedprice")],
+                            None, ALL_TIME, ctx(strategy))
+
+
+def agg_zoo(strategy=None):
+    """Every aggregator type incl. min/max, cross-type sums and a filtered aggregation."""
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("c_region")], None, None, "all", None,
+        [agg("count", "n", "count"), agg("longSum", "lsum", "ps_availqty"), agg("longMin", "lmin", "ps_availqty"), agg("longMax", "lmax", "ps_availqty"),
+         agg("doubleMin", "dmin", "l_discount"), agg("doubleMax", "dmax", "ps_supplycost"), agg("doubleSum", "dsum_of_long", "ps_availqty"),
+         agg("longSum", "lsum_of_double", "l_quantity"), agg("doubleMin", "dmin_of_long", "ps_availqty"), agg("longMax", "lmax_of_double", "l_extendedprice"),
+         FilteredAggregationSpec("n_air", SelectorFilterSpec("l_shipmode", "AIR"), agg("count", "n_air", "count")),
+         FilteredAggregationSpec("price_r", SelectorFilterSpec("l_returnflag", "R"), agg("doubleSum", "price_r", "l_extendedprice")),
+         CardinalityAggregationSpec("d_nation", ["s_nation"]), CardinalityAggregationSpec("d_cust", ["o_custkey"])],
+        None, ALL_TIME, ctx(strategy))
+
+
+def having_query(strategy=None):
+    return GroupByQuerySpec(
+        DS, [DefaultDimensionSpec("s_nation")], LimitSpec(2147483647, [OrderByColumnSpec("n", "descending"), OrderByColumnSpec("s_nation")]),
+        LogicalBinaryOpHavingSpec("and", [ComparisonHavingSpec("greaterThan", "n", 10.0), NotOpHavingSpec("not", ComparisonHavingSpec("lessThan", "price", 1000.0))]),
+        "all", None, [agg("count", "n", "count"), agg("doubleSum", "price", "l_extendedprice")], None, ALL_TIME, ctx(strategy))
+
+
+def topn_variants():
+    a = [agg("doubleSum", "revenue", "l_extendedprice"), agg("count", "n", "count")]
+    return [
+        ("numeric_desc", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 3, NumericTopNMetricSpec("revenue"))),
+        ("numeric_inverted", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 3, InvertedTopNMetricSpec("inverted", NumericTopNMetricSpec("revenue")))),
+        ("lexicographic", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 4, LexiographicTopNMetricSpec("Brand#23"))),
+        ("int_count", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("c_nation"), 200, NumericTopNMetricSpec("n"))),
+    ]
