@@ -234,6 +234,7 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
       c.n_keys = 1;
       c.n_slots = 1;
       c.n_hll = 0;
+      c.ignore_key_base = 1;
       size_t smem = scan_smem_bytes(STRAT_LANE, 1, 1);
       int grid = scan_grid_size(STRAT_LANE, smem, sm_count_);
       unsigned long long* part = nullptr;

@@ -210,7 +210,7 @@ __device__ __forceinline__ void process_unit(const ScanParams& p, const DevSpan&
 
   key_t key[4];
 #pragma unroll
-  for (int i = 0; i < 4; i++) key[i] = (key_t)sp.key_base;
+  for (int i = 0; i < 4; i++) key[i] = p.ignore_key_base ? (key_t)0 : (key_t)sp.key_base;
   for (int d = 0; d < p.n_dims; d++) {
     uint32_t ids[4];
     load_ids4(cols[p.dims[d].col], p.dims[d].width, r0, ids);
@@ -428,7 +428,8 @@ size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots) {
 
 template <int STRAT>
 static int occupancy(size_t smem) {
-  if (smem > 48 * 1024) SDO_CUDA(cudaFuncSetAttribute(scan_kernel<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // static shared memory counts against the 48 KB default too, so opt in well before the edge
+  if (smem > 32 * 1024) SDO_CUDA(cudaFuncSetAttribute(scan_kernel<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int nb = 0;
   SDO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, scan_kernel<STRAT>, SCAN_THREADS, smem));
   return nb;

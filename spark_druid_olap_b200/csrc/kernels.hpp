@@ -99,6 +99,8 @@ struct ScanParams {
   DevAgg aggs[MAX_AGGS];
   int32_t n_slots;  // per group, slot 0 = row count
   int32_t n_hll;
+  int32_t ignore_key_base;  // count-only pass: all rows fall into key 0
+  int32_t pad0;
   uint64_t n_keys;  // dense key-space size (LANE / BLOCK / GLOBAL)
   int32_t slot_op[MAX_SLOTS];
   uint64_t slot_init[MAX_SLOTS];

@@ -187,7 +187,7 @@ def topn_variants():
     a = [agg("doubleSum", "revenue", "l_extendedprice"), agg("count", "n", "count")]
     return [
         ("numeric_desc", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 3, NumericTopNMetricSpec("revenue"))),
-        ("numeric_inverted", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 3, InvertedTopNMetricSpec("inverted", NumericTopNMetricSpec("revenue")))),
+        ("numeric_inverted", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 3, InvertedTopNMetricSpec(NumericTopNMetricSpec("revenue")))),
         ("lexicographic", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("p_brand"), 4, LexiographicTopNMetricSpec("Brand#23"))),
         ("int_count", TopNQuerySpec(DS, ALL_TIME, "all", None, a, None, DefaultDimensionSpec("c_nation"), 200, NumericTopNMetricSpec("n"))),
     ]
