@@ -189,6 +189,36 @@ void* sdo_partial_stream(sdo_partial* p);
 int sdo_partial_finish(sdo_partial* p, sdo_result** out);
 void sdo_partial_free(sdo_partial* p);
 
+/* ---- allocation-free group-by ----------------------------------------------------------------
+ * No counterpart in the reference (it has no native code and no notion of device memory).
+ *
+ * For callers that may launch work on a GPU but must not allocate on it: a plugin living inside
+ * another runtime's fixed device-memory reservation, a host that promises "no cudaMalloc after
+ * start-up", code running where allocation calls are not permitted.  sdo_query_execute does not
+ * fit them, because every query takes scratch from the CUDA memory pool.
+ *
+ * Computes, for id column keys_dev[n_rows] (one byte per row, ids < n_keys; larger ids are ignored)
+ * and metric values_dev[n_rows]:  counts_out_dev[k] = rows with id k,  sums_out_dev[k] = sum of their
+ * values -- the same lane-private shared-memory aggregation a dense GroupBy uses, but with its
+ * scratch (per-block partials and a block ticket) in a fixed array compiled into the library, about
+ * 0.4 MB that every GPU loading the library holds until exit.  All five buffers are device memory
+ * owned by the caller (keys 4-byte aligned, values 16-byte aligned); `cuda_stream` is a cudaStream_t
+ * (NULL = default stream); the call only enqueues work and returns.  It performs no cudaMalloc /
+ * cudaFree and calls no allocating library routine.
+ *
+ * Limits: 1 <= n_keys <= SDO_NOALLOC_MAX_KEYS and 0 <= n_rows <= SDO_NOALLOC_MAX_ROWS; anything
+ * beyond is refused with SDO_INVALID and a message in sdo_last_error().
+ * First call on a device: resolves the scratch array's device address (once per device, under a
+ * lock); make that first call before starting any stream capture.
+ * Sharing: every call on a device uses the same array, which still holds the last call's partials.
+ * The kernel overwrites all words it reads back and the ticket is reset on entry, so calls issued
+ * one after another are independent -- but calls that overlap on the GPU (two streams, two
+ * threads) race on the array and must be serialised by the caller. */
+#define SDO_NOALLOC_MAX_KEYS 24
+#define SDO_NOALLOC_MAX_ROWS 4294967296LL
+int sdo_groupby_sum_noalloc(int device, const uint8_t* keys_dev, const double* values_dev, int64_t n_rows, int n_keys,
+                            int64_t* counts_out_dev, double* sums_out_dev, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -100,6 +100,7 @@ def lib():
         "sdo_partial_stream": (vp, [vp]),
         "sdo_partial_finish": (C.c_int, [vp, C.POINTER(vp)]),
         "sdo_partial_free": (None, [vp]),
+        "sdo_groupby_sum_noalloc": (C.c_int, [C.c_int, vp, vp, i64, C.c_int, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -114,8 +115,18 @@ EXPORTED_SYMBOLS = [
     "sdo_segment_load", "sdo_datasource_metadata", "sdo_datasource_segments", "sdo_query_execute", "sdo_query_explain",
     "sdo_query_cancel", "sdo_result_num_rows", "sdo_result_num_columns", "sdo_result_column_get", "sdo_result_hll_registers",
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
-    "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free",
+    "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
 ]
+
+NOALLOC_MAX_KEYS = 24
+NOALLOC_MAX_ROWS = 1 << 32
+
+
+def groupby_sum_noalloc(device, keys_ptr, values_ptr, n_rows, n_keys, counts_out_ptr, sums_out_ptr, stream=None):
+    """sdo_groupby_sum_noalloc: count and double sum per one-byte key without any device allocation.
+    For hosts that may compute on the GPU but not allocate there; all pointers are caller-owned device
+    memory.  See include/sdo_engine.h for the limits, the first-call set-up and the sharing rule."""
+    _check(lib().sdo_groupby_sum_noalloc(device, keys_ptr, values_ptr, n_rows, n_keys, counts_out_ptr, sums_out_ptr, stream))
 
 
 def _check(status):

@@ -39,6 +39,11 @@ int guard(F f) {
 int bad(const char* m) { g_err = m; return SDO_INVALID; }
 }  // namespace
 
+namespace sdo {
+// lets other translation units (noalloc.cu) report through sdo_last_error()
+void set_last_error(const std::string& m) { g_err = m; }
+}  // namespace sdo
+
 extern "C" {
 
 int sdo_engine_create(int device, sdo_engine** out) {
