@@ -118,6 +118,7 @@ def main():
     ap.add_argument("--ref-sf", type=float, default=2.0, help="scale factor of the bounded CPU sample")
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--extra", action="store_true", help="also time the other config shapes (Q1, Q3L, timeseries, by-orderkey)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -229,7 +230,7 @@ def main():
         "clocks": clocks,
         "result_rows": last.n_rows if last is not None else None,
     }
-    if world == 1:
+    if world == 1 and not args.no_cpu:
         try:
             line["cpu_baseline"] = cpu_baseline_q5t(min(args.sf, args.ref_sf))
         except Exception as ex:  # the baseline is reporting only; never a fallback

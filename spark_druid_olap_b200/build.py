@@ -16,7 +16,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
 ENGINE_SRCS = ["kernels.cu", "noalloc.cu", "spec.cpp", "store.cpp", "plan.cpp", "engine.cpp", "capi.cpp"]
-ENGINE_HDRS = ["common.hpp", "json.hpp", "timeutil.hpp", "spec.hpp", "store.hpp", "plan.hpp", "kernels.hpp",
+ENGINE_HDRS = ["scan_unit.cuh", "common.hpp", "json.hpp", "timeutil.hpp", "spec.hpp", "store.hpp", "plan.hpp", "kernels.hpp",
                "engine.hpp", "xxh64.hpp", os.path.join("..", "..", "include", "sdo_engine.h")]
 ENGINE_LIB = os.path.join(HERE, "libsdo_engine.so")
 GEN_LIB = os.path.join(HERE, "libsdo_tpchgen.so")

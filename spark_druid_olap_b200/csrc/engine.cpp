@@ -196,7 +196,7 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
   p.spans = (const DevSpan*)(d + off_spans);
   p.n_spans = (uint32_t)n_spans;
   p.n_units = plan.n_units;
-  p.units_per_chunk = 8;
+  p.units_per_chunk = 2;
   p.n_cols = (uint32_t)n_cols;
   p.segptr = (const void* const*)(d + off_segptr);
   p.n_leaves = (int)plan.leaves.size();
@@ -220,6 +220,7 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
   p.counters = ctx->counters;
   SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, 64, s));
 
+  if (plan.rows_scanned >= (1ll << 32)) throw Unsupported("a single launch scans at most 2^32 rows per GPU");
   int strat = plan.strategy;
   st->strategy = strat;
   const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;

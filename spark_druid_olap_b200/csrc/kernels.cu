@@ -143,7 +143,10 @@ struct Acc<STRAT_LANE> {
   typedef uint32_t key_t;
   unsigned long long* base;  // smem + tid
   int ns;
+  static constexpr int SLOT_STRIDE = SCAN_THREADS;  // elements between consecutive slots of one group
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)(g * ns + slot) * SCAN_THREADS; }
+  // a thread's own count stays far below 2^32: bump the low word only
+  __device__ __forceinline__ void count1(unsigned long long* q) const { *(unsigned int*)q += 1u; }
   __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { *q += (unsigned long long)v; }
   __device__ __forceinline__ void add_f64(unsigned long long* q, double v) const { *(double*)q += v; }
   __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v < c) *(long long*)q = v; }
@@ -161,21 +164,29 @@ struct Acc<STRAT_BLOCK> : AtomicOps {
   typedef uint32_t key_t;
   unsigned long long* base;  // smem table
   int ns;
+  static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)g * ns + slot; }
+  // one launch scans fewer than 2^32 rows (checked on the host), so a block's count fits the low
+  // word: a native 32-bit shared atomic instead of the 64-bit compare-and-swap loop
+  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd((unsigned int*)q, 1u); }
 };
 template <>
 struct Acc<STRAT_GLOBAL> : AtomicOps {
   typedef uint64_t key_t;
   unsigned long long* base;
   int ns;
+  static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
+  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
 };
 template <>
 struct Acc<STRAT_HASH> : AtomicOps {
   typedef uint64_t key_t;
   unsigned long long* base;
   int ns;
+  static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
+  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
 };
 
 // find-or-claim the slot of `key` (linear probing).  Returns HASH_EMPTY if the table is full.
@@ -193,144 +204,15 @@ __device__ __forceinline__ uint64_t hash_claim(unsigned long long* hkeys, uint64
   return HASH_EMPTY;
 }
 
-// ---------------------------------------------------------------------------------------------
-// one unit = up to 1024 rows of one span
-// ---------------------------------------------------------------------------------------------
-template <int STRAT>
-__device__ __forceinline__ void process_unit(const ScanParams& p, const DevSpan& sp, uint32_t unit_in_span, const Acc<STRAT>& acc) {
-  typedef typename Acc<STRAT>::key_t key_t;
-  const uint32_t r0 = (sp.row_begin & ~3u) + unit_in_span * UNIT_ROWS + threadIdx.x * ROWS_PER_THREAD;
-  if (r0 >= sp.row_end) return;
-  uint32_t m = 0xF;
-  if (r0 < sp.row_begin) m &= 0xFu << (sp.row_begin - r0);
-  if (r0 + 4 > sp.row_end) m &= 0xFu >> (r0 + 4 - sp.row_end);
-  const void* const* cols = p.segptr + (size_t)sp.seg * p.n_cols;
-  if (p.n_ops) m &= eval_filter(p, cols, r0);
-  if (!m) return;
-
-  key_t key[4];
-#pragma unroll
-  for (int i = 0; i < 4; i++) key[i] = p.ignore_key_base ? (key_t)0 : (key_t)sp.key_base;
-  for (int d = 0; d < p.n_dims; d++) {
-    uint32_t ids[4];
-    load_ids4(cols[p.dims[d].col], p.dims[d].width, r0, ids);
-    const key_t stride = (key_t)p.dims[d].stride;
-#pragma unroll
-    for (int i = 0; i < 4; i++) key[i] += (key_t)ids[i] * stride;
-  }
-  if (STRAT == STRAT_HASH) {
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      if ((m >> i) & 1u) {
-        uint64_t h = hash_claim(p.hkeys, p.hmask, (uint64_t)key[i]);
-        if (h == HASH_EMPTY) { p.counters[1] = 1; m &= ~(1u << i); }
-        key[i] = (key_t)h;
-      }
-    }
-  }
-  // slot 0: row count of the group
-#pragma unroll
-  for (int i = 0; i < 4; i++)
-    if ((m >> i) & 1u) acc.add_i64(acc.at(key[i], 0), 1);
-
-  for (int a = 0; a < p.n_aggs; a++) {
-    const DevAgg& ag = p.aggs[a];
-    uint32_t ma = m;
-    if (ag.leaf >= 0) {
-      ma &= leaf_mask(p.leaves[ag.leaf], cols, r0);
-      if (!ma) continue;
-    }
-    switch (ag.op) {
-      case AGG_SUM_F64: {
-        double v[4];
-        load_f64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) acc.add_f64(acc.at(key[i], ag.slot), v[i]);
-        break;
-      }
-      case AGG_SUM_I64: {
-        long long v[4];
-        load_i64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) acc.add_i64(acc.at(key[i], ag.slot), v[i]);
-        break;
-      }
-      case AGG_COUNT_IF: {
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) acc.add_i64(acc.at(key[i], ag.slot), 1);
-        break;
-      }
-      case AGG_MIN_F64: case AGG_MAX_F64: {
-        double v[4];
-        load_f64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) {
-            if (ag.op == AGG_MIN_F64) acc.min_i64(acc.at(key[i], ag.slot), f64_to_ord(v[i]));
-            else acc.max_i64(acc.at(key[i], ag.slot), f64_to_ord(v[i]));
-          }
-        break;
-      }
-      case AGG_MIN_I64: case AGG_MAX_I64: {
-        long long v[4];
-        load_i64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) {
-            if (ag.op == AGG_MIN_I64) acc.min_i64(acc.at(key[i], ag.slot), v[i]);
-            else acc.max_i64(acc.at(key[i], ag.slot), v[i]);
-          }
-        break;
-      }
-      case AGG_SUM_F64_I64: case AGG_MIN_F64_I64: case AGG_MAX_F64_I64: {
-        long long v[4];
-        load_i64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) {
-            if (ag.op == AGG_SUM_F64_I64) acc.add_f64(acc.at(key[i], ag.slot), (double)v[i]);
-            else if (ag.op == AGG_MIN_F64_I64) acc.min_i64(acc.at(key[i], ag.slot), f64_to_ord((double)v[i]));
-            else acc.max_i64(acc.at(key[i], ag.slot), f64_to_ord((double)v[i]));
-          }
-        break;
-      }
-      case AGG_SUM_I64_F64: case AGG_MIN_I64_F64: case AGG_MAX_I64_F64: {
-        double v[4];
-        load_f64x4(cols[ag.col], r0, v);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) {
-            if (ag.op == AGG_SUM_I64_F64) acc.add_i64(acc.at(key[i], ag.slot), (long long)v[i]);
-            else if (ag.op == AGG_MIN_I64_F64) acc.min_i64(acc.at(key[i], ag.slot), (long long)v[i]);
-            else acc.max_i64(acc.at(key[i], ag.slot), (long long)v[i]);
-          }
-        break;
-      }
-      case AGG_HLL: {
-        uint32_t ids[4];
-        load_ids4(cols[ag.col], ag.width, r0, ids);
-#pragma unroll
-        for (int i = 0; i < 4; i++)
-          if ((ma >> i) & 1u) {
-            uint8_t* regs = p.hll + (((uint64_t)key[i] * (uint64_t)p.n_hll + (uint64_t)ag.hll_index) << HLL_P);
-            hll_update(regs, hll_value(ag, ids[i]));
-          }
-        break;
-      }
-      default: break;
-    }
-  }
-}
+// one unit of the scan (filter -> key -> aggregate over 4096 rows)
+#include "scan_unit.cuh"
 
 // coarse index over spans lives right after the sentinel span: see plan.cpp (layout of the
 // per-query device blob).  COARSE_UNITS units per coarse entry.
 constexpr uint32_t COARSE_UNITS = 64;
 
 template <int STRAT>
-__global__ void __launch_bounds__(SCAN_THREADS) scan_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse) {
+__global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse) {
   extern __shared__ __align__(16) unsigned long long smem[];
   __shared__ uint32_t s_chunk, s_span;
   const int tid = threadIdx.x;

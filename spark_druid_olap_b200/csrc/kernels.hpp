@@ -13,7 +13,7 @@ constexpr int MAX_AGGS = 16;
 constexpr int MAX_SLOTS = MAX_AGGS + 1;
 constexpr int SCAN_THREADS = 256;
 constexpr int ROWS_PER_THREAD = 4;
-constexpr int UNIT_ROWS = SCAN_THREADS * ROWS_PER_THREAD;  // 1024 rows: one pass of a block
+constexpr int UNIT_ROWS = SCAN_THREADS * ROWS_PER_THREAD * 4;  // 4096 rows: one pass of a block (4 vectors per thread)
 constexpr uint64_t HASH_EMPTY = 0xFFFFFFFFFFFFFFFFull;
 
 // A span is a run of rows of one segment that shares its time-derived key part; interval pruning
