@@ -281,6 +281,13 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
   }
 
   size_t smem = scan_smem_bytes(strat, plan.n_keys, plan.n_slots);
+  p.hll_mode = HLL_IN_GLOBAL;
+  if (plan.n_hll && strat != STRAT_HASH) {
+    // keep the sketches in shared memory when they fit next to the aggregate table
+    if (plan.n_keys * (uint64_t)plan.n_hll * HLL_M + smem <= 96 * 1024) p.hll_mode = HLL_IN_SMEM_ALL;
+    else if (plan.dev_dims.empty() && (size_t)plan.n_hll * HLL_M + smem <= 200 * 1024) p.hll_mode = HLL_IN_SMEM_SPAN;
+    smem += scan_hll_smem_bytes(p.hll_mode, plan.n_keys, plan.n_hll);
+  }
   int grid = scan_grid_size(strat, smem, sm_count_);
   const uint32_t n_chunks = (plan.n_units + p.units_per_chunk - 1) / p.units_per_chunk;
   grid = (int)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid, n_chunks));

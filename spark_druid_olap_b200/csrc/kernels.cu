@@ -126,6 +126,36 @@ __device__ __forceinline__ void hll_update(uint8_t* regs, uint32_t packed) {
     old = prev;
   }
 }
+// same update on a shared-memory sketch
+__device__ __forceinline__ void hll_update_sm(unsigned int* words, uint32_t packed) {
+  const uint32_t idx = packed >> 6, rho = packed & 63u;
+  unsigned int* word = words + (idx >> 2);
+  const int sh = (idx & 3u) * 8;
+  unsigned int old = *(volatile unsigned int*)word;
+  for (;;) {
+    if (((old >> sh) & 0xffu) >= rho) return;
+    unsigned int nw = (old & ~(0xffu << sh)) | (rho << sh);
+    unsigned int prev = atomicCAS(word, old, nw);
+    if (prev == old) return;
+    old = prev;
+  }
+}
+// merge `n_words` shared-memory sketch words into the HBM registers (byte-wise max) and clear them
+__device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned int* global_words, uint32_t n_words) {
+  for (uint32_t w = threadIdx.x; w < n_words; w += SCAN_THREADS) {
+    const unsigned int mine = sm_words[w];
+    if (!mine) continue;
+    sm_words[w] = 0u;
+    unsigned int old = *(volatile unsigned int*)(global_words + w);
+    for (;;) {
+      const unsigned int nw = __vmaxu4(old, mine);
+      if (nw == old) break;
+      const unsigned int prev = atomicCAS(global_words + w, old, nw);
+      if (prev == old) break;
+      old = prev;
+    }
+  }
+}
 __device__ __forceinline__ uint32_t hll_value(const DevAgg& a, uint32_t id) {
   if (a.hll_mode == HLL_LUT) return __ldg(a.hll_lut + id);
   if (a.hll_mode == HLL_DIRECT_INT) return hll_pack(xxh64_int((int32_t)id, HLL_SEED));
@@ -143,10 +173,12 @@ struct Acc<STRAT_LANE> {
   typedef uint32_t key_t;
   unsigned long long* base;  // smem + tid
   int ns;
+  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
   static constexpr int SLOT_STRIDE = SCAN_THREADS;  // elements between consecutive slots of one group
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)(g * ns + slot) * SCAN_THREADS; }
   // a thread's own count stays far below 2^32: bump the low word only
   __device__ __forceinline__ void count1(unsigned long long* q) const { *(unsigned int*)q += 1u; }
+  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { *(unsigned int*)q += (unsigned int)c; }
   __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { *q += (unsigned long long)v; }
   __device__ __forceinline__ void add_f64(unsigned long long* q, double v) const { *(double*)q += v; }
   __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v < c) *(long long*)q = v; }
@@ -164,29 +196,35 @@ struct Acc<STRAT_BLOCK> : AtomicOps {
   typedef uint32_t key_t;
   unsigned long long* base;  // smem table
   int ns;
+  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
   static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)g * ns + slot; }
   // one launch scans fewer than 2^32 rows (checked on the host), so a block's count fits the low
   // word: a native 32-bit shared atomic instead of the 64-bit compare-and-swap loop
   __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd((unsigned int*)q, 1u); }
+  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd((unsigned int*)q, (unsigned int)c); }
 };
 template <>
 struct Acc<STRAT_GLOBAL> : AtomicOps {
   typedef uint64_t key_t;
   unsigned long long* base;
   int ns;
+  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
   static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
   __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
+  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd(q, (unsigned long long)c); }
 };
 template <>
 struct Acc<STRAT_HASH> : AtomicOps {
   typedef uint64_t key_t;
   unsigned long long* base;
   int ns;
+  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
   static constexpr int SLOT_STRIDE = 1;
   __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
   __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
+  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd(q, (unsigned long long)c); }
 };
 
 // find-or-claim the slot of `key` (linear probing).  Returns HASH_EMPTY if the table is full.
@@ -219,6 +257,15 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_cons
   const int ns = p.n_slots;
   Acc<STRAT> acc;
   acc.ns = ns;
+  // shared-memory HLL sketches sit behind the aggregate table
+  const uint32_t hll_sm_words = p.hll_mode == HLL_IN_SMEM_ALL ? (uint32_t)p.n_keys * p.n_hll * (HLL_M / 4)
+                                : (p.hll_mode == HLL_IN_SMEM_SPAN ? (uint32_t)p.n_hll * (HLL_M / 4) : 0u);
+  {
+    size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS : (STRAT == STRAT_BLOCK ? (size_t)p.n_keys * ns : 0);
+    acc.hll_sm = (unsigned int*)(smem + table_words);
+    for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
+  }
+  uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (block-uniform)
   if (STRAT == STRAT_LANE) {
     const uint32_t n = (uint32_t)p.n_keys * ns;
     for (uint32_t x = 0; x < n; x++) smem[(size_t)x * SCAN_THREADS + tid] = p.slot_init[x % ns];
@@ -253,8 +300,20 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_cons
         sp = p.spans[s];
         next_begin = p.spans[s + 1].unit_begin;
       }
+      if (p.hll_mode == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
+        // the cached sketch belongs to another group: merge it into HBM, start an empty one
+        __syncthreads();
+        if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)p.n_hll * HLL_M), hll_sm_words);
+        hll_key = sp.key_base;
+        __syncthreads();
+      }
       process_unit<STRAT>(p, sp, u - sp.unit_begin, acc);
     }
+  }
+  if (hll_sm_words) {
+    __syncthreads();
+    if (p.hll_mode == HLL_IN_SMEM_ALL) hll_flush_sm(acc.hll_sm, (unsigned int*)p.hll, hll_sm_words);
+    else if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)p.n_hll * HLL_M), hll_sm_words);
   }
 
   if (STRAT == STRAT_LANE) {
@@ -302,6 +361,11 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_cons
   }
 }
 
+size_t scan_hll_smem_bytes(int hll_mode, uint64_t n_keys, int n_hll) {
+  if (hll_mode == HLL_IN_SMEM_ALL) return (size_t)n_keys * n_hll * HLL_M;
+  if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * HLL_M;
+  return 0;
+}
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots) {
   if (strategy == STRAT_LANE) return (size_t)n_keys * n_slots * SCAN_THREADS * 8;
   if (strategy == STRAT_BLOCK) return (size_t)n_keys * n_slots * 8;

@@ -63,6 +63,12 @@ enum AggOp : int32_t {
 enum SlotOp : int32_t { SLOT_SUM_I64 = 0, SLOT_SUM_F64 = 1, SLOT_MIN_I64 = 2, SLOT_MAX_I64 = 3 };
 
 enum HllMode : int32_t { HLL_DIRECT_INT = 0, HLL_DIRECT_LONG = 1, HLL_LUT = 2 };
+// where HLL registers are updated during the scan
+enum HllPlace : int32_t {
+  HLL_IN_GLOBAL = 0,     // straight into the HBM register table
+  HLL_IN_SMEM_ALL = 1,   // every group's sketch lives in shared memory, merged into HBM at block end
+  HLL_IN_SMEM_SPAN = 2,  // no grouping dimension: the key is constant per span, one cached sketch per block
+};
 struct DevAgg {
   int32_t op;
   int32_t col;        // metric column slot (or dimension slot for HLL)
@@ -100,7 +106,7 @@ struct ScanParams {
   int32_t n_slots;  // per group, slot 0 = row count
   int32_t n_hll;
   int32_t ignore_key_base;  // count-only pass: all rows fall into key 0
-  int32_t pad0;
+  int32_t hll_mode;         // HllPlace: where the registers live while scanning
   uint64_t n_keys;  // dense key-space size (LANE / BLOCK / GLOBAL)
   int32_t slot_op[MAX_SLOTS];
   uint64_t slot_init[MAX_SLOTS];
@@ -122,6 +128,7 @@ void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n
 
 // scan
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots);
+size_t scan_hll_smem_bytes(int hll_mode, uint64_t n_keys, int n_hll);
 int scan_grid_size(int strategy, size_t smem_bytes, int sm_count);
 void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem_bytes, cudaStream_t st);
 void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, const uint64_t* slot_init_dev_or_null,

@@ -134,7 +134,31 @@ __device__ __forceinline__ uint32_t eval_filter16(const ScanParams& p, const voi
 }
 
 // aggregate N consecutive rows starting at r0 (N = 4: vector loads; N = 1: scalar loads); m = which rows
-template <int STRAT, int N>
+__device__ __forceinline__ double warp_add(double v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+__device__ __forceinline__ long long warp_add(long long v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+  return v;
+}
+__device__ __forceinline__ long long warp_min(long long v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
+}
+__device__ __forceinline__ long long warp_max(long long v) {
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, off));
+  return v;
+}
+
+// WARP = called by all 32 lanes together (lanes without rows pass m = 0): lets a warp whose surviving
+// rows all share one key (time buckets, sorted low-cardinality keys) fold them with shuffles and
+// issue one atomic per aggregate instead of one per row.
+template <int STRAT, int N, bool WARP>
 __device__ __forceinline__ void accumulate(const ScanParams& p, const void* const* cols, const Acc<STRAT>& acc, uint64_t key_base,
                                            uint32_t r0, uint32_t m) {
   typedef typename Acc<STRAT>::key_t key_t;
@@ -162,9 +186,31 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
   unsigned long long* row[N];
 #pragma unroll
   for (int i = 0; i < N; i++) row[i] = acc.at(key[i], 0);
+  bool uni = false, is_leader = false;
+  unsigned long long* rowL = row[0];
+  if (WARP && STRAT != STRAT_LANE) {
+    key_t lk = key[0];
 #pragma unroll
-  for (int i = 0; i < N; i++)
-    if ((m >> i) & 1u) acc.count1(row[i]);  // slot 0: row count of the group
+    for (int i = N - 1; i >= 0; i--)
+      if ((m >> i) & 1u) { lk = key[i]; rowL = row[i]; }
+    bool same = true;
+#pragma unroll
+    for (int i = 0; i < N; i++)
+      if (((m >> i) & 1u) && key[i] != lk) same = false;
+    const unsigned have = __ballot_sync(0xffffffffu, m != 0u);
+    const int leader = __ffs(have) - 1;
+    const key_t kl = __shfl_sync(0xffffffffu, lk, leader);
+    uni = __all_sync(0xffffffffu, m == 0u || (same && lk == kl));
+    is_leader = (int)(threadIdx.x & 31u) == leader;
+  }
+  if (uni) {
+    const int c = __reduce_add_sync(0xffffffffu, __popc(m));
+    if (is_leader) acc.countn(rowL, c);
+  } else {
+#pragma unroll
+    for (int i = 0; i < N; i++)
+      if ((m >> i) & 1u) acc.count1(row[i]);  // slot 0: row count of the group
+  }
 
   const int n_aggs = p.n_aggs;
   for (int a = 0; a < n_aggs; a++) {
@@ -172,7 +218,7 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
     uint32_t ma = m;
     if (ag.leaf >= 0) {
       ma &= leaf_test<N>(p.leaves[ag.leaf], cols, r0);
-      if (!ma) continue;
+      if (!WARP && !ma) continue;
     }
     const int so = ag.slot * Acc<STRAT>::SLOT_STRIDE;
 #define SDO_ROWS(EXPR)                                     \
@@ -182,34 +228,73 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
       EXPR;                                                \
     }                                                      \
   }
+// uniform-key warp: fold the rows with shuffles, one atomic by the leader lane
+#define SDO_SUMF(VAL)                                                                   \
+  if (uni) {                                                                            \
+    double t = 0.0;                                                                     \
+    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t += (VAL);       \
+    t = warp_add(t);                                                                    \
+    if (is_leader) acc.add_f64(rowL + so, t);                                           \
+  } else { SDO_ROWS(acc.add_f64(q, (VAL))) }
+#define SDO_SUMI(VAL)                                                                   \
+  if (uni) {                                                                            \
+    long long t = 0;                                                                    \
+    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t += (VAL);       \
+    t = warp_add(t);                                                                    \
+    if (is_leader) acc.add_i64(rowL + so, t);                                           \
+  } else { SDO_ROWS(acc.add_i64(q, (VAL))) }
+#define SDO_MINI(VAL)                                                                   \
+  if (uni) {                                                                            \
+    long long t = 0x7FFFFFFFFFFFFFFFll;                                                 \
+    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t = min(t, (long long)(VAL)); \
+    t = warp_min(t);                                                                    \
+    if (is_leader) acc.min_i64(rowL + so, t);                                           \
+  } else { SDO_ROWS(acc.min_i64(q, (VAL))) }
+#define SDO_MAXI(VAL)                                                                   \
+  if (uni) {                                                                            \
+    long long t = (long long)0x8000000000000000ull;                                     \
+    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t = max(t, (long long)(VAL)); \
+    t = warp_max(t);                                                                    \
+    if (is_leader) acc.max_i64(rowL + so, t);                                           \
+  } else { SDO_ROWS(acc.max_i64(q, (VAL))) }
     switch (ag.op) {
-      case AGG_SUM_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.add_f64(q, v[i])) break; }
-      case AGG_SUM_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.add_i64(q, v[i])) break; }
-      case AGG_COUNT_IF: { SDO_ROWS(acc.add_i64(q, 1)) break; }
-      case AGG_MIN_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.min_i64(q, f64_to_ord(v[i]))) break; }
-      case AGG_MAX_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.max_i64(q, f64_to_ord(v[i]))) break; }
-      case AGG_MIN_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.min_i64(q, v[i])) break; }
-      case AGG_MAX_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.max_i64(q, v[i])) break; }
-      case AGG_SUM_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.add_f64(q, (double)v[i])) break; }
-      case AGG_MIN_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.min_i64(q, f64_to_ord((double)v[i]))) break; }
-      case AGG_MAX_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.max_i64(q, f64_to_ord((double)v[i]))) break; }
-      case AGG_SUM_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.add_i64(q, (long long)v[i])) break; }
-      case AGG_MIN_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.min_i64(q, (long long)v[i])) break; }
-      case AGG_MAX_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_ROWS(acc.max_i64(q, (long long)v[i])) break; }
+      case AGG_SUM_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_SUMF(v[i]) break; }
+      case AGG_SUM_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_SUMI(v[i]) break; }
+      case AGG_COUNT_IF: { SDO_SUMI(1ll) break; }
+      case AGG_MIN_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
+      case AGG_MAX_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
+      case AGG_MIN_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_MINI(v[i]) break; }
+      case AGG_MAX_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_MAXI(v[i]) break; }
+      case AGG_SUM_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_SUMF((double)v[i]) break; }
+      case AGG_MIN_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_MINI(f64_to_ord((double)v[i])) break; }
+      case AGG_MAX_F64_I64: { long long v[N]; load_i64<N>(cols[ag.col], r0, v); SDO_MAXI(f64_to_ord((double)v[i])) break; }
+      case AGG_SUM_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_SUMI((long long)v[i]) break; }
+      case AGG_MIN_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_MINI((long long)v[i]) break; }
+      case AGG_MAX_I64_F64: { double v[N]; load_f64<N>(cols[ag.col], r0, v); SDO_MAXI((long long)v[i]) break; }
       case AGG_HLL: {
         uint32_t ids[N];
         load_ids<N>(cols[ag.col], ag.width, r0, ids);
 #pragma unroll
         for (int i = 0; i < N; i++)
           if ((ma >> i) & 1u) {
-            uint8_t* regs = p.hll + (((uint64_t)key[i] * (uint64_t)p.n_hll + (uint64_t)ag.hll_index) << HLL_P);
-            hll_update(regs, hll_value(ag, ids[i]));
+            const uint32_t packed = hll_value(ag, ids[i]);
+            if (p.hll_mode == HLL_IN_GLOBAL) {
+              uint8_t* regs = p.hll + (((uint64_t)key[i] * (uint64_t)p.n_hll + (uint64_t)ag.hll_index) << HLL_P);
+              hll_update(regs, packed);
+            } else {
+              const uint32_t set = (p.hll_mode == HLL_IN_SMEM_ALL ? (uint32_t)key[i] * (uint32_t)p.n_hll : 0u) + (uint32_t)ag.hll_index;
+              hll_update_sm(acc.hll_sm + set * (HLL_M / 4), packed);
+            }
           }
         break;
       }
       default: break;
     }
 #undef SDO_ROWS
+#undef SDO_SUMF
+#undef SDO_SUMI
+#undef SDO_MINI
+#undef SDO_MAXI
   }
 }
 
@@ -240,14 +325,17 @@ __device__ __forceinline__ void process_unit(const ScanParams& p, const DevSpan&
       if (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        accumulate<STRAT, 1>(p, cols, acc, key_base, base + (uint32_t)(b >> 2) * VEC_STRIDE + (uint32_t)(b & 3), 1u);
+        accumulate<STRAT, 1, false>(p, cols, acc, key_base, base + (uint32_t)(b >> 2) * VEC_STRIDE + (uint32_t)(b & 3), 1u);
       }
     }
   } else {
 #pragma unroll 1
     for (int j = 0; j < VECS; j++) {
       const uint32_t mj = (m >> (4 * j)) & 0xFu;
-      if (mj) accumulate<STRAT, 4>(p, cols, acc, key_base, base + j * VEC_STRIDE, mj);
+      if (!__any_sync(0xffffffffu, mj != 0u)) continue;
+      // lanes whose vector j lies outside the span join with m = 0 and read a harmless in-span address
+      const uint32_t r0 = ((vmask >> j) & 1u) ? base + j * VEC_STRIDE : (sp.row_begin & ~3u);
+      accumulate<STRAT, 4, true>(p, cols, acc, key_base, r0, mj);
     }
   }
 }
