@@ -539,6 +539,12 @@ def execute(tbl, q, return_registers=False):
                 raise NotImplementedError(t)
         for g in range(ng):
             out[g][name] = vals[g]
+    return finalize(q, out, registers, [name for name, _ in decoders], return_registers)
+
+
+def finalize(q, out, registers, key_names, return_registers=False):
+    """Post-aggregations, having, ordering and limit over grouped rows (each carrying its sortable "__key")."""
+    qt = q["queryType"]
     for p in q.get("postAggregations") or []:
         for r in out:
             r[p["name"]] = _post(p, r)
@@ -557,7 +563,8 @@ def execute(tbl, q, return_registers=False):
             col = m if isinstance(m, str) else m["metric"]
             idx.sort(key=lambda i: ((out[i][col] if inverted else -out[i][col]), out[i]["__key"]))
         else:
-            dn = dims[0].get("outputName", dims[0]["dimension"])
+            d0 = q["dimension"]
+            dn = d0 if isinstance(d0, str) else d0.get("outputName", d0["dimension"])
             ps = m.get("previousStop") or ""
             if ps:
                 idx = [i for i in idx if (_cmp_bytes(out[i][dn], ps) < 0 if inverted else _cmp_bytes(out[i][dn], ps) > 0)]
@@ -565,7 +572,7 @@ def execute(tbl, q, return_registers=False):
         idx = idx[:q["threshold"]]
     elif qt == "groupBy" and q.get("limitSpec"):
         ls = q["limitSpec"]
-        dim_pos = {name: c for c, (name, _) in enumerate(decoders)}
+        dim_pos = {name: c for c, name in enumerate(key_names)}
         import functools
 
         def cmp(i, j):

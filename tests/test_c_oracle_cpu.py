@@ -1,0 +1,59 @@
+"""The threaded C restatement (timed CPU baseline) against the numpy oracle on the query corpus: the two share the
+predicate semantics but not the execution (C: per-thread hash aggregate + Neumaier sums; numpy: unique/fsum)."""
+import json
+
+import numpy as np
+import pytest
+
+import helpers as H
+import queries as Q
+from oracle import c_oracle
+from oracle import druid_oracle as orc
+
+SF = 0.02
+
+
+@pytest.fixture(scope="module")
+def tables(native_libs):
+    from spark_druid_olap_b200 import tpch
+    c_oracle.build()
+    tbl = H.oracle_table(tpch.FlatTable(SF, H.TEST_COLUMNS + ["order_year"]))
+    return tbl, c_oracle.CTable(tbl)
+
+
+def test_c_xxh64_matches_python(tables):
+    L = c_oracle._load()
+    for v in (0, 1, -1, 42, 123456789, 2147483647, -2147483648):
+        assert L.oc_xxh64_int(v, 42) == orc.spark_hash(v, "int")
+    for v in (0, 1, -1, 1 << 40, -(1 << 62), 600000000):
+        assert L.oc_xxh64_long(v, 42) == orc.spark_hash(v, "long")
+
+
+CASES = [("q1", lambda: Q.q1_style(), False), ("basic_agg", lambda: Q.basic_agg(), False), ("ship_range", lambda: Q.ship_date_range(), False),
+         ("proj_filt", lambda: Q.proj_filt_range(), False), ("q3", lambda: Q.q3(), False), ("q3_limit", lambda: Q.q3(10), True), ("q5", lambda: Q.q5(), False),
+         ("q5_topn", lambda: Q.q5_topn(), True), ("q8", lambda: Q.q8(), False), ("ts_day", lambda: Q.timeseries("P1D"), False),
+         ("ts_month", lambda: Q.timeseries("P1M"), False), ("by_orderkey", lambda: Q.by_orderkey(), False), ("agg_zoo", lambda: Q.agg_zoo(), False),
+         ("having", lambda: Q.having_query(), True)] + [("filter_" + n, (lambda f_: lambda: Q.with_filter(f_))(f), False) for n, f in Q.filter_cases() if n != "ts_null_guard"]
+
+
+@pytest.mark.parametrize("name,mk,ordered", CASES, ids=[c[0] for c in CASES])
+def test_c_oracle_equals_numpy_oracle(tables, name, mk, ordered):
+    tbl, ct = tables
+    q = json.loads(mk().to_json())
+    for threads in (1, 5):
+        got = c_oracle.execute(ct, q, threads=threads)
+        assert got is not None, "shape not covered by the C oracle"
+        H.assert_rows_equal(got, orc.execute(tbl, q), ordered=ordered, what=f"{name}[{threads} threads]")
+
+
+def test_c_oracle_hll_registers_exact(tables):
+    tbl, ct = tables
+    q = json.loads(Q.timeseries("P1M").to_json())
+    _, r1 = c_oracle.execute(ct, q, return_registers=True)
+    _, r2 = orc.execute(tbl, q, return_registers=True)
+    assert np.array_equal(r1["custs"], r2["custs"])
+
+
+def test_shapes_outside_c_oracle_fall_back(tables):
+    tbl, ct = tables
+    assert c_oracle.execute(ct, json.loads(Q.q7().to_json())) is None  # timeFormat dimension: numpy oracle only

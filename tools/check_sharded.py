@@ -1,0 +1,61 @@
+"""torchrun --nproc-per-node N tools/check_sharded.py [sf]: every rank loads shard `rank` of N, runs the corpus through the
+sharded path (NCCL merge) and rank 0 (dense) / all ranks (sparse) compare with the oracle on the whole table."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import faulthandler  # noqa: E402
+import torch  # noqa: E402
+
+faulthandler.dump_traceback_later(100, exit=True)
+import torch.distributed as dist  # noqa: E402
+import helpers as H  # noqa: E402
+import queries as Q  # noqa: E402
+import spark_druid_olap_b200 as sdo  # noqa: E402
+from oracle import druid_oracle as orc  # noqa: E402
+from spark_druid_olap_b200 import sharded, tpch  # noqa: E402
+
+sf = float(sys.argv[1]) if len(sys.argv) > 1 else 0.05
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "o_orderkey", "o_custkey", "o_orderdate", "o_shippriority",
+        "c_mktsegment", "s_region", "s_nation", "count"]
+eng = sdo.Engine(local)
+eng.create_datasource("tpch")
+mine = tpch.FlatTable(sf, cols, rank, world)
+eng.load("tpch", mine.engine_columns(), partition=rank)
+whole = H.oracle_table([tpch.FlatTable(sf, cols, r, world) for r in range(world)])
+ok = True
+for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style("block"), False), ("ts_month_hll", Q.timeseries("P1M"), False),
+                            ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
+                            ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)]:
+    q = json.loads(spec.to_json())
+    print(f'[rank {rank}] {name} ...', flush=True)
+    res, info = sharded.execute_sharded(eng, q)
+    print(f'[rank {rank}] {name} engine done', flush=True)
+    want = orc.execute(whole, q)
+    try:
+        if info["dense"]:
+            if rank == 0:
+                H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered, what=name)
+        else:
+            # sparse: every rank holds a disjoint share; gather and compare the union
+            parts = [None] * world
+            dist.all_gather_object(parts, H.engine_rows(res))
+            if rank == 0:
+                H.assert_rows_equal([r for p in parts for r in p], want, what=name)
+        if rank == 0:
+            print(f"OK   {name:22s} dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
+    except AssertionError as e:
+        ok = False
+        print(f"FAIL {name} rank {rank}: {e}")
+flag = torch.tensor([0 if ok else 1], device="cuda")
+dist.all_reduce(flag)
+if rank == 0:
+    print("sharded check:", "PASS" if int(flag) == 0 else "FAIL", f"world={world} sf={sf}")
+dist.destroy_process_group()
+sys.exit(0 if int(flag) == 0 else 1)
