@@ -93,6 +93,17 @@ class CTable:
         self.day0 = int(self.time.min()) // 86400000 if len(self.time) else 0
         self.days = (int(self.time.max()) // 86400000 - self.day0 + 1) if len(self.time) else 0
         self._hll_tables = {}
+        self._ranked = {}
+
+    def ranked(self, name):
+        """(codes re-ranked by the UTF-8 byte order of their strings, that order) -- cached: it is table preparation, not query work."""
+        if name not in self._ranked:
+            d = self.dims[name]
+            order = sorted(range(len(d[2])), key=lambda i: d[2][i].encode("utf-8"))
+            rank = np.empty(len(d[2]), dtype=np.int32)
+            rank[order] = np.arange(len(order), dtype=np.int32)
+            self._ranked[name] = (np.ascontiguousarray(rank[d[1]]), order)
+        return self._ranked[name]
 
     def hll_table(self, name):
         if name not in self._hll_tables:
@@ -203,11 +214,7 @@ def _execute(ct, q, threads, return_registers):
         cd = _Dim()
         name = d.get("outputName", d["dimension"])
         if dd[0] == "str":
-            order = sorted(range(len(dd[2])), key=lambda i: dd[2][i].encode("utf-8"))
-            rank = np.empty(len(dd[2]), dtype=np.int32)
-            rank[order] = np.arange(len(order), dtype=np.int32)
-            col = rank[dd[1]]  # rank by UTF-8 order so that key order is string order
-            keep.append(col)
+            col, order = ct.ranked(d["dimension"])  # codes re-ranked by UTF-8 order so that key order is string order
             cd.col_type, cd.col, cd.base, cd.card = 0, col.ctypes.data, 0, len(dd[2])
             ss = [dd[2][i] for i in order]
             decoders.append((name, len(dd[2]), 0, (lambda ss_: lambda v: ss_[int(v)])(ss)))
