@@ -176,6 +176,19 @@ typedef struct {
   int n_hll;
 } sdo_partial_view;
 
+/* Shards of one datasource that live in different engines must share one id space per dimension before
+ * their partials can be merged: a string dimension needs the same sorted dictionary everywhere, an integer
+ * dimension the same cardinality.  (A Druid broker merges on string values, so the reference needs no such
+ * step; here the merge is on packed ids.)  sdo_dimension_dictionary exposes a string dimension's dictionary
+ * (n entries, offsets[n+1] into bytes; integer dimensions report n = 0; pointers stay valid until the
+ * dimension is next extended or the datasource dropped); sdo_dimension_extend merges `n_values` strings
+ * into it -- re-encoding resident segments on the device when ids move -- or raises an integer dimension's
+ * cardinality to at least `min_cardinality`. */
+int sdo_dimension_dictionary(sdo_engine* e, const char* datasource, const char* dimension, int64_t* n_out,
+                             const int64_t** offsets_out, const char** bytes_out, int64_t* cardinality_out);
+int sdo_dimension_extend(sdo_engine* e, const char* datasource, const char* dimension, int64_t n_values,
+                         const int64_t* value_offsets, const char* value_bytes, int64_t min_cardinality);
+
 int sdo_query_partial(sdo_engine* e, const char* query_json, size_t len, sdo_partial** out);
 int sdo_partial_view_get(sdo_partial* p, sdo_partial_view* out);
 /* Sparse path: split local groups by owner = mix(key) % n_ranks into n_ranks contiguous runs

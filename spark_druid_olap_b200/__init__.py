@@ -101,6 +101,8 @@ def lib():
         "sdo_partial_finish": (C.c_int, [vp, C.POINTER(vp)]),
         "sdo_partial_free": (None, [vp]),
         "sdo_groupby_sum_noalloc": (C.c_int, [C.c_int, vp, vp, i64, C.c_int, vp, vp, vp]),
+        "sdo_dimension_dictionary": (C.c_int, [vp, cp, cp, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), C.POINTER(i64)]),
+        "sdo_dimension_extend": (C.c_int, [vp, cp, cp, i64, vp, vp, i64]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -116,6 +118,7 @@ EXPORTED_SYMBOLS = [
     "sdo_query_cancel", "sdo_result_num_rows", "sdo_result_num_columns", "sdo_result_column_get", "sdo_result_hll_registers",
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
+    "sdo_dimension_dictionary", "sdo_dimension_extend",
 ]
 
 NOALLOC_MAX_KEYS = 24
@@ -329,6 +332,23 @@ class Engine:
         out = C.c_char_p()
         _check(lib().sdo_datasource_segments(self._h, name.encode(), C.byref(out)))
         return json.loads(out.value.decode())
+
+    def dimension_dictionary(self, datasource, dimension):
+        """(list of dictionary strings, cardinality); the list is empty for integer dimensions."""
+        n, card = C.c_int64(), C.c_int64()
+        offs, raw = C.c_void_p(), C.c_void_p()
+        _check(lib().sdo_dimension_dictionary(self._h, datasource.encode(), dimension.encode(), C.byref(n), C.byref(offs), C.byref(raw), C.byref(card)))
+        if n.value == 0:
+            return [], int(card.value)
+        o = np.ctypeslib.as_array(C.cast(offs, C.POINTER(C.c_int64)), (n.value + 1,))
+        b = C.string_at(raw, int(o[n.value]))
+        return [b[o[i]:o[i + 1]].decode("utf-8") for i in range(n.value)], int(card.value)
+
+    def extend_dimension(self, datasource, dimension, values=(), min_cardinality=0):
+        """Merge `values` into a string dimension's dictionary / raise an integer dimension's cardinality."""
+        offsets, blob = _pack_strings(list(values))
+        _check(lib().sdo_dimension_extend(self._h, datasource.encode(), dimension.encode(), len(values), offsets.ctypes.data if len(values) else None,
+                                          blob.ctypes.data if len(values) else None, int(min_cardinality)))
 
     def execute(self, query):
         """QuerySpec.executeQuery: query JSON in, columnar result out (DruidQuerySpec.scala:598-599)."""

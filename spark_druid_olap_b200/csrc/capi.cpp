@@ -159,6 +159,33 @@ void sdo_result_free(sdo_result* r) {
   delete r;
 }
 
+int sdo_dimension_dictionary(sdo_engine* e, const char* datasource, const char* dimension, int64_t* n_out, const int64_t** offsets_out,
+                             const char** bytes_out, int64_t* cardinality_out) {
+  if (!e || !datasource || !dimension || !n_out || !offsets_out || !bytes_out) return bad("sdo_dimension_dictionary: NULL argument");
+  return guard([&] {
+    auto ds = e->e->store().get(datasource);
+    int di = ds->dim_index(dimension);
+    if (di < 0) throw NotFound(std::string("unknown dimension '") + dimension + "'");
+    // keep the snapshot alive in a per-thread slot: dictionaries are replaced, never mutated
+    thread_local std::shared_ptr<Dictionary> hold;
+    hold = e->e->store().dictionary(datasource, dimension);
+    const bool is_dict = ds->dims[di].enc == DimEncoding::Dict;
+    *n_out = is_dict ? hold->size() : 0;
+    *offsets_out = hold->offsets.data();
+    *bytes_out = hold->bytes.data();
+    if (cardinality_out) *cardinality_out = ds->dims[di].cardinality;
+  });
+}
+int sdo_dimension_extend(sdo_engine* e, const char* datasource, const char* dimension, int64_t n_values, const int64_t* value_offsets,
+                         const char* value_bytes, int64_t min_cardinality) {
+  if (!e || !datasource || !dimension || (n_values > 0 && (!value_offsets || !value_bytes))) return bad("sdo_dimension_extend: NULL argument");
+  return guard([&] {
+    Dictionary d;
+    for (int64_t i = 0; i < n_values; i++) d.push(value_bytes + value_offsets[i], (size_t)(value_offsets[i + 1] - value_offsets[i]));
+    e->e->store().extend_dimension(datasource, dimension, n_values > 0 ? &d : nullptr, min_cardinality);
+  });
+}
+
 int sdo_query_partial(sdo_engine* e, const char* query_json, size_t len, sdo_partial** out) {
   if (!e || !query_json || !out) return bad("sdo_query_partial: NULL argument");
   *out = nullptr;

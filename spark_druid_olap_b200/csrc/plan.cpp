@@ -537,6 +537,28 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
     }
     if (used) plan.seg_index.push_back((int)si);
   }
+  if (plan.has_time_key && spec.has_time_boundary) {
+    // Sharded execution: every rank must number the time keys identically, whatever days its own
+    // segments happen to hold.  Enumerate the datasource's time grid (query granularity) over the
+    // globally agreed boundary and the query intervals.
+    Granularity qg;
+    if (ds.query_granularity != "NONE" && ds.query_granularity != "ALL") qg = simple_granularity(ds.query_granularity);
+    if (qg.kind != Granularity::Period || qg.months || qg.period_ms <= 0)
+      throw Unsupported("sharded time-keyed queries need a fixed-period queryGranularity (e.g. DAY, HOUR) on the datasource");
+    const int64_t unit = qg.period_ms;
+    const int64_t g0 = bucket_start(qg, spec.tb_min), g1 = bucket_start(qg, spec.tb_max);
+    if ((g1 - g0) / unit > (1ll << 22)) throw Unsupported("time grid too fine for a sharded time-keyed query");
+    for (int64_t t = g0; t <= g1; t += unit) {
+      bool in = false;
+      for (auto& iv : ivs)
+        if (t >= iv.start && t < iv.end) { in = true; break; }
+      if (!in) continue;
+      TimeKey tk;
+      if (plan.has_bucket) tk.bucket = bucket_start(spec.granularity, t);
+      for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second));
+      tk_ids[tk] = 0;
+    }
+  }
   if (plan.has_time_key) {
     uint64_t id = 0;
     for (auto& kv : tk_ids) { kv.second = id++; plan.time_keys.push_back(kv.first); }

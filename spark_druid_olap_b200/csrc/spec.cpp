@@ -320,6 +320,13 @@ QuerySpec parse_query_spec(const Json& j) {
     q.query_id = c->get_str("queryId", "");
     q.skip_empty_buckets = c->get_bool("skipEmptyBuckets", true);
     q.gpu_strategy = c->get_str("gpuStrategy", "");
+    if (const Json* tb = c->find("gpuTimeBoundary")) {
+      if (!tb->is_arr() || tb->arr.size() != 2 || !tb->arr[0].is_num() || !tb->arr[1].is_num()) throw Invalid("context.gpuTimeBoundary must be [minMs, maxMs]");
+      q.has_time_boundary = true;
+      q.tb_min = tb->arr[0].is_int ? tb->arr[0].inum : (int64_t)tb->arr[0].num;
+      q.tb_max = tb->arr[1].is_int ? tb->arr[1].inum : (int64_t)tb->arr[1].num;
+      if (q.tb_max < q.tb_min) throw Invalid("context.gpuTimeBoundary: max < min");
+    }
   }
   if (q.type == QuerySpec::GroupBy) {
     if (const Json* d = j.find("dimensions")) {

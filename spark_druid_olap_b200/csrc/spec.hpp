@@ -92,6 +92,10 @@ struct QuerySpec {
   std::string query_id;
   bool skip_empty_buckets = true;
   std::string gpu_strategy;  // context.gpuStrategy: force lane|block|global|hash (tests)
+  // context.gpuTimeBoundary = [minMs, maxMs]: the datasource's time range over ALL shards, set by the
+  // sharded host layer so that every rank numbers time-derived keys the same way
+  bool has_time_boundary = false;
+  int64_t tb_min = 0, tb_max = 0;
 };
 
 // Throws Invalid (malformed spec), Unsupported (javascript / spatial / search / select ...).

@@ -153,6 +153,114 @@ struct DevBuf {
 size_t padded_bytes(int64_t n_rows, int width) { return round_up((size_t)n_rows * width + 64, 256); }
 }  // namespace
 
+
+// Re-encode dimension `di` of every resident segment: ids through `lut` (nullptr = unchanged) into `new_width` bytes.
+void Store::reencode_segments(DataSource& ds, int di, const std::vector<uint32_t>* lut, int new_width) {
+  if (device_ < 0) {
+    for (auto& s : ds.segments)
+      if ((int)s->dim_width.size() > di) s->dim_width[di] = new_width;
+    return;
+  }
+  std::unique_ptr<DevBuf> dl;
+  if (lut) {
+    dl.reset(new DevBuf(lut->size() * 4));
+    SDO_CUDA(cudaMemcpy(dl->p, lut->data(), lut->size() * 4, cudaMemcpyHostToDevice));
+  }
+  for (auto& s : ds.segments) {
+    if ((int)s->dim_data.size() <= di || !s->dim_data[di]) continue;
+    int ow = s->dim_width[di];
+    void* nb = nullptr;
+    SDO_CUDA(cudaMalloc(&nb, padded_bytes(s->n_rows, new_width)));
+    SDO_CUDA(cudaMemset(nb, 0, padded_bytes(s->n_rows, new_width)));
+    launch_reencode(s->dim_data[di], ow, nb, new_width, s->n_rows, dl ? (const uint32_t*)dl->p : nullptr, 0);
+    SDO_CUDA(cudaDeviceSynchronize());
+    s->device_bytes += padded_bytes(s->n_rows, new_width);
+    s->device_bytes -= padded_bytes(s->n_rows, ow);
+    cudaFree(s->dim_data[di]);
+    s->dim_data[di] = nb;
+    s->dim_width[di] = new_width;
+  }
+}
+
+// Merge the values of `bd` into the sorted, de-duplicated datasource dictionary of dimension `di`; resident
+// segments are re-encoded when ids move or widen.  code_to_id (optional) maps bd's entries to the new ids.
+void Store::merge_dictionary(DataSource& ds, int di, const Dictionary& bd, std::vector<uint32_t>* code_to_id) {
+  DimMeta& dm = ds.dims[di];
+  const Dictionary& od = *dm.dict;
+  int64_t nb = bd.size(), no = od.size();
+  std::vector<int64_t> border((size_t)nb);
+  std::iota(border.begin(), border.end(), 0);
+  std::sort(border.begin(), border.end(), [&](int64_t a, int64_t b) { return utf8_cmp(bd.data(a), bd.len(a), bd.data(b), bd.len(b)) < 0; });
+  Dictionary merged;
+  std::vector<uint32_t> old_to_new((size_t)no);
+  std::vector<uint32_t> c2i((size_t)nb, 0);
+  int64_t i = 0, j = 0;
+  while (i < no || j < nb) {
+    int cmp;
+    if (i >= no) cmp = 1;
+    else if (j >= nb) cmp = -1;
+    else cmp = utf8_cmp(od.data(i), od.len(i), bd.data(border[j]), bd.len(border[j]));
+    uint32_t id = (uint32_t)merged.size();
+    if (cmp < 0) { merged.push(od.data(i), od.len(i)); old_to_new[i++] = id; }
+    else if (cmp > 0) {
+      const char* p = bd.data(border[j]);
+      size_t n = bd.len(border[j]);
+      merged.push(p, n);
+      c2i[border[j++]] = id;
+      // duplicates inside the batch dictionary map to the same id
+      while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) c2i[border[j++]] = id;
+    } else {
+      merged.push(od.data(i), od.len(i));
+      old_to_new[i++] = id;
+      const char* p = merged.data(id);
+      size_t n = merged.len(id);
+      while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) c2i[border[j++]] = id;
+    }
+  }
+  bool changed = merged.size() != no;
+  int w = std::max(dm.width, width_for(merged.size()));
+  if (changed && no > 0) {
+    bool identity = true;
+    for (int64_t k = 0; k < no; k++)
+      if (old_to_new[k] != (uint32_t)k) { identity = false; break; }
+    if (!identity || w != dm.width) reencode_segments(ds, di, identity ? nullptr : &old_to_new, w);
+    if (dm.hll_lut) { cudaFree(dm.hll_lut); dm.hll_lut = nullptr; dm.hll_lut_card = 0; }
+  }
+  dm.dict = std::make_shared<Dictionary>(std::move(merged));
+  dm.cardinality = dm.dict->size();
+  dm.width = w;
+  if (code_to_id) code_to_id->swap(c2i);
+}
+
+// Make a dimension's id space at least as large as asked: merge `values` into a string dictionary, or
+// raise an integer dimension's cardinality.  Used to align shards that live in different engines.
+void Store::extend_dimension(const std::string& name, const std::string& dim, const Dictionary* values, int64_t min_cardinality) {
+  auto ds = get(name);
+  std::unique_lock<std::shared_mutex> lk(ds->mu);
+  if (device_ >= 0) SDO_CUDA(cudaSetDevice(device_));
+  int di = ds->dim_index(dim);
+  if (di < 0) throw NotFound("unknown dimension '" + dim + "' in datasource '" + name + "'");
+  DimMeta& dm = ds->dims[di];
+  if (dm.enc == DimEncoding::Dict) {
+    if (values && values->size() > 0) merge_dictionary(*ds, di, *values, nullptr);
+  } else {
+    if (min_cardinality > 4294967295ll) throw Unsupported("integer dimension cardinality beyond 2^32 - 1");
+    if (min_cardinality > dm.cardinality) {
+      dm.cardinality = min_cardinality;
+      int w = width_for(dm.cardinality);
+      if (w > dm.width) { reencode_segments(*ds, di, nullptr, w); dm.width = w; }
+    }
+  }
+}
+
+std::shared_ptr<Dictionary> Store::dictionary(const std::string& name, const std::string& dim) const {
+  auto ds = get(name);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  int di = ds->dim_index(dim);
+  if (di < 0) throw NotFound("unknown dimension '" + dim + "' in datasource '" + name + "'");
+  return ds->dims[di].dict;
+}
+
 void Store::load(const std::string& name, int64_t n_rows, const std::vector<LoadColumn>& cols, int partition) {
   auto ds = get(name);
   std::unique_lock<std::shared_mutex> lk(ds->mu);
@@ -223,35 +331,6 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
     std::vector<uint32_t> code_to_id;   // Dict
   };
   std::vector<DimLoad> dloads;
-  auto reencode_existing = [&](int di, const std::vector<uint32_t>* lut, int new_width) {
-    DimMeta& dm = ds->dims[di];
-    (void)dm;
-    if (!dev) {
-      for (auto& s : ds->segments)
-        if ((int)s->dim_width.size() > di) s->dim_width[di] = new_width;
-      return;
-    }
-    std::unique_ptr<DevBuf> dl;
-    if (lut) {
-      dl.reset(new DevBuf(lut->size() * 4));
-      SDO_CUDA(cudaMemcpy(dl->p, lut->data(), lut->size() * 4, cudaMemcpyHostToDevice));
-    }
-    for (auto& s : ds->segments) {
-      if ((int)s->dim_data.size() <= di || !s->dim_data[di]) continue;
-      int ow = s->dim_width[di];
-      void* nb = nullptr;
-      SDO_CUDA(cudaMalloc(&nb, padded_bytes(s->n_rows, new_width)));
-      SDO_CUDA(cudaMemset(nb, 0, padded_bytes(s->n_rows, new_width)));
-      launch_reencode(s->dim_data[di], ow, nb, new_width, s->n_rows, dl ? (const uint32_t*)dl->p : nullptr, 0);
-      SDO_CUDA(cudaDeviceSynchronize());
-      s->device_bytes += padded_bytes(s->n_rows, new_width);
-      s->device_bytes -= padded_bytes(s->n_rows, ow);
-      cudaFree(s->dim_data[di]);
-      s->dim_data[di] = nb;
-      s->dim_width[di] = new_width;
-    }
-  };
-
   for (auto& c : cols) {
     if (c.kind != 1) continue;
     if (!c.data) throw Invalid("dimension '" + c.name + "' has no data");
@@ -285,7 +364,7 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
       if (mn < 0 || mx >= 4294967295ll) throw Unsupported("integer dimension '" + c.name + "' has values outside [0, 2^32-2]");
       dm.cardinality = std::max(dm.cardinality, mx + 1);
       int w = width_for(dm.cardinality);
-      if (w > dm.width) { reencode_existing(di, nullptr, w); dm.width = w; }
+      if (w > dm.width) { reencode_segments(*ds, di, nullptr, w); dm.width = w; }
     } else {
       // batch dictionary
       Dictionary bd;
@@ -309,50 +388,7 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
           dl.owned_codes[i] = it->second;
         }
       }
-      // merged, sorted, de-duplicated dictionary
-      const Dictionary& od = *dm.dict;
-      int64_t nb = bd.size(), no = od.size();
-      std::vector<int64_t> border((size_t)nb);
-      std::iota(border.begin(), border.end(), 0);
-      std::sort(border.begin(), border.end(), [&](int64_t a, int64_t b) { return utf8_cmp(bd.data(a), bd.len(a), bd.data(b), bd.len(b)) < 0; });
-      Dictionary merged;
-      std::vector<uint32_t> old_to_new((size_t)no);
-      dl.code_to_id.assign((size_t)nb, 0);
-      int64_t i = 0, j = 0;
-      while (i < no || j < nb) {
-        int cmp;
-        if (i >= no) cmp = 1;
-        else if (j >= nb) cmp = -1;
-        else cmp = utf8_cmp(od.data(i), od.len(i), bd.data(border[j]), bd.len(border[j]));
-        uint32_t id = (uint32_t)merged.size();
-        if (cmp < 0) { merged.push(od.data(i), od.len(i)); old_to_new[i++] = id; }
-        else if (cmp > 0) {
-          const char* p = bd.data(border[j]);
-          size_t n = bd.len(border[j]);
-          merged.push(p, n);
-          dl.code_to_id[border[j++]] = id;
-          // duplicates inside the batch dictionary map to the same id
-          while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) dl.code_to_id[border[j++]] = id;
-        } else {
-          merged.push(od.data(i), od.len(i));
-          old_to_new[i++] = id;
-          const char* p = merged.data(id);
-          size_t n = merged.len(id);
-          while (j < nb && utf8_cmp(bd.data(border[j]), bd.len(border[j]), p, n) == 0) dl.code_to_id[border[j++]] = id;
-        }
-      }
-      bool changed = merged.size() != no;
-      int w = std::max(dm.width, width_for(merged.size()));
-      if (changed && no > 0) {
-        bool identity = true;
-        for (int64_t k = 0; k < no; k++)
-          if (old_to_new[k] != (uint32_t)k) { identity = false; break; }
-        if (!identity || w != dm.width) reencode_existing(di, identity ? nullptr : &old_to_new, w);
-        if (dm.hll_lut) { cudaFree(dm.hll_lut); dm.hll_lut = nullptr; dm.hll_lut_card = 0; }
-      }
-      dm.dict = std::make_shared<Dictionary>(std::move(merged));
-      dm.cardinality = dm.dict->size();
-      dm.width = w;
+      merge_dictionary(*ds, di, bd, &dl.code_to_id);
     }
     dloads.push_back(std::move(dl));
   }
@@ -511,7 +547,9 @@ std::string Store::metadata_json(const std::string& name) const {
   json_escape(o, ds->query_granularity);
   o += ",\"segmentGranularity\":";
   json_escape(o, ds->segment_granularity);
-  if (lo <= hi) o += ",\"timeBoundary\":{\"minTime\":\"" + format_iso_instant(lo) + "\",\"maxTime\":\"" + format_iso_instant(hi) + "\"}";
+  if (lo <= hi)
+    o += ",\"timeBoundary\":{\"minTime\":\"" + format_iso_instant(lo) + "\",\"maxTime\":\"" + format_iso_instant(hi) + "\",\"minMs\":" + std::to_string((long long)lo) +
+         ",\"maxMs\":" + std::to_string((long long)hi) + "}";
   o += "}";
   return o;
 }

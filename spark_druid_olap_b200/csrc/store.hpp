@@ -111,6 +111,8 @@ class Store {
   std::shared_ptr<DataSource> get(const std::string& name) const;
   std::string metadata_json(const std::string& name) const;
   std::string segments_json(const std::string& name) const;
+  void extend_dimension(const std::string& name, const std::string& dim, const Dictionary* values, int64_t min_cardinality);
+  std::shared_ptr<Dictionary> dictionary(const std::string& name, const std::string& dim) const;
   int device() const { return device_; }
 
  private:
@@ -118,6 +120,8 @@ class Store {
   mutable std::mutex mu_;
   std::map<std::string, std::shared_ptr<DataSource>> sources_;
   void free_segment(Segment& s);
+  void reencode_segments(DataSource& ds, int di, const std::vector<uint32_t>* lut, int new_width);
+  void merge_dictionary(DataSource& ds, int di, const Dictionary& bd, std::vector<uint32_t>* code_to_id);
 };
 
 int64_t truncate_time(const std::string& gran, int64_t t);

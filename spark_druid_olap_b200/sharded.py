@@ -13,6 +13,8 @@ merged into the owner's hash table; every rank then finishes its disjoint share.
 The tensor-level functions work on any device/backend (the CPU tests drive them over gloo);
 execute_sharded binds them to an engine's device buffers without copies.
 """
+import json
+
 import torch
 import torch.distributed as dist
 
@@ -72,12 +74,76 @@ def exchange_sparse(keys, slots, counts, group=None):
     return rkeys, rslots
 
 
-def execute_sharded(engine, query, group=None, root=0):
+_boundary_cache = {}
+_aligned = set()
+
+
+def align_datasource(engine, datasource, group=None, force=False):
+    """Give every rank's shard of `datasource` the same id space: string dimensions get the union of all
+    ranks' dictionaries (device re-encode where ids move), integer dimensions the largest cardinality.
+    Packed group keys, dense table shapes and HLL lookup tables then mean the same thing on every rank.
+    Done once per engine and datasource; call again with force=True after loading more segments."""
+    key = (id(engine), datasource)
+    if key in _aligned and not force:
+        return
+    world = dist.get_world_size(group)
+    md = engine.metadata(datasource)
+    dims = sorted(n for n, c in md["columns"].items() if c["type"] == "STRING")
+    names = [None] * world
+    dist.all_gather_object(names, dims, group=group)
+    if any(n != dims for n in names):
+        raise ValueError(f"ranks disagree on the dimensions of {datasource}: {names}")
+    for d in dims:
+        values, card = engine.dimension_dictionary(datasource, d)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (values, card), group=group)
+        union = set()
+        for v, _ in gathered:
+            union.update(v)
+        extra = sorted(union.difference(values))
+        engine.extend_dimension(datasource, d, extra, max(c for _, c in gathered) if not union else 0)
+    _aligned.add(key)
+    _boundary_cache.pop(key, None)
+
+
+def global_time_boundary(engine, datasource, group=None):
+    """[min_ms, max_ms] of the datasource over all ranks (cached per engine and datasource).
+    Time-derived group keys are numbered on this grid so that every rank uses the same key space."""
+    key = (id(engine), datasource)
+    if key not in _boundary_cache:
+        tb = engine.metadata(datasource).get("timeBoundary")
+        lo, hi = (tb["minMs"], tb["maxMs"]) if tb else (2 ** 62, -2 ** 62)
+        dev = torch.device("cuda", engine.device) if engine.device >= 0 else torch.device("cpu")
+        t = torch.tensor([-lo, hi], dtype=torch.int64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+        _boundary_cache[key] = (-int(t[0]), int(t[1]))
+    return _boundary_cache[key]
+
+
+def with_time_boundary(query, boundary):
+    """The query as a dict with context.gpuTimeBoundary set."""
+    if hasattr(query, "to_json"):
+        query = json.loads(query.to_json())
+    elif isinstance(query, (bytes, str)):
+        query = json.loads(query)
+    else:
+        query = dict(query)
+    ctx = dict(query.get("context") or {})
+    ctx["gpuTimeBoundary"] = [int(boundary[0]), int(boundary[1])]
+    query["context"] = ctx
+    return query
+
+
+def execute_sharded(engine, query, group=None, root=0, force_exchange=False):
     """Run `query` over every rank's local segments and return the merged Result on `root`
     (dense key spaces) or this rank's share of the groups (sparse key spaces; see `sparse` flag).
     Returns (result_or_None, info)."""
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
+    if world > 1:
+        q = with_time_boundary(query, (0, 0))
+        align_datasource(engine, q["dataSource"], group)
+        query = with_time_boundary(q, global_time_boundary(engine, q["dataSource"], group))
     part = engine.partial(query)
     try:
         v = part.view()
@@ -101,7 +167,8 @@ def execute_sharded(engine, query, group=None, root=0):
                     return part.finish(), info
                 return None, info
             # sparse: hash-partitioned all-to-all, every rank keeps the groups it owns
-            if world > 1:
+            # (force_exchange runs the partition / exchange / merge steps even on one rank: tests)
+            if world > 1 or force_exchange:
                 counts = part.partition(world)
                 v = part.view()
                 n = int(v.n_keys)

@@ -260,3 +260,38 @@ def test_unsorted_string_load_and_incremental_dictionary(gpu_engine):
         H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), orc.execute(tbl_trunc, qd))
     finally:
         gpu_engine.drop_datasource(name)
+
+
+def test_extend_dimension_keeps_results(gpu_engine):
+    """Aligning shards across engines: merging foreign values into a dictionary (ids move, width may grow) and raising an
+    integer dimension's cardinality must not change any result -- only the id space."""
+    from spark_druid_olap_b200 import tpch
+    name = "tpch_extend"
+    try:
+        gpu_engine.drop_datasource(name)
+    except Exception:
+        pass
+    tabs = tpch.load_into(gpu_engine, name, 0.01, ["s_nation", "l_shipmode", "o_orderkey", "l_extendedprice", "o_custkey", "count"], keep=True)
+    tbl = H.oracle_table(tabs)
+    try:
+        q = Q.GroupByQuerySpec(name, [Q.DefaultDimensionSpec("s_nation"), Q.DefaultDimensionSpec("l_shipmode")], None, None, "all",
+                               Q.BoundFilterSpec("s_nation", lower="C", lowerStrict=False),
+                               [Q.agg("count", "n", "count"), Q.agg("doubleSum", "p", "l_extendedprice"), Q.CardinalityAggregationSpec("dn", ["s_nation"]),
+                                Q.CardinalityAggregationSpec("dc", ["o_custkey"])], None, Q.ALL_TIME)
+        q2 = Q.GroupByQuerySpec(name, [Q.DefaultDimensionSpec("o_orderkey")], None, None, "all", None, [Q.agg("count", "n", "count")], None, Q.ALL_TIME)
+        want, want2 = orc.execute(tbl, json.loads(q.to_json())), orc.execute(tbl, json.loads(q2.to_json()))
+        H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), want)
+        before = gpu_engine.explain(q)["keySpace"], gpu_engine.explain(q2)["keySpace"]
+        vals, card = gpu_engine.dimension_dictionary(name, "s_nation")
+        assert len(vals) == card == 25 and vals == sorted(vals, key=lambda s: s.encode())
+        extra = ["AARDVARK LAND", "", "MIDDLE KINGDOM", "ZZ TOP"] + [f"FILLER {i:04d}" for i in range(300)]  # ids move and the width grows to 2 bytes
+        gpu_engine.extend_dimension(name, "s_nation", extra)
+        gpu_engine.extend_dimension(name, "o_orderkey", min_cardinality=5_000_000)
+        assert gpu_engine.dimension_dictionary(name, "o_orderkey") == ([], 5_000_000)
+        assert gpu_engine.metadata(name)["columns"]["s_nation"]["cardinality"] == 25 + len(extra)
+        after = gpu_engine.explain(q)["keySpace"], gpu_engine.explain(q2)["keySpace"]
+        assert after[0] > before[0] and after[1] == 5_000_000
+        H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), want)
+        H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q2)), want2)
+    finally:
+        gpu_engine.drop_datasource(name)

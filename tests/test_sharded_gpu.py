@@ -55,3 +55,36 @@ def test_sharded_equals_oracle_world1(dist_engine, mk, ordered):
     want = orc.execute(tbl, q)
     H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered)
     assert info["dense"] == (res.stats["strategy"] != "hash")
+
+
+def test_time_keys_are_numbered_on_the_global_grid(dist_engine):
+    """With context.gpuTimeBoundary (set by the sharded layer) the time-key space comes from the datasource's time grid,
+    not from the days this rank happens to hold -- so all ranks build tables of the same shape."""
+    from spark_druid_olap_b200 import sharded
+    eng, tbl, name = dist_engine
+    day = 86400000
+    lo, hi = int(tbl.time.min()) - 40 * day, int(tbl.time.max()) + 75 * day  # other ranks hold earlier and later days
+    for spec in (Q.timeseries("P1D"), Q.timeseries("P1M"), Q.q7()):
+        q = sharded.with_time_boundary(_with_ds(spec, name), (lo, hi))
+        if spec.queryType == "groupBy":
+            q["filter"] = None
+            q["dimensions"] = q["dimensions"][2:]  # just the year(l_shipdate) extraction
+            del q["filter"]
+        plain = dict(q, context={})
+        e_grid, e_local = eng.explain(q), eng.explain(plain)
+        assert e_grid["timeKeys"] >= e_local["timeKeys"]
+        H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, plain))
+    q = sharded.with_time_boundary(_with_ds(Q.timeseries("P1D"), name), (lo, hi))
+    a, b = orc.parse_interval(Q.ALL_TIME[0])  # the grid is clipped by the query interval
+    assert eng.explain(q)["timeKeys"] == (min(hi, b - day) - max(lo, a)) // day + 1
+
+
+@pytest.mark.parametrize("mk,ordered", [(lambda: Q.by_orderkey("hash"), False), (lambda: Q.q3(), False), (lambda: Q.q3(10), True)])
+def test_sparse_partition_exchange_merge_on_one_rank(dist_engine, mk, ordered):
+    """The sparse path's device steps (split rows by owner, all-to-all, merge received rows) with a single owner."""
+    from spark_druid_olap_b200 import sharded
+    eng, tbl, name = dist_engine
+    q = _with_ds(mk(), name)
+    res, info = sharded.execute_sharded(eng, q, force_exchange=True)
+    assert not info["dense"]
+    H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, q), ordered=ordered)

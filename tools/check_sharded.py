@@ -45,9 +45,15 @@ for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style
         else:
             # sparse: every rank holds a disjoint share; gather and compare the union
             parts = [None] * world
-            dist.all_gather_object(parts, H.engine_rows(res))
+            rows_here = H.engine_rows(res)
+            cnt_col = [k for k in rows_here[0] if k in ('n',)] if rows_here else []
+            print(f'[rank {rank}] {name}: {len(rows_here)} result rows, sum n = {sum(r[cnt_col[0]] for r in rows_here) if cnt_col else None}, local rows {mine.n_rows}, info {info}', flush=True)
+            dist.all_gather_object(parts, rows_here)
             if rank == 0:
-                H.assert_rows_equal([r for p in parts for r in p], want, what=name)
+                allrows = [r for p in parts for r in p]
+                keys = [r.get('o_orderkey') for r in allrows]
+                print(f'union {len(allrows)} rows, distinct keys {len(set(keys))}, want {len(want)}', flush=True)
+                H.assert_rows_equal(allrows, want, what=name)
         if rank == 0:
             print(f"OK   {name:22s} dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
     except AssertionError as e:
