@@ -15,8 +15,8 @@ CSRC = os.path.join(HERE, "csrc")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
-ENGINE_SRCS = ["kernels.cu", "noalloc.cu", "spec.cpp", "store.cpp", "plan.cpp", "engine.cpp", "capi.cpp"]
-ENGINE_HDRS = ["scan_unit.cuh", "common.hpp", "json.hpp", "timeutil.hpp", "spec.hpp", "store.hpp", "plan.hpp", "kernels.hpp",
+ENGINE_SRCS = ["kernels.cu", "noalloc.cu", "jit.cpp", "spec.cpp", "store.cpp", "plan.cpp", "engine.cpp", "capi.cpp"]
+ENGINE_HDRS = ["scan_kernel.cuh", "jit.hpp", "common.hpp", "json.hpp", "timeutil.hpp", "spec.hpp", "store.hpp", "plan.hpp", "kernels.hpp",
                "engine.hpp", "xxh64.hpp", os.path.join("..", "..", "include", "sdo_engine.h")]
 ENGINE_LIB = os.path.join(HERE, "libsdo_engine.so")
 GEN_LIB = os.path.join(HERE, "libsdo_tpchgen.so")
@@ -59,7 +59,7 @@ def build_engine(force=False, verbose=False):
         if verbose and out.strip():
             print(out)
     if force or procs or _newer(ENGINE_LIB, objs):
-        _run([NVCC, "-shared", "-o", ENGINE_LIB] + objs + ARCH + ["-cudart", "static", "-Xlinker", "--no-undefined", "-lpthread"])
+        _run([NVCC, "-shared", "-o", ENGINE_LIB] + objs + ARCH + ["-cudart", "static", "-Xlinker", "--no-undefined", "-lpthread", "-ldl"])
     return ENGINE_LIB
 
 

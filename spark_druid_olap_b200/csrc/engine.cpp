@@ -7,6 +7,7 @@
 #include <numeric>
 
 #include "../../include/sdo_engine.h"
+#include "jit.hpp"
 #include "xxh64.hpp"
 
 namespace sdo {
@@ -288,7 +289,22 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
     else if (plan.dev_dims.empty() && (size_t)plan.n_hll * HLL_M + smem <= 200 * 1024) p.hll_mode = HLL_IN_SMEM_SPAN;
     smem += scan_hll_smem_bytes(p.hll_mode, plan.n_keys, plan.n_hll);
   }
-  int grid = scan_grid_size(strat, smem, sm_count_);
+  // run-time specialised kernel for this query shape (large scans, or when the query asks for it)
+  const JitKernel* jk = nullptr;
+  {
+    static const char* env = getenv("SDO_JIT");
+    const bool env_off = env && env[0] == '0', env_on = env && env[0] == '1';
+    bool want = plan.spec.gpu_jit > 0 || (plan.spec.gpu_jit < 0 && !env_off && (env_on || plan.rows_scanned >= opt_.jit_min_rows));
+    if (want) {
+      double ms = 0;
+      jk = jit_get(strat, p, &ms);
+      st->jit_compile_ms = ms;
+    }
+  }
+  st->jit = jk != nullptr;
+  int grid = 0;
+  if (jk) grid = jit_blocks_per_sm(jk, smem) * sm_count_;
+  if (grid <= 0) { jk = nullptr; st->jit = false; grid = scan_grid_size(strat, smem, sm_count_); }
   const uint32_t n_chunks = (plan.n_units + p.units_per_chunk - 1) / p.units_per_chunk;
   grid = (int)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid, n_chunks));
   if (strat == STRAT_LANE) {
@@ -296,7 +312,10 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
     p.table = st->partials;
   }
   SDO_CUDA(cudaEventRecord(ctx->ev[1], s));
-  launch_scan(strat, p, grid, smem, s);
+  if (!jk || !jit_launch(jk, p, grid, smem, s)) {
+    st->jit = false;
+    launch_scan(strat, p, grid, smem, s);
+  }
   SDO_CUDA(cudaEventRecord(ctx->ev[2], s));
   st->launches += 1;
   if (strat == STRAT_LANE) {
@@ -759,11 +778,11 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   snprintf(buf, sizeof buf,
            "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
            "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
-           "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":%s,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu}",
+           "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":%s,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu,\"jit\":%s,\"jitCompileMs\":%.3f}",
            plan.always_false ? "none" : strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row,
            (long long)plan.algorithmic_bytes, (unsigned long long)n, (unsigned long long)m, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms,
            st->launches, st->h2d_bytes, st->d2h_bytes, device_topk ? "true" : "false", plan.spans.size(), plan.seg_index.size(),
-           (unsigned long long)plan.n_keys);
+           (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms);
   res->stats = buf;
   return res.release();
 }

@@ -56,6 +56,8 @@ struct ScanState {
   int launches = 0;
   size_t h2d_bytes = 0, d2h_bytes = 0;
   float scan_ms = 0;
+  bool jit = false;           // the scan ran on a run-time specialised kernel
+  double jit_compile_ms = 0;  // > 0 when this query paid for the compilation
   // sparse rows after compaction / merging (multi-GPU)
   unsigned long long* rows_keys = nullptr;
   unsigned long long* rows_slots = nullptr;

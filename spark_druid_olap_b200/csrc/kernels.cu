@@ -1,364 +1,23 @@
-// CUDA kernels of the OLAP-index hot path (sm_100a): fused scan -> filter -> group-by aggregate
-// over dictionary-encoded segment columns, plus the small kernels around it (loader encode,
-// partial reduction, compaction, top-k, HLL lookup tables, multi-GPU partition/merge).
-//
-// What these replace: the per-segment work of a Druid historical behind
-// DruidClient.performQuery (/root/reference/src/main/scala/org/sparklinedata/druid/client/
-// DruidClient.scala:228-285): bitmap-index filter -> cursor -> per-row dictionary-id key ->
-// BufferAggregator.aggregate -> merge ("hot loop on the Druid side").
-//
-// Shape of the scan kernel (all strategies):
-//   * persistent grid, blocks pull chunks of units (1 unit = 1024 rows = 256 threads x 4 rows)
-//     from an atomic ticket; a unit never crosses a span, spans never cross segments;
-//   * a thread owns 4 consecutive rows, so it loads a 1-byte id column with one 32-bit load,
-//     a 2-byte one with one 64-bit load, a 4-byte one with one 128-bit load and an 8-byte
-//     metric with two 128-bit loads -- one 32-byte DRAM sector per metric per thread, skipped
-//     entirely when none of its 4 rows passes the filter;
-//   * the filter is a postfix program over leaf masks (4 bits per thread), evaluated on a
-//     bit-packed stack held in one register;
-//   * the key is span.key_base + sum(id_d * stride_d);
-//   * aggregation: STRAT_LANE  lane-private accumulators in shared memory (no atomics, fixed
-//                              reduction order => bit-reproducible sums),
-//                  STRAT_BLOCK block-shared table in shared memory, shared atomics, flushed once,
-//                  STRAT_GLOBAL direct-indexed table in HBM, global atomics,
-//                  STRAT_HASH  open-addressing table in HBM, atomicCAS claim + global atomics.
+// CUDA kernels of the OLAP-index hot path (sm_100a).  The fused scan -> filter -> group-by aggregate
+// kernel lives in scan_kernel.cuh (shared with the run-time specialiser, jit.cpp); this file instantiates
+// its ahead-of-time (interpreting) variants and holds the small kernels around it: table initialisation,
+// partial reduction, compaction of occupied groups, top-k, HLL gather, loader encode / re-encode,
+// multi-GPU partition / merge.
+#include <algorithm>
 #include <cstdio>
 
 #include "common.hpp"
 #include "kernels.hpp"
+#include "scan_kernel.cuh"
 #include "xxh64.hpp"
 
 namespace sdo {
 
-// ---------------------------------------------------------------------------------------------
-// small device helpers
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void load_ids4(const void* base, int width, uint32_t r0, uint32_t (&out)[4]) {
-  if (width == 1) {
-    uint32_t w = __ldcs((const uint32_t*)((const uint8_t*)base + r0));
-    out[0] = w & 0xffu; out[1] = (w >> 8) & 0xffu; out[2] = (w >> 16) & 0xffu; out[3] = w >> 24;
-  } else if (width == 2) {
-    uint2 w = __ldcs((const uint2*)((const uint16_t*)base + r0));
-    out[0] = w.x & 0xffffu; out[1] = w.x >> 16; out[2] = w.y & 0xffffu; out[3] = w.y >> 16;
-  } else {
-    uint4 w = __ldcs((const uint4*)((const uint32_t*)base + r0));
-    out[0] = w.x; out[1] = w.y; out[2] = w.z; out[3] = w.w;
-  }
-}
-__device__ __forceinline__ void load_f64x4(const void* base, uint32_t r0, double (&v)[4]) {
-  const double2* p = (const double2*)((const double*)base + r0);
-  double2 a = __ldcs(p), b = __ldcs(p + 1);
-  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-}
-__device__ __forceinline__ void load_i64x4(const void* base, uint32_t r0, long long (&v)[4]) {
-  const longlong2* p = (const longlong2*)((const long long*)base + r0);
-  longlong2 a = __ldcs(p), b = __ldcs(p + 1);
-  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
-}
-// order-preserving map double <-> int64 (its own inverse)
 __host__ __device__ __forceinline__ long long f64_ord(long long bits) { return bits ^ ((bits >> 63) & 0x7FFFFFFFFFFFFFFFll); }
-__device__ __forceinline__ long long f64_to_ord(double d) { return f64_ord(__double_as_longlong(d)); }
-
-__device__ __forceinline__ uint64_t mix64(uint64_t x) {
-  x ^= x >> 33;
-  x *= 0xff51afd7ed558ccdull;
-  x ^= x >> 33;
-  x *= 0xc4ceb9fe1a85ec53ull;
-  x ^= x >> 33;
-  return x;
-}
-
-__device__ __forceinline__ uint32_t leaf_mask(const DevLeaf& lf, const void* const* cols, uint32_t r0) {
-  uint32_t ids[4];
-  load_ids4(cols[lf.col], lf.width, r0, ids);
-  uint32_t m = 0;
-  if (lf.kind == LEAF_RANGE) {
-    const uint32_t lo = lf.lo, span = lf.hi - lf.lo;
-#pragma unroll
-    for (int i = 0; i < 4; i++) m |= (uint32_t)((ids[i] - lo) < span) << i;
-  } else {
-    const uint32_t* bits = lf.bits;
-#pragma unroll
-    for (int i = 0; i < 4; i++) m |= ((__ldg(bits + (ids[i] >> 5)) >> (ids[i] & 31)) & 1u) << i;
-  }
-  return m;
-}
-
-__device__ __forceinline__ uint32_t eval_filter(const ScanParams& p, const void* const* cols, uint32_t r0) {
-  uint64_t st = 0;  // stack of 4-bit masks, top in the low nibble
-  const int n = p.n_ops;
-  for (int k = 0; k < n; k++) {
-    const uint32_t op = p.op_code[k];
-    if (op == FOP_LEAF) {
-      st = (st << 4) | leaf_mask(p.leaves[p.op_arg[k]], cols, r0);
-    } else if (op == FOP_AND) {
-      uint64_t a = st & 0xF;
-      st >>= 4;
-      st = (st & ~0xFull) | (st & a);
-    } else if (op == FOP_OR) {
-      uint64_t a = st & 0xF;
-      st >>= 4;
-      st |= a;
-    } else if (op == FOP_NOT) {
-      st ^= 0xF;
-    } else if (op == FOP_TRUE) {
-      st = (st << 4) | 0xF;
-    } else {
-      st = st << 4;
-    }
-  }
-  return (uint32_t)(st & 0xF);
-}
-
-// HLL++ register update: byte registers packed 4 per word; plain read first (most updates are
-// no-ops once a register has warmed up), compare-and-swap on the word only when it must grow.
-__device__ __forceinline__ void hll_update(uint8_t* regs, uint32_t packed) {
-  const uint32_t idx = packed >> 6, rho = packed & 63u;
-  if (regs[idx] >= rho) return;
-  unsigned int* word = (unsigned int*)(regs + (idx & ~3u));
-  const int sh = (idx & 3u) * 8;
-  unsigned int old = *(volatile unsigned int*)word;
-  for (;;) {
-    if (((old >> sh) & 0xffu) >= rho) return;
-    unsigned int nw = (old & ~(0xffu << sh)) | (rho << sh);
-    unsigned int prev = atomicCAS(word, old, nw);
-    if (prev == old) return;
-    old = prev;
-  }
-}
-// same update on a shared-memory sketch
-__device__ __forceinline__ void hll_update_sm(unsigned int* words, uint32_t packed) {
-  const uint32_t idx = packed >> 6, rho = packed & 63u;
-  unsigned int* word = words + (idx >> 2);
-  const int sh = (idx & 3u) * 8;
-  unsigned int old = *(volatile unsigned int*)word;
-  for (;;) {
-    if (((old >> sh) & 0xffu) >= rho) return;
-    unsigned int nw = (old & ~(0xffu << sh)) | (rho << sh);
-    unsigned int prev = atomicCAS(word, old, nw);
-    if (prev == old) return;
-    old = prev;
-  }
-}
-// merge `n_words` shared-memory sketch words into the HBM registers (byte-wise max) and clear them
-__device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned int* global_words, uint32_t n_words) {
-  for (uint32_t w = threadIdx.x; w < n_words; w += SCAN_THREADS) {
-    const unsigned int mine = sm_words[w];
-    if (!mine) continue;
-    sm_words[w] = 0u;
-    unsigned int old = *(volatile unsigned int*)(global_words + w);
-    for (;;) {
-      const unsigned int nw = __vmaxu4(old, mine);
-      if (nw == old) break;
-      const unsigned int prev = atomicCAS(global_words + w, old, nw);
-      if (prev == old) break;
-      old = prev;
-    }
-  }
-}
-__device__ __forceinline__ uint32_t hll_value(const DevAgg& a, uint32_t id) {
-  if (a.hll_mode == HLL_LUT) return __ldg(a.hll_lut + id);
-  if (a.hll_mode == HLL_DIRECT_INT) return hll_pack(xxh64_int((int32_t)id, HLL_SEED));
-  return hll_pack(xxh64_long((int64_t)id, HLL_SEED));
-}
-
-// ---------------------------------------------------------------------------------------------
-// accumulation policies
-// ---------------------------------------------------------------------------------------------
-template <int STRAT>
-struct Acc;
-
-template <>
-struct Acc<STRAT_LANE> {
-  typedef uint32_t key_t;
-  unsigned long long* base;  // smem + tid
-  int ns;
-  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
-  static constexpr int SLOT_STRIDE = SCAN_THREADS;  // elements between consecutive slots of one group
-  __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)(g * ns + slot) * SCAN_THREADS; }
-  // a thread's own count stays far below 2^32: bump the low word only
-  __device__ __forceinline__ void count1(unsigned long long* q) const { *(unsigned int*)q += 1u; }
-  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { *(unsigned int*)q += (unsigned int)c; }
-  __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { *q += (unsigned long long)v; }
-  __device__ __forceinline__ void add_f64(unsigned long long* q, double v) const { *(double*)q += v; }
-  __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v < c) *(long long*)q = v; }
-  __device__ __forceinline__ void max_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v > c) *(long long*)q = v; }
-};
-// shared-memory or global atomics; the pointer's address space is visible after inlining
-struct AtomicOps {
-  __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { atomicAdd(q, (unsigned long long)v); }
-  __device__ __forceinline__ void add_f64(unsigned long long* q, double v) const { atomicAdd((double*)q, v); }
-  __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { atomicMin((long long*)q, v); }
-  __device__ __forceinline__ void max_i64(unsigned long long* q, long long v) const { atomicMax((long long*)q, v); }
-};
-template <>
-struct Acc<STRAT_BLOCK> : AtomicOps {
-  typedef uint32_t key_t;
-  unsigned long long* base;  // smem table
-  int ns;
-  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
-  static constexpr int SLOT_STRIDE = 1;
-  __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + (size_t)g * ns + slot; }
-  // one launch scans fewer than 2^32 rows (checked on the host), so a block's count fits the low
-  // word: a native 32-bit shared atomic instead of the 64-bit compare-and-swap loop
-  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd((unsigned int*)q, 1u); }
-  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd((unsigned int*)q, (unsigned int)c); }
-};
-template <>
-struct Acc<STRAT_GLOBAL> : AtomicOps {
-  typedef uint64_t key_t;
-  unsigned long long* base;
-  int ns;
-  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
-  static constexpr int SLOT_STRIDE = 1;
-  __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
-  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
-  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd(q, (unsigned long long)c); }
-};
-template <>
-struct Acc<STRAT_HASH> : AtomicOps {
-  typedef uint64_t key_t;
-  unsigned long long* base;
-  int ns;
-  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
-  static constexpr int SLOT_STRIDE = 1;
-  __device__ __forceinline__ unsigned long long* at(key_t g, int slot) const { return base + g * (uint64_t)ns + slot; }
-  __device__ __forceinline__ void count1(unsigned long long* q) const { atomicAdd(q, 1ull); }
-  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd(q, (unsigned long long)c); }
-};
-
-// find-or-claim the slot of `key` (linear probing).  Returns HASH_EMPTY if the table is full.
-__device__ __forceinline__ uint64_t hash_claim(unsigned long long* hkeys, uint64_t mask, uint64_t key) {
-  uint64_t h = mix64(key) & mask;
-  for (uint64_t probes = 0; probes <= mask; probes++) {
-    unsigned long long cur = *(volatile unsigned long long*)(hkeys + h);
-    if (cur == key) return h;
-    if (cur == HASH_EMPTY) {
-      unsigned long long prev = atomicCAS(hkeys + h, HASH_EMPTY, (unsigned long long)key);
-      if (prev == HASH_EMPTY || prev == key) return h;
-    }
-    h = (h + 1) & mask;
-  }
-  return HASH_EMPTY;
-}
-
-// one unit of the scan (filter -> key -> aggregate over 4096 rows)
-#include "scan_unit.cuh"
-
-// coarse index over spans lives right after the sentinel span: see plan.cpp (layout of the
-// per-query device blob).  COARSE_UNITS units per coarse entry.
-constexpr uint32_t COARSE_UNITS = 64;
 
 template <int STRAT>
 __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse) {
-  extern __shared__ __align__(16) unsigned long long smem[];
-  __shared__ uint32_t s_chunk, s_span;
-  const int tid = threadIdx.x;
-  const int ns = p.n_slots;
-  Acc<STRAT> acc;
-  acc.ns = ns;
-  // shared-memory HLL sketches sit behind the aggregate table
-  const uint32_t hll_sm_words = p.hll_mode == HLL_IN_SMEM_ALL ? (uint32_t)p.n_keys * p.n_hll * (HLL_M / 4)
-                                : (p.hll_mode == HLL_IN_SMEM_SPAN ? (uint32_t)p.n_hll * (HLL_M / 4) : 0u);
-  {
-    size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS : (STRAT == STRAT_BLOCK ? (size_t)p.n_keys * ns : 0);
-    acc.hll_sm = (unsigned int*)(smem + table_words);
-    for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
-  }
-  uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (block-uniform)
-  if (STRAT == STRAT_LANE) {
-    const uint32_t n = (uint32_t)p.n_keys * ns;
-    for (uint32_t x = 0; x < n; x++) smem[(size_t)x * SCAN_THREADS + tid] = p.slot_init[x % ns];
-    acc.base = smem + tid;
-  } else if (STRAT == STRAT_BLOCK) {
-    const uint32_t n = (uint32_t)p.n_keys * ns;
-    for (uint32_t x = tid; x < n; x += SCAN_THREADS) smem[x] = p.slot_init[x % ns];
-    acc.base = smem;
-  } else {
-    acc.base = p.table;
-  }
-  __syncthreads();
-
-  for (;;) {
-    if (tid == 0) s_chunk = atomicAdd(&p.counters[0], 1u);
-    __syncthreads();
-    const uint32_t u0 = s_chunk * p.units_per_chunk;
-    if (u0 >= p.n_units) break;
-    const uint32_t u1 = min(p.n_units, u0 + p.units_per_chunk);
-    {
-      const uint32_t lo = coarse[u0 / COARSE_UNITS], hi = coarse[u0 / COARSE_UNITS + 1];
-      for (uint32_t s = lo + tid; s <= hi && s < p.n_spans; s += SCAN_THREADS)
-        if (p.spans[s].unit_begin <= u0 && u0 < p.spans[s + 1].unit_begin) s_span = s;
-    }
-    __syncthreads();
-    uint32_t s = s_span;
-    DevSpan sp = p.spans[s];
-    uint32_t next_begin = p.spans[s + 1].unit_begin;
-    for (uint32_t u = u0; u < u1; u++) {
-      while (u >= next_begin) {
-        s++;
-        sp = p.spans[s];
-        next_begin = p.spans[s + 1].unit_begin;
-      }
-      if (p.hll_mode == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
-        // the cached sketch belongs to another group: merge it into HBM, start an empty one
-        __syncthreads();
-        if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)p.n_hll * HLL_M), hll_sm_words);
-        hll_key = sp.key_base;
-        __syncthreads();
-      }
-      process_unit<STRAT>(p, sp, u - sp.unit_begin, acc);
-    }
-  }
-  if (hll_sm_words) {
-    __syncthreads();
-    if (p.hll_mode == HLL_IN_SMEM_ALL) hll_flush_sm(acc.hll_sm, (unsigned int*)p.hll, hll_sm_words);
-    else if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)p.n_hll * HLL_M), hll_sm_words);
-  }
-
-  if (STRAT == STRAT_LANE) {
-    // fixed-order reduction of the 256 lane-private copies: 8 strided values per lane, then a
-    // shuffle tree; one warp per (key, slot)
-    __syncthreads();
-    const uint32_t n = (uint32_t)p.n_keys * ns;
-    const int warp = tid >> 5, lane = tid & 31;
-    unsigned long long* out = p.table + (size_t)blockIdx.x * n;
-    for (uint32_t x = warp; x < n; x += SCAN_THREADS / 32) {
-      const unsigned long long* src = smem + (size_t)x * SCAN_THREADS;
-      const int op = p.slot_op[x % ns];
-      unsigned long long v = src[lane];
-#pragma unroll
-      for (int j = 1; j < SCAN_THREADS / 32; j++) {
-        unsigned long long w = src[lane + 32 * j];
-        if (op == SLOT_SUM_I64) v += w;
-        else if (op == SLOT_SUM_F64) v = __double_as_longlong(__longlong_as_double(v) + __longlong_as_double(w));
-        else if (op == SLOT_MIN_I64) v = (unsigned long long)min((long long)v, (long long)w);
-        else v = (unsigned long long)max((long long)v, (long long)w);
-      }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1) {
-        unsigned long long w = __shfl_down_sync(0xffffffffu, v, off);
-        if (op == SLOT_SUM_I64) v += w;
-        else if (op == SLOT_SUM_F64) v = __double_as_longlong(__longlong_as_double(v) + __longlong_as_double(w));
-        else if (op == SLOT_MIN_I64) v = (unsigned long long)min((long long)v, (long long)w);
-        else v = (unsigned long long)max((long long)v, (long long)w);
-      }
-      if (lane == 0) out[x] = v;
-    }
-  } else if (STRAT == STRAT_BLOCK) {
-    __syncthreads();
-    const uint32_t n = (uint32_t)p.n_keys * ns;
-    for (uint32_t x = tid; x < n; x += SCAN_THREADS) {
-      const unsigned long long v = smem[x];
-      const int sl = x % ns;
-      if (v == p.slot_init[sl]) continue;
-      const int op = p.slot_op[sl];
-      if (op == SLOT_SUM_I64) atomicAdd(p.table + x, v);
-      else if (op == SLOT_SUM_F64) atomicAdd((double*)(p.table + x), __longlong_as_double(v));
-      else if (op == SLOT_MIN_I64) atomicMin((long long*)(p.table + x), (long long)v);
-      else atomicMax((long long*)(p.table + x), (long long)v);
-    }
-  }
+  scan_body<STRAT>(p, coarse);
 }
 
 size_t scan_hll_smem_bytes(int hll_mode, uint64_t n_keys, int n_hll) {

@@ -1,8 +1,20 @@
 // Device-side contract of the scan / filter / aggregate kernels (kernels.cu) and their launchers.
 #pragma once
+#ifdef __CUDACC_RTC__
+// NVRTC (run-time specialisation): no host headers; fixed-width types by hand
+typedef unsigned char uint8_t;
+typedef unsigned short uint16_t;
+typedef unsigned int uint32_t;
+typedef unsigned long long uint64_t;
+typedef signed char int8_t;
+typedef short int16_t;
+typedef int int32_t;
+typedef long long int64_t;
+#else
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#endif
 
 namespace sdo {
 
@@ -117,6 +129,7 @@ struct ScanParams {
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 
+#ifndef __CUDACC_RTC__
 // ---- launchers (host) ---------------------------------------------------------------------------
 // loader helpers
 void launch_encode_dim(const void* src, bool src64, const int32_t* perm, int64_t r0, int64_t n, const uint32_t* lut,
@@ -155,5 +168,7 @@ void launch_partition_rows(const unsigned long long* keys, const unsigned long l
                            unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,
                            unsigned long long* cursors_dev, cudaStream_t st);
 void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
+
+#endif  // !__CUDACC_RTC__
 
 }  // namespace sdo

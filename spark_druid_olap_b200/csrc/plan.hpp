@@ -88,6 +88,7 @@ struct PlanOptions {
   uint64_t block_max_bytes = 160 * 1024;        // shared-memory table
   uint64_t global_max_keys = 1ull << 26;        // direct-indexed HBM table
   uint64_t hll_max_bytes = 8ull << 30;
+  int64_t jit_min_rows = 2000000;               // scans at least this long get a shape-specialised kernel
 };
 
 Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds, const PlanOptions& opt);

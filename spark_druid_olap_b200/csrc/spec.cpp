@@ -320,6 +320,7 @@ QuerySpec parse_query_spec(const Json& j) {
     q.query_id = c->get_str("queryId", "");
     q.skip_empty_buckets = c->get_bool("skipEmptyBuckets", true);
     q.gpu_strategy = c->get_str("gpuStrategy", "");
+    if (c->has("gpuJit")) q.gpu_jit = c->get_bool("gpuJit", false) ? 1 : 0;
     if (const Json* tb = c->find("gpuTimeBoundary")) {
       if (!tb->is_arr() || tb->arr.size() != 2 || !tb->arr[0].is_num() || !tb->arr[1].is_num()) throw Invalid("context.gpuTimeBoundary must be [minMs, maxMs]");
       q.has_time_boundary = true;

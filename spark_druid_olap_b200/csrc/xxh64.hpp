@@ -5,8 +5,10 @@
 // tests pin it to the public XXH64 test vectors.  Call sites in the reference:
 //   sources/druid/AggregateTransform.scala:454-479 (approx_count_distinct -> cardinality aggregator).
 #pragma once
+#ifndef __CUDACC_RTC__
 #include <cstddef>
 #include <cstdint>
+#endif
 
 #if defined(__CUDACC__)
 #define SDO_HD __host__ __device__ __forceinline__
