@@ -136,10 +136,10 @@ int sdo_result_column_get(const sdo_result* r, int i, sdo_result_column* out) {
   out->name = c.name.c_str();
   out->type = c.type;
   switch (c.type) {
-    case SDO_RES_INT64: case SDO_RES_DIM_INT64: case SDO_RES_TIMESTAMP: out->values = c.i64.data(); break;
-    case SDO_RES_FLOAT64: out->values = c.f64.data(); break;
+    case SDO_RES_INT64: case SDO_RES_DIM_INT64: case SDO_RES_TIMESTAMP: out->values = c.raw ? c.raw : (const void*)c.i64.data(); break;
+    case SDO_RES_FLOAT64: out->values = c.raw ? c.raw : (const void*)c.f64.data(); break;
     case SDO_RES_STRING:
-      out->values = c.ids.data();
+      out->values = c.raw ? c.raw : (const void*)c.ids.data();
       out->dict_offsets = c.dict->offsets.data();
       out->dict_bytes = c.dict->bytes.data();
       out->n_dict = c.dict->size();

@@ -501,6 +501,13 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
             }
         }
       }
+      // A large result that needs no host-side work (no post-aggregation, having, ordering or sketches)
+      // is turned into its columns on the device and copied straight into pinned result buffers.
+      {
+        const QuerySpec& q = plan.spec;
+        const bool ordered = q.type == QuerySpec::TopN || (q.type == QuerySpec::GroupBy && q.limit.present);
+        if (n > 65536 && !ordered && !q.has_having && q.post_aggregations.empty() && plan.n_hll == 0) return finalize_columnar(ctx, plan, st, t_start_ms);
+      }
       SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
       if (topk_slot >= 0 && !plan.n_hll) {
         int k = (int)k_want;
@@ -784,6 +791,145 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
            st->launches, st->h2d_bytes, st->d2h_bytes, device_topk ? "true" : "false", plan.spans.size(), plan.seg_index.size(),
            (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms);
   res->stats = buf;
+  return res.release();
+}
+
+// ---- pinned result buffers ------------------------------------------------------------------------------
+PinnedPool::~PinnedPool() {
+  for (auto& b : free_) cudaFreeHost(b.first);
+}
+void* PinnedPool::get(size_t bytes, size_t* got) {
+  bytes = round_up(std::max<size_t>(bytes, 1), 1 << 20);
+  {
+    std::lock_guard<std::mutex> lk(mu_);
+    size_t best = free_.size();
+    for (size_t i = 0; i < free_.size(); i++)
+      if (free_[i].second >= bytes && free_[i].second <= 2 * bytes && (best == free_.size() || free_[i].second < free_[best].second)) best = i;
+    if (best < free_.size()) {
+      void* p = free_[best].first;
+      *got = free_[best].second;
+      pooled_ -= *got;
+      free_.erase(free_.begin() + best);
+      return p;
+    }
+  }
+  void* p = nullptr;
+  SDO_CUDA(cudaMallocHost(&p, bytes));
+  *got = bytes;
+  return p;
+}
+void PinnedPool::put(void* p, size_t bytes) {
+  std::lock_guard<std::mutex> lk(mu_);
+  if (pooled_ + bytes > (16ull << 30)) { cudaFreeHost(p); return; }
+  free_.emplace_back(p, bytes);
+  pooled_ += bytes;
+}
+
+// Large, unordered result without host-side post-processing: decode keys and aggregate slots into
+// result columns on the device, then one D2H copy per column into pinned buffers the result owns.
+Result* Engine::finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms) {
+  cudaStream_t s = ctx->stream;
+  const uint64_t n = st->n_rows;
+  const QuerySpec& q = plan.spec;
+  std::unique_ptr<Result> res(new Result());
+  res->pool = &pinned_pool_;
+  res->n_rows = (int64_t)n;
+  MatParams mp;
+  memset(&mp, 0, sizeof mp);
+  mp.n = n;
+  mp.ns = plan.n_slots;
+  mp.has_tk = plan.has_time_key ? 1 : 0;
+  mp.tk_stride = plan.tk_stride;
+  std::vector<void*> dev_bufs;
+  struct Copy { void* dev; size_t bytes; size_t col; };
+  std::vector<Copy> copies;
+  auto dev_alloc = [&](size_t bytes) {
+    void* p = nullptr;
+    SDO_CUDA(cudaMallocAsync(&p, std::max<size_t>(bytes, 16), s));
+    dev_bufs.push_back(p);
+    return p;
+  };
+  auto add_column = [&](const std::string& name, int type, void* dev, size_t bytes) {
+    ResultColumn c;
+    c.name = name;
+    c.type = type;
+    res->columns.push_back(std::move(c));
+    copies.push_back({dev, bytes, res->columns.size() - 1});
+  };
+  SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
+  if (plan.has_bucket) {
+    std::vector<long long> lut(plan.time_keys.size());
+    for (size_t i = 0; i < lut.size(); i++) lut[i] = plan.time_keys[i].bucket;
+    void* dl = dev_alloc(lut.size() * 8);
+    SDO_CUDA(cudaMemcpyAsync(dl, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice, s));
+    SDO_CUDA(cudaStreamSynchronize(s));  // `lut` is pageable and goes out of scope
+    mp.bucket_lut = (const long long*)dl;
+    mp.ts_out = (long long*)dev_alloc(n * 8);
+    add_column("timestamp", SDO_RES_TIMESTAMP, mp.ts_out, n * 8);
+  }
+  bool any_time_dim = false;
+  for (auto& pd : plan.dims) any_time_dim |= pd.is_time;
+  if (any_time_dim) mp.tk_out = (uint32_t*)dev_alloc(n * 4);
+  for (auto& pd : plan.dims) {
+    if (pd.is_time) {
+      // ids = time key; dictionary entry i = the formatted value of time key i
+      add_column(pd.output_name, SDO_RES_STRING, mp.tk_out, n * 4);
+      auto d = std::make_shared<Dictionary>();
+      for (auto& tk : plan.time_keys) d->push(tk.formatted[pd.time_fmt].data(), tk.formatted[pd.time_fmt].size());
+      res->columns.back().dict = d;
+      continue;
+    }
+    const int k = mp.n_dims++;
+    mp.stride[k] = pd.stride;
+    mp.card[k] = pd.card;
+    const DimMeta& dm = plan.ds->dims[pd.ds_dim];
+    if (dm.enc == DimEncoding::Dict) {
+      mp.dim_is64[k] = 0;
+      mp.dim_out[k] = dev_alloc(n * 4);
+      add_column(pd.output_name, SDO_RES_STRING, mp.dim_out[k], n * 4);
+      res->columns.back().dict = dm.dict;
+    } else {
+      mp.dim_is64[k] = 1;
+      mp.dim_out[k] = dev_alloc(n * 8);
+      add_column(pd.output_name, SDO_RES_DIM_INT64, mp.dim_out[k], n * 8);
+    }
+  }
+  for (auto& pa : plan.aggs) {
+    const int k = mp.n_aggs++;
+    mp.agg_slot[k] = pa.slot;
+    mp.agg_mul[k] = pa.const_value;
+    mp.agg_mode[k] = pa.const_times_count ? MAT_I64_TIMES : (pa.slot_is_f64_ord ? MAT_F64_ORD : (pa.out_float ? MAT_F64_BITS : MAT_I64));
+    mp.agg_out[k] = dev_alloc(n * 8);
+    add_column(pa.name, pa.out_float ? SDO_RES_FLOAT64 : SDO_RES_INT64, mp.agg_out[k], n * 8);
+  }
+  launch_materialize(st->rows_keys, st->rows_slots, mp, s);
+  st->launches += 1;
+  // the same device buffer may back several columns (time-format dimensions share tk_out)
+  for (auto& c : copies) {
+    ResultColumn& col = res->columns[c.col];
+    col.raw = pinned_pool_.get(c.bytes, &col.raw_bytes);
+    SDO_CUDA(cudaMemcpyAsync(col.raw, c.dev, c.bytes, cudaMemcpyDeviceToHost, s));
+    st->d2h_bytes += c.bytes;
+  }
+  SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
+  SDO_CUDA(cudaStreamSynchronize(s));
+  for (void* p : dev_bufs) SDO_CUDA(cudaFreeAsync(p, s));
+  float ms_h2d = 0, ms_scan = 0, ms_dev = 0;
+  cudaEventElapsedTime(&ms_h2d, ctx->ev[0], ctx->ev[1]);
+  cudaEventElapsedTime(&ms_scan, ctx->ev[1], ctx->ev[2]);
+  cudaEventElapsedTime(&ms_dev, ctx->ev[0], ctx->ev[4]);
+  st->scan_ms = ms_scan;
+  char buf[1024];
+  snprintf(buf, sizeof buf,
+           "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
+           "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
+           "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":false,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu,\"jit\":%s,\"jitCompileMs\":%.3f,"
+           "\"columnar\":true}",
+           strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row, (long long)plan.algorithmic_bytes,
+           (unsigned long long)n, (unsigned long long)n, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms, st->launches, st->h2d_bytes, st->d2h_bytes,
+           plan.spans.size(), plan.seg_index.size(), (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms);
+  res->stats = buf;
+  (void)q;
   return res.release();
 }
 

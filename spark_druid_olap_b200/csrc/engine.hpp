@@ -16,6 +16,19 @@
 
 namespace sdo {
 
+// Pinned host buffers for large result columns, recycled across queries (cudaMallocHost is slow).
+class PinnedPool {
+ public:
+  ~PinnedPool();
+  void* get(size_t bytes, size_t* got);
+  void put(void* p, size_t bytes);
+
+ private:
+  std::mutex mu_;
+  std::vector<std::pair<void*, size_t>> free_;
+  size_t pooled_ = 0;
+};
+
 struct ResultColumn {
   std::string name;
   int type = 0;  // sdo_res_type
@@ -24,12 +37,19 @@ struct ResultColumn {
   std::vector<uint32_t> ids;
   std::shared_ptr<Dictionary> dict;  // STRING
   std::vector<uint8_t> hll;          // cardinality columns: n_rows * 512 registers
+  void* raw = nullptr;               // large results: column values in a pooled pinned buffer instead of the vectors
+  size_t raw_bytes = 0;
 };
 
 struct Result {
   int64_t n_rows = 0;
   std::vector<ResultColumn> columns;
   std::string stats;
+  PinnedPool* pool = nullptr;  // owner of the raw buffers (the engine must outlive its results)
+  ~Result() {
+    for (auto& c : columns)
+      if (c.raw && pool) pool->put(c.raw, c.raw_bytes);
+  }
 };
 
 // one in-flight query's device resources
@@ -103,6 +123,8 @@ class Engine {
   std::mutex cancel_mu_;
   std::set<std::string> cancelled_;
   std::mutex lut_mu_;
+  PinnedPool pinned_pool_;
+  Result* finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
 
   QueryCtx* acquire_ctx();
   void release_ctx(QueryCtx* c);

@@ -394,3 +394,50 @@ void launch_merge_rows(const unsigned long long* keys, const unsigned long long*
 }
 
 }  // namespace sdo
+
+// ---------------------------------------------------------------------------------------------
+// large results: rows -> result columns on the device
+// ---------------------------------------------------------------------------------------------
+namespace sdo {
+__global__ void materialize_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots,
+                                   const __grid_constant__ MatParams mp) {
+  uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+  for (; r < mp.n; r += step) {
+    unsigned long long k = keys[r];
+    if (mp.has_tk) {
+      const unsigned long long tk = k / mp.tk_stride;
+      k -= tk * mp.tk_stride;
+      if (mp.tk_out) mp.tk_out[r] = (uint32_t)tk;
+      if (mp.ts_out) mp.ts_out[r] = mp.bucket_lut[tk];
+    }
+    for (int d = 0; d < mp.n_dims; d++) {
+      const unsigned long long id = (k / mp.stride[d]) % mp.card[d];
+      if (mp.dim_is64[d]) ((long long*)mp.dim_out[d])[r] = (long long)id;
+      else ((uint32_t*)mp.dim_out[d])[r] = (uint32_t)id;
+    }
+    for (int a = 0; a < mp.n_aggs; a++) {
+      const unsigned long long raw = slots[r * mp.ns + mp.agg_slot[a]];
+      switch (mp.agg_mode[a]) {
+        case MAT_I64: ((long long*)mp.agg_out[a])[r] = (long long)raw; break;
+        case MAT_F64_BITS: ((unsigned long long*)mp.agg_out[a])[r] = raw; break;
+        case MAT_I64_TIMES: ((long long*)mp.agg_out[a])[r] = (long long)raw * mp.agg_mul[a]; break;
+        default: {  // order-preserving int64 back to a double; untouched min / max slots become +/- infinity
+          const long long o = (long long)raw;
+          double v;
+          if (o == 0x7FFFFFFFFFFFFFFFll) v = __longlong_as_double(0x7FF0000000000000ll);
+          else if (o == (long long)0x8000000000000000ull) v = __longlong_as_double((long long)0xFFF0000000000000ull);
+          else v = __longlong_as_double(f64_ord(o));
+          ((double*)mp.agg_out[a])[r] = v;
+        }
+      }
+    }
+  }
+}
+void launch_materialize(const unsigned long long* keys, const unsigned long long* slots, const MatParams& mp, cudaStream_t st) {
+  if (!mp.n) return;
+  int grid = (int)std::min<uint64_t>((mp.n + 255) / 256, 148 * 16);
+  materialize_kernel<<<grid, 256, 0, st>>>(keys, slots, mp);
+  SDO_CUDA(cudaGetLastError());
+}
+}  // namespace sdo

@@ -163,6 +163,25 @@ void launch_topk(const unsigned long long* keys, const unsigned long long* slots
 size_t topk_scratch_elems(uint64_t n, int k);
 void launch_gather_rows(const unsigned long long* keys, const unsigned long long* slots, const unsigned long long* idx, uint64_t k, int ns,
                         unsigned long long* out_keys, unsigned long long* out_slots, cudaStream_t st);
+// Large results: turn compacted (key, slots) rows into the result's columns on the device, so the host
+// only receives finished column arrays (dimension ids / integer values, timestamps, aggregate columns).
+enum MatMode : int32_t { MAT_I64 = 0, MAT_F64_BITS = 1, MAT_F64_ORD = 2, MAT_I64_TIMES = 3 };
+struct MatParams {
+  uint64_t n;
+  int32_t ns, n_dims, n_aggs, has_tk;
+  uint64_t tk_stride;
+  uint64_t stride[MAX_DIMS], card[MAX_DIMS];
+  void* dim_out[MAX_DIMS];      // uint32 ids or int64 values
+  int32_t dim_is64[MAX_DIMS];
+  uint32_t* tk_out;             // time key per row (ids of time-format dimensions), or NULL
+  long long* ts_out;            // bucket start per row, or NULL
+  const long long* bucket_lut;  // [n_tk]
+  int32_t agg_slot[MAX_AGGS], agg_mode[MAX_AGGS];
+  long long agg_mul[MAX_AGGS];
+  void* agg_out[MAX_AGGS];      // int64 or double columns
+};
+void launch_materialize(const unsigned long long* keys, const unsigned long long* slots, const MatParams& mp, cudaStream_t st);
+
 // sparse multi-GPU merge helpers
 void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
                            unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,

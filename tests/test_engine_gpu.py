@@ -295,3 +295,31 @@ def test_extend_dimension_keeps_results(gpu_engine):
         H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q2)), want2)
     finally:
         gpu_engine.drop_datasource(name)
+
+
+def test_large_result_columnar_path(gpu_engine):
+    """More than 65536 groups and nothing to do on the host: keys and aggregates are decoded into columns on the device.
+    Covers every column kind: timestamp, time-format dimension, dictionary dimension, integer dimension, long / double
+    sums, min / max of doubles and a constant-metric longSum."""
+    from spark_druid_olap_b200 import tpch
+    name = "tpch_big"
+    try:
+        gpu_engine.drop_datasource(name)
+    except Exception:
+        pass
+    tabs = tpch.load_into(gpu_engine, name, 0.06, ["o_orderkey", "l_returnflag", "l_extendedprice", "ps_availqty", "count"], keep=True)
+    tbl = H.oracle_table(tabs)
+    try:
+        a = Q.agg
+        for strategy in ("hash", "global"):
+            q = Q.GroupByQuerySpec(name, [Q.DefaultDimensionSpec("o_orderkey"), Q.DefaultDimensionSpec("l_returnflag"),
+                                          Q.ExtractionDimensionSpec("__time", "ym", Q.TimeFormatExtractionFunctionSpec("yyyy-MM"))], None, None,
+                                   Q.PeriodGranularitySpec("P1Y"), None,
+                                   [a("count", "n", "count"), a("longSum", "c1", "count"), a("longSum", "q", "ps_availqty"), a("doubleSum", "p", "l_extendedprice"),
+                                    a("doubleMax", "pmax", "l_extendedprice"), a("doubleMin", "pmin", "l_extendedprice")], None, Q.ALL_TIME,
+                                   Q.ctx(strategy) if strategy == "hash" else None)
+            res = gpu_engine.execute(q)
+            assert res.stats.get("columnar") is True and res.n_rows > 65536
+            H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, json.loads(q.to_json())), what=strategy)
+    finally:
+        gpu_engine.drop_datasource(name)
