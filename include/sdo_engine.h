@@ -174,6 +174,7 @@ typedef struct {
   const int* slot_ops;  /* host int[n_slots]: 0 = int64 sum, 1 = float64 sum, 2 = int64 min, 3 = int64 max */
   void* hll;            /* device uint8[n_keys * n_hll * 512] registers or NULL */
   int n_hll;
+  int64_t blob_bytes;   /* dense: table and registers are one contiguous block of this many bytes starting at `slots` */
 } sdo_partial_view;
 
 /* Shards of one datasource that live in different engines must share one id space per dimension before
@@ -191,6 +192,11 @@ int sdo_dimension_extend(sdo_engine* e, const char* datasource, const char* dime
 
 int sdo_query_partial(sdo_engine* e, const char* query_json, size_t len, sdo_partial** out);
 int sdo_partial_view_get(sdo_partial* p, sdo_partial_view* out);
+/* Dense path, small tables: copy this rank's blob (blob_bytes) into a caller-owned device buffer (so it can be
+ * all-gathered in one collective whatever mix of sum / min / max slots it holds), then fold the n_ranks gathered
+ * blobs, in rank order, back into this rank's table.  Both only enqueue work on the partial's stream. */
+int sdo_partial_export(sdo_partial* p, void* dst_dev, int64_t dst_bytes);
+int sdo_partial_merge_gathered(sdo_partial* p, const void* gathered_dev, int n_ranks);
 /* Sparse path: split local groups by owner = mix(key) % n_ranks into n_ranks contiguous runs
  * (counts_out[n_ranks], host), reordering keys/slots in place on the device. */
 int sdo_partial_partition(sdo_partial* p, int n_ranks, int64_t* counts_out);

@@ -59,7 +59,7 @@ class _ResultColumn(C.Structure):
 
 class PartialView(C.Structure):
     _fields_ = [("dense", C.c_int), ("n_keys", C.c_int64), ("n_slots", C.c_int), ("keys", C.c_void_p), ("slots", C.c_void_p),
-                ("slot_ops", C.POINTER(C.c_int)), ("hll", C.c_void_p), ("n_hll", C.c_int)]
+                ("slot_ops", C.POINTER(C.c_int)), ("hll", C.c_void_p), ("n_hll", C.c_int), ("blob_bytes", C.c_int64)]
 
 
 _lib = None
@@ -95,6 +95,8 @@ def lib():
         "sdo_result_free": (None, [vp]),
         "sdo_query_partial": (C.c_int, [vp, cp, sz, C.POINTER(vp)]),
         "sdo_partial_view_get": (C.c_int, [vp, C.POINTER(PartialView)]),
+        "sdo_partial_export": (C.c_int, [vp, vp, i64]),
+        "sdo_partial_merge_gathered": (C.c_int, [vp, vp, C.c_int]),
         "sdo_partial_partition": (C.c_int, [vp, C.c_int, C.POINTER(i64)]),
         "sdo_partial_merge_rows": (C.c_int, [vp, vp, vp, i64]),
         "sdo_partial_stream": (vp, [vp]),
@@ -118,7 +120,7 @@ EXPORTED_SYMBOLS = [
     "sdo_query_cancel", "sdo_result_num_rows", "sdo_result_num_columns", "sdo_result_column_get", "sdo_result_hll_registers",
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
-    "sdo_dimension_dictionary", "sdo_dimension_extend",
+    "sdo_dimension_dictionary", "sdo_dimension_extend", "sdo_partial_export", "sdo_partial_merge_gathered",
 ]
 
 NOALLOC_MAX_KEYS = 24
@@ -261,6 +263,12 @@ class Partial:
 
     def stream(self):
         return lib().sdo_partial_stream(self.handle)
+
+    def export(self, dst_ptr, dst_bytes):
+        _check(lib().sdo_partial_export(self.handle, dst_ptr, dst_bytes))
+
+    def merge_gathered(self, gathered_ptr, n_ranks):
+        _check(lib().sdo_partial_merge_gathered(self.handle, gathered_ptr, n_ranks))
 
     def partition(self, n_ranks):
         counts = (C.c_int64 * n_ranks)()

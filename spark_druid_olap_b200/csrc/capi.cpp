@@ -198,6 +198,14 @@ int sdo_partial_view_get(sdo_partial* p, sdo_partial_view* out) {
   if (!p || !out) return bad("sdo_partial_view_get: NULL argument");
   return guard([&] { p->p->engine->partial_view(p->p, out); });
 }
+int sdo_partial_export(sdo_partial* p, void* dst_dev, int64_t dst_bytes) {
+  if (!p || !dst_dev) return bad("sdo_partial_export: NULL argument");
+  return guard([&] { p->p->engine->partial_export(p->p, dst_dev, dst_bytes); });
+}
+int sdo_partial_merge_gathered(sdo_partial* p, const void* gathered_dev, int n_ranks) {
+  if (!p || !gathered_dev) return bad("sdo_partial_merge_gathered: NULL argument");
+  return guard([&] { p->p->engine->partial_merge_gathered(p->p, gathered_dev, n_ranks); });
+}
 int sdo_partial_partition(sdo_partial* p, int n_ranks, int64_t* counts_out) {
   if (!p || !counts_out) return bad("sdo_partial_partition: NULL argument");
   return guard([&] { p->p->engine->partial_partition(p->p, n_ranks, counts_out); });

@@ -23,9 +23,13 @@ static double now_ms() {
 // reported as such -- the registers themselves (sdo_result_hll_registers) are exact.
 double hll_estimate(const uint8_t* regs) {
   const double m = HLL_M;
+  static const struct Pow2 {
+    double inv[64];
+    Pow2() { for (int i = 0; i < 64; i++) inv[i] = 1.0 / (double)(1ull << i); }  // exact powers of two: same sum as dividing
+  } pow2;
   double zinv = 0, V = 0;
   for (int j = 0; j < HLL_M; j++) {
-    zinv += 1.0 / (double)(1ull << regs[j]);
+    zinv += pow2.inv[regs[j] & 63];
     if (regs[j] == 0) V += 1;
   }
   const double alpha_m2 = (0.7213 / (1.0 + 1.079 / m)) * m * m;
@@ -266,14 +270,26 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
     p.table = st->table;
   } else {
     st->table_rows = plan.n_keys;
-    SDO_CUDA(cudaMallocAsync((void**)&st->table, std::max<uint64_t>(cells, 1) * 8, s));
+    // dense table and its HLL registers share one block: a partial is then a single contiguous blob
+    const size_t tb = round_up(std::max<uint64_t>(cells, 1) * 8, 256);
+    const size_t hb = plan.n_hll ? (size_t)plan.n_keys * plan.n_hll * HLL_M : 0;
+    if (hb > opt_.hll_max_bytes) throw Unsupported("cardinality aggregation needs " + std::to_string(hb) + " bytes of registers");
+    SDO_CUDA(cudaMallocAsync((void**)&st->table, tb + hb, s));
+    st->dense_blob_bytes = tb + hb;
+    st->dense_table_bytes = tb;
+    if (hb) {
+      st->hll = (uint8_t*)st->table + tb;
+      st->hll_in_table = true;
+      SDO_CUDA(cudaMemsetAsync(st->hll, 0, hb, s));
+      p.hll = st->hll;
+    }
     if (strat != STRAT_LANE) {
       launch_fill_slots(st->table, plan.n_keys, plan.n_slots, nullptr, p, s);
       st->launches += 1;
       p.table = st->table;
     }
   }
-  if (plan.n_hll) {
+  if (plan.n_hll && !st->hll_in_table) {
     size_t hb = (size_t)st->table_rows * plan.n_hll * HLL_M;
     if (hb > opt_.hll_max_bytes) throw Unsupported("cardinality aggregation needs " + std::to_string(hb) + " bytes of registers");
     SDO_CUDA(cudaMallocAsync((void**)&st->hll, hb, s));
@@ -359,7 +375,7 @@ void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
 void Engine::free_state(QueryCtx* ctx, ScanState* st) {
   if (device_ < 0) return;
   cudaStream_t s = ctx->stream;
-  void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll};
+  void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll_in_table ? nullptr : (void*)st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll};
   for (void* p : ptrs)
     if (p) cudaFreeAsync(p, s);
   st->blob = nullptr; st->table = nullptr; st->hkeys = nullptr; st->hll = nullptr; st->partials = nullptr;
@@ -1021,7 +1037,25 @@ void Engine::partial_view(Partial* p, void* out_) {
     v->keys = nullptr;
     v->slots = p->st.table;
     v->hll = p->st.hll;
+    v->blob_bytes = (int64_t)p->st.dense_blob_bytes;
   }
+}
+
+void Engine::partial_export(Partial* p, void* dst_dev, int64_t dst_bytes) {
+  if (p->st.strategy == STRAT_HASH || p->st.rows_valid || !p->st.dense_blob_bytes) throw Invalid("sdo_partial_export applies to dense partials only");
+  if (dst_bytes < (int64_t)p->st.dense_blob_bytes) throw Invalid("sdo_partial_export: destination too small");
+  SDO_CUDA(cudaSetDevice(device_));
+  SDO_CUDA(cudaMemcpyAsync(dst_dev, p->st.table, p->st.dense_blob_bytes, cudaMemcpyDeviceToDevice, p->ctx->stream));
+}
+
+void Engine::partial_merge_gathered(Partial* p, const void* gathered_dev, int n_ranks) {
+  if (p->st.strategy == STRAT_HASH || p->st.rows_valid || !p->st.dense_blob_bytes) throw Invalid("sdo_partial_merge_gathered applies to dense partials only");
+  if (n_ranks < 1) throw Invalid("n_ranks out of range");
+  SDO_CUDA(cudaSetDevice(device_));
+  const uint64_t cells = p->st.table_rows * (uint64_t)p->plan.n_slots;
+  launch_merge_gathered((const unsigned long long*)gathered_dev, n_ranks, p->st.dense_blob_bytes, p->st.dense_table_bytes, cells, p->plan.n_slots,
+                        p->st.params, p->st.table, p->ctx->stream);
+  p->st.launches += 1;
 }
 
 void Engine::partial_partition(Partial* p, int n_ranks, int64_t* counts_out) {

@@ -71,6 +71,9 @@ struct ScanState {
   unsigned long long* table = nullptr;
   unsigned long long* hkeys = nullptr;
   uint8_t* hll = nullptr;
+  bool hll_in_table = false;      // dense: registers live behind the table in the same allocation
+  size_t dense_blob_bytes = 0;    // dense: bytes of table (+ registers), contiguous
+  size_t dense_table_bytes = 0;   // dense: bytes of the table part (256-aligned)
   void* blob = nullptr;      // per-query device blob (spans, coarse index, segptr, bitsets)
   unsigned long long* partials = nullptr;
   int launches = 0;
@@ -108,6 +111,8 @@ class Engine {
   void cancel(const std::string& query_id);
   Partial* partial(const char* json, size_t len);
   void partial_view(Partial* p, void* view_out);
+  void partial_export(Partial* p, void* dst_dev, int64_t dst_bytes);
+  void partial_merge_gathered(Partial* p, const void* gathered_dev, int n_ranks);
   void partial_partition(Partial* p, int n_ranks, int64_t* counts_out);
   void partial_merge_rows(Partial* p, const void* keys, const void* slots, int64_t n);
   Result* partial_finish(Partial* p);

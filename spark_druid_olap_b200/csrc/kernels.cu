@@ -441,3 +441,39 @@ void launch_materialize(const unsigned long long* keys, const unsigned long long
   SDO_CUDA(cudaGetLastError());
 }
 }  // namespace sdo
+
+// ---------------------------------------------------------------------------------------------
+// dense multi-GPU merge of all-gathered partial blobs
+// ---------------------------------------------------------------------------------------------
+namespace sdo {
+__global__ void merge_gathered_kernel(const unsigned long long* __restrict__ gathered, int n_ranks, uint64_t blob_words, uint64_t table_words,
+                                      uint64_t cells, int ns, const __grid_constant__ ScanParams p, unsigned long long* __restrict__ table) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+  for (; i < blob_words; i += step) {
+    if (i < table_words) {
+      if (i >= cells) continue;  // alignment padding
+      const int op = p.slot_op[i % ns];
+      unsigned long long v = gathered[i];
+      for (int r = 1; r < n_ranks; r++) v = slot_merge(op, v, gathered[(uint64_t)r * blob_words + i]);  // rank order: reproducible
+      table[i] = v;
+    } else {
+      // HLL registers: byte-wise max, 8 registers per word
+      unsigned long long v = gathered[i];
+      for (int r = 1; r < n_ranks; r++) {
+        const unsigned long long w = gathered[(uint64_t)r * blob_words + i];
+        v = ((unsigned long long)__vmaxu4((unsigned)(v >> 32), (unsigned)(w >> 32)) << 32) | __vmaxu4((unsigned)v, (unsigned)w);
+      }
+      table[i] = v;
+    }
+  }
+}
+void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size_t blob_bytes, size_t table_bytes, uint64_t cells, int n_slots,
+                           const ScanParams& p, unsigned long long* table, cudaStream_t st) {
+  const uint64_t words = blob_bytes / 8;
+  if (!words) return;
+  int grid = (int)std::min<uint64_t>((words + 255) / 256, 148 * 8);
+  merge_gathered_kernel<<<grid, 256, 0, st>>>(gathered, n_ranks, words, table_bytes / 8, cells, n_slots, p, table);
+  SDO_CUDA(cudaGetLastError());
+}
+}  // namespace sdo

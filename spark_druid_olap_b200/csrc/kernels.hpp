@@ -186,6 +186,9 @@ void launch_materialize(const unsigned long long* keys, const unsigned long long
 void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
                            unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,
                            unsigned long long* cursors_dev, cudaStream_t st);
+// dense multi-GPU merge: fold n_ranks gathered blobs (table + HLL registers each) into this rank's table
+void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size_t blob_bytes, size_t table_bytes, uint64_t cells, int n_slots,
+                           const ScanParams& p, unsigned long long* table, cudaStream_t st);
 void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
 
 #endif  // !__CUDACC_RTC__

@@ -76,6 +76,16 @@ def exchange_sparse(keys, slots, counts, group=None):
 
 _boundary_cache = {}
 _aligned = set()
+_buffers = {}
+GATHER_MAX_BYTES = 4 << 20  # dense partials up to this size are merged by all-gather + one fold kernel
+
+
+def _gather_buffers(dev, nbytes, world):
+    """Reusable (local, gathered) byte tensors for the small-table merge."""
+    key = (dev.index, nbytes, world)
+    if key not in _buffers:
+        _buffers[key] = (torch.empty(nbytes, dtype=torch.uint8, device=dev), torch.empty(nbytes * world, dtype=torch.uint8, device=dev))
+    return _buffers[key]
 
 
 def align_datasource(engine, datasource, group=None, force=False):
@@ -151,6 +161,19 @@ def execute_sharded(engine, query, group=None, root=0, force_exchange=False):
         stream = torch.cuda.ExternalStream(part.stream(), device=dev)
         info = {"dense": bool(v.dense), "n_keys": int(v.n_keys), "n_slots": int(v.n_slots), "merge_bytes": 0}
         with torch.cuda.stream(stream):
+            if v.dense and (world > 1 or force_exchange) and 0 < v.blob_bytes <= GATHER_MAX_BYTES:
+                # small table: one all-gather of the raw blobs (any mix of sum / min / max slots and HLL registers),
+                # folded in rank order by one kernel on the root
+                nb = int(v.blob_bytes)
+                local, gathered = _gather_buffers(dev, nb, world)
+                part.export(local.data_ptr(), nb)
+                dist.all_gather_into_tensor(gathered, local, group=group)
+                info["merge_bytes"] += nb * (world - 1)
+                if rank == root:
+                    part.merge_gathered(gathered.data_ptr(), world)
+                    return part.finish(), info
+                stream.synchronize()
+                return None, info
             if v.dense:
                 ops = [v.slot_ops[i] for i in range(v.n_slots)]
                 if world > 1 and v.n_keys > 0:

@@ -55,6 +55,12 @@ def test_sharded_equals_oracle_world1(dist_engine, mk, ordered):
     want = orc.execute(tbl, q)
     H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered)
     assert info["dense"] == (res.stats["strategy"] != "hash")
+    # same again through the exchange steps (dense: export -> all-gather -> fold; sparse: partition -> all-to-all -> merge)
+    res2, info2 = sharded.execute_sharded(eng, q, force_exchange=True)
+    H.assert_rows_equal(H.engine_rows(res2), want, ordered=ordered)
+    if info["dense"] and res.hll:
+        for k in res.hll:
+            assert (res.hll[k] == res2.hll[k]).all()
 
 
 def test_time_keys_are_numbered_on_the_global_grid(dist_engine):
