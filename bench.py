@@ -25,6 +25,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 METRIC = "tpch_flat_rows_scanned_per_s"
 UNIT = "rows/s"
 Q5T_COLUMNS = ["s_region", "o_orderdate", "s_nation", "l_extendedprice"]
+Q5T_TRAFFIC_BYTES = 277343232  # ncu capture of scan_kernel on SF10 Q5T (profiles/r01_ncu_q5t_*): 273.58 MB read + 3.77 MB written
 EXTRA_COLUMNS = ["c_mktsegment", "o_orderkey", "o_shippriority", "l_returnflag", "l_linestatus", "l_quantity", "l_discount", "o_custkey"]
 
 
@@ -153,11 +154,18 @@ def main():
     rows_local = plan["rowsScanned"]
     alg_bytes = plan["algorithmicBytes"]
 
+    L = sdo.lib()
+
     def step():
+        """One Q5T query.  N = 1: the C-ABI call itself (query JSON in host memory in, columnar result in host memory out);
+        N > 1: partial scan on every rank, NCCL merge, result on rank 0.  Returns (stats JSON bytes, result rows) or None."""
         if world == 1:
-            return eng.execute(q5t)
+            h = eng.execute_raw(q5t)
+            out = (L.sdo_result_stats_json(h), int(L.sdo_result_num_rows(h)))
+            L.sdo_result_free(h)
+            return out
         r, info = sharded.execute_sharded(eng, q5t)
-        return r
+        return (json.dumps(r.stats).encode(), r.n_rows) if r is not None else None
 
     def sync():
         torch.cuda.synchronize()
@@ -170,26 +178,28 @@ def main():
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    scan_ms, dev_ms, launches, h2d, d2h = [], [], 0, 0, 0
+    raw_stats, result_rows = [], None
     sync()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
     t0 = time.perf_counter()
-    last = None
     for _ in range(args.steps):
         r = step()
         if r is not None:
-            last = r
-            scan_ms.append(r.stats["scanKernelMs"])
-            dev_ms.append(r.stats["deviceMs"])
-            launches += r.stats["launches"]
-            h2d += r.stats["h2dBytes"]
-            d2h += r.stats["d2hBytes"]
+            raw_stats.append(r[0])
+            result_rows = r[1]
     ev1.record()
     sync()
     wall = time.perf_counter() - t0
     ev_ms = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
+    stats = [json.loads(x) for x in raw_stats]
+    scan_ms = [x["scanKernelMs"] for x in stats]
+    dev_ms = [x["deviceMs"] for x in stats]
+    launches = sum(x["launches"] for x in stats)
+    h2d = sum(x["h2dBytes"] for x in stats)
+    d2h = sum(x["d2hBytes"] for x in stats)
+    jit = bool(stats and stats[-1].get("jit"))
     if world > 1:
         t = torch.tensor([wall, ev_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -206,11 +216,10 @@ def main():
 
     peak, peak_src = peaks()
     e2e_ms = 1000 * wall / args.steps
-    if world == 1:
-        # device time of a step: CUDA events on the engine's stream around plan H2D + kernels + result D2H
-        ms_per_step = sum(dev_ms) / len(dev_ms)
-    else:
-        ms_per_step = ev_ms / args.steps
+    # device time of a step, same definition at every N: CUDA events on the engine's stream of the rank that finishes
+    # the query (rank 0) from the plan upload to the end of the result download -- at N > 1 that span contains the wait for
+    # the other ranks' partials (NCCL all-gather on the same stream) and the merge kernel
+    ms_per_step = sum(dev_ms) / len(dev_ms)
     value = rows_total / (ms_per_step / 1000)
     scan = sum(scan_ms) / len(scan_ms)
     achieved = alg_bytes / (scan / 1000) / 1e9
@@ -220,15 +229,18 @@ def main():
         "config": {"workload": f"TPC-H flattened SF{args.sf:g}/GPU, Q5-style TopN 10 of s_nation by sum(l_extendedprice), selector(s_region)+bound(o_orderdate) (BASELINE configs[1])",
                    "rows_per_gpu": n_local, "rows_scanned_per_step": rows_total, "bytes_per_row": plan["bytesPerRow"], "strategy": plan["strategy"],
                    "l2": "inputs larger than L2 (%.0f MB scanned per step per GPU)" % (alg_bytes / 1e6), "parallelism": f"segments sharded over {world} GPU(s)",
-                   "value_timing": "CUDA events on the engine stream per query (plan upload + kernels + result download)" if world == 1 else "CUDA events around K sharded steps, max over ranks",
+                   "value_timing": "CUDA events on the engine stream per query: plan upload + scan kernels (+ NCCL merge of partials on the same stream at N > 1) + result download",
+                   "kernel_variant": "run-time specialised (NVRTC) scan kernel" if jit else "ahead-of-time scan kernel",
                    "load_s": round(t_load, 2)},
         "e2e": {"value": rows_total / (e2e_ms / 1000), "unit": UNIT, "ms_per_query": e2e_ms, "h2d_bytes_per_step": h2d // max(1, args.steps),
                 "d2h_bytes_per_step": d2h // max(1, args.steps), "what": "sdo_query_execute: query JSON (host) in, columnar result (host) out"},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": Q5T_TRAFFIC_BYTES if abs(args.sf - 10.0) < 1e-9 else None,
+                     "traffic_note": "dram__bytes_read+write per launch from profiles/ (ncu --set full): below the algorithmic bytes because 32-byte metric/key sectors without a surviving row are never fetched",
                      "kernel": f"scan_kernel<{plan['strategy']}>", "kernel_ms": scan, "algorithmic_bytes": alg_bytes, "peak_source": peak_src},
         "clocks": clocks,
-        "result_rows": last.n_rows if last is not None else None,
+        "result_rows": result_rows,
+        "wall_ms_per_step_cuda_events": ev_ms / args.steps,
     }
     if world == 1 and not args.no_cpu:
         try:
