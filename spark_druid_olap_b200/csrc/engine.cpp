@@ -142,6 +142,32 @@ const uint16_t* Engine::ensure_hll_lut(DataSource& ds, int di, cudaStream_t st) 
   return (const uint16_t*)lut;
 }
 
+// The dimension's sketch column of one segment (uint16 per row), built on first use: the per-row analogue of
+// Druid's ingest-time hyperUnique metric.  Depends on row values only, so dictionary re-encodes leave it valid.
+const void* Engine::ensure_hll_column(DataSource& ds, int di, Segment& sg, cudaStream_t st) {
+  {
+    std::lock_guard<std::mutex> lk(lut_mu_);
+    if ((int)sg.dim_hll.size() > di && sg.dim_hll[di]) return sg.dim_hll[di];
+  }
+  const DimMeta& dm = ds.dims[di];
+  const uint16_t* lut = nullptr;
+  int mode;
+  if (dm.enc == DimEncoding::Direct) mode = dm.src_type == 1 ? HLL_DIRECT_INT : HLL_DIRECT_LONG;
+  else { mode = HLL_LUT; lut = ensure_hll_lut(ds, di, st); }
+  std::lock_guard<std::mutex> lk(lut_mu_);
+  if ((int)sg.dim_hll.size() <= di) sg.dim_hll.resize(ds.dims.size(), nullptr);
+  if (sg.dim_hll[di]) return sg.dim_hll[di];
+  const size_t nb = round_up((size_t)sg.n_rows * 2 + 64, 256);
+  void* col = nullptr;
+  SDO_CUDA(cudaMalloc(&col, nb));
+  SDO_CUDA(cudaMemsetAsync(col, 0, nb, st));
+  launch_hll_column(sg.dim_data[di], sg.dim_width[di], mode, lut, sg.n_rows, (uint16_t*)col, st);
+  SDO_CUDA(cudaStreamSynchronize(st));
+  sg.dim_hll[di] = col;
+  sg.device_bytes += nb;
+  return col;
+}
+
 static uint64_t pow2_ceil(uint64_t v) {
   uint64_t p = 1;
   while (p < v) p <<= 1;
@@ -183,7 +209,8 @@ void Engine::run_scan(QueryCtx* ctx, Plan& plan, ScanState* st) {
       const PlanColumn& pc = plan.columns[c];
       const void* p = pc.is_metric ? sg.metric_data[pc.index] : sg.dim_data[pc.index];
       if (!p) throw Unsupported("segment " + format_iso_instant(sg.start_ms) + " has no data for column '" + (pc.is_metric ? ds.metrics[pc.index].name : ds.dims[pc.index].name) + "'");
-      if (!pc.is_metric && sg.dim_width[pc.index] != pc.width) throw std::runtime_error("internal: segment id width differs from datasource width");
+      if (pc.is_hll) p = ensure_hll_column(ds, pc.index, *ds.segments[plan.seg_index[si]], s);
+      else if (!pc.is_metric && sg.dim_width[pc.index] != pc.width) throw std::runtime_error("internal: segment id width differs from datasource width");
       sp[si * n_cols + c] = p;
     }
   }

@@ -140,6 +140,7 @@ class Engine {
   Result* finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
   void free_state(QueryCtx* ctx, ScanState* st);
   const uint16_t* ensure_hll_lut(DataSource& ds, int di, cudaStream_t st);
+  const void* ensure_hll_column(DataSource& ds, int di, Segment& sg, cudaStream_t st);
 };
 
 double hll_estimate(const uint8_t* regs);

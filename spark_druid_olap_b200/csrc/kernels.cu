@@ -477,3 +477,24 @@ void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size
   SDO_CUDA(cudaGetLastError());
 }
 }  // namespace sdo
+
+// ---------------------------------------------------------------------------------------------
+// HLL sketch column: one packed (register index, rho) per row, built once per (segment, dimension)
+// ---------------------------------------------------------------------------------------------
+namespace sdo {
+__global__ void hll_column_kernel(const void* __restrict__ ids, int width, int mode, const uint16_t* __restrict__ lut, int64_t n,
+                                  uint16_t* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t step = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += step) {
+    const uint32_t id = width == 1 ? ((const uint8_t*)ids)[i] : (width == 2 ? ((const uint16_t*)ids)[i] : ((const uint32_t*)ids)[i]);
+    out[i] = (uint16_t)hll_value(mode, lut, id);
+  }
+}
+void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut, int64_t n, uint16_t* out, cudaStream_t st) {
+  if (!n) return;
+  int grid = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  hll_column_kernel<<<grid, 256, 0, st>>>(ids, width, mode, lut, n, out);
+  SDO_CUDA(cudaGetLastError());
+}
+}  // namespace sdo

@@ -74,7 +74,9 @@ enum AggOp : int32_t {
 // how two partial slots merge (PostAggregate.scala:39-60: count/sum -> sum, min -> min, max -> max)
 enum SlotOp : int32_t { SLOT_SUM_I64 = 0, SLOT_SUM_F64 = 1, SLOT_MIN_I64 = 2, SLOT_MAX_I64 = 3 };
 
-enum HllMode : int32_t { HLL_DIRECT_INT = 0, HLL_DIRECT_LONG = 1, HLL_LUT = 2 };
+// how a row's (register index << 6 | rho) is obtained: hashed from an integer id, looked up per dictionary id, or
+// read ready-made from the dimension's sketch column (what the scan kernel uses)
+enum HllMode : int32_t { HLL_DIRECT_INT = 0, HLL_DIRECT_LONG = 1, HLL_LUT = 2, HLL_PACKED = 3 };
 // where HLL registers are updated during the scan
 enum HllPlace : int32_t {
   HLL_IN_GLOBAL = 0,     // straight into the HBM register table
@@ -138,6 +140,9 @@ void launch_reencode(const void* src, int src_width, void* dst, int dst_width, i
 void launch_gather64(const void* src, const int32_t* perm, int64_t r0, int64_t n, void* dst, cudaStream_t st);
 // HLL lookup table of a string dictionary: lut[i] = hll_pack(xxh64(bytes of entry i))
 void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n, uint16_t* lut, cudaStream_t st);
+// sketch column of a dimension: out[row] = hll_pack(XxHash64(value of row)), from the id column (mode HLL_DIRECT_* hashes
+// the integer id, HLL_LUT looks the dictionary id up)
+void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut, int64_t n, uint16_t* out, cudaStream_t st);
 
 // scan
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots);

@@ -37,14 +37,15 @@ struct CNode {
 struct Compiler {
   const DataSource& ds;
   Plan& plan;
-  std::map<std::pair<bool, int>, int> col_slot;  // (is_metric, index) -> slot
+  std::map<std::pair<int, int>, int> col_slot;  // (kind, index) -> slot
 
-  int column_slot(bool is_metric, int index) {
-    auto key = std::make_pair(is_metric, index);
+  int column_slot(bool is_metric, int index, bool is_hll = false) {
+    auto key = std::make_pair(is_hll ? 2 : (is_metric ? 1 : 0), index);
     auto it = col_slot.find(key);
     if (it != col_slot.end()) return it->second;
     int slot = (int)plan.columns.size();
-    plan.columns.push_back({is_metric, index, is_metric ? 8 : ds.dims[index].width});
+    if (slot >= 250) throw Unsupported("query references too many columns");
+    plan.columns.push_back({is_metric, index, is_hll ? 2 : (is_metric ? 8 : ds.dims[index].width), is_hll});
     col_slot[key] = slot;
     return slot;
   }
@@ -470,11 +471,13 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
         pa.out_float = true;
         pa.hll_index = da.hll_index = plan.n_hll++;
         da.op = AGG_HLL;
-        da.col = cc.column_slot(false, di);
-        da.width = dm.width;
+        // the scan reads the dimension's precomputed sketch column (2 bytes per row), not its ids
+        da.col = cc.column_slot(false, di, true);
+        da.width = 2;
         da.slot = 0;
-        if (dm.enc == DimEncoding::Direct) da.hll_mode = dm.src_type == 1 ? HLL_DIRECT_INT : HLL_DIRECT_LONG;
-        else { da.hll_mode = HLL_LUT; hll_dim = di; }
+        da.hll_mode = HLL_PACKED;
+        hll_dim = di;
+        (void)dm;
         break;
       }
     }
@@ -674,7 +677,7 @@ std::string explain_json(const Plan& p) {
     if (i) o += ",";
     const auto& c = p.columns[i];
     o += "{\"name\":";
-    json_escape(o, c.is_metric ? p.ds->metrics[c.index].name : p.ds->dims[c.index].name);
+    json_escape(o, c.is_metric ? p.ds->metrics[c.index].name : (c.is_hll ? "hll16(" + p.ds->dims[c.index].name + ")" : p.ds->dims[c.index].name));
     o += ",\"width\":" + std::to_string(c.width) + "}";
   }
   o += "],\"filter\":{\"ops\":[";

@@ -14,7 +14,9 @@
 
 namespace sdo {
 
-struct PlanColumn { bool is_metric; int index; int width; };  // one slot of a segptr row
+// One slot of a segptr row.  kind 0 = dimension ids, 1 = metric, 2 = the dimension's precomputed HLL++ sketch column
+// (uint16 per row: register index << 6 | rho of the row's value), built on first use like a Druid hyperUnique metric.
+struct PlanColumn { bool is_metric; int index; int width; bool is_hll = false; };
 
 struct PlanDim {
   std::string output_name;

@@ -195,6 +195,7 @@ __device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned in
   }
 }
 __device__ __forceinline__ uint32_t hll_value(int mode, const uint16_t* lut, uint32_t id) {
+  if (mode == HLL_PACKED) return id;  // the column already holds idx << 6 | rho
   if (mode == HLL_LUT) return __ldg(lut + id);
   if (mode == HLL_DIRECT_INT) return hll_pack(xxh64_int((int32_t)id, HLL_SEED));
   return hll_pack(xxh64_long((int64_t)id, HLL_SEED));

@@ -90,8 +90,11 @@ void Store::free_segment(Segment& s) {
     if (p) cudaFree(p);
   for (void* p : s.metric_data)
     if (p) cudaFree(p);
+  for (void* p : s.dim_hll)
+    if (p) cudaFree(p);
   s.dim_data.clear();
   s.metric_data.clear();
+  s.dim_hll.clear();
 }
 
 void Store::create(const std::string& name, const std::string& options_json) {
@@ -434,6 +437,7 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
     s->partition = partition;
     s->n_rows = ct.r1 - ct.r0;
     s->dim_data.assign(ds->dims.size(), nullptr);
+    s->dim_hll.assign(ds->dims.size(), nullptr);
     s->dim_width.assign(ds->dims.size(), 0);
     s->metric_data.assign(ds->metrics.size(), nullptr);
     for (int64_t r = ct.r0; r < ct.r1; r++) {
@@ -504,6 +508,7 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
   // older segments may lack columns that arrived later
   for (auto& s : ds->segments) {
     s->dim_data.resize(ds->dims.size(), nullptr);
+    s->dim_hll.resize(ds->dims.size(), nullptr);
     s->dim_width.resize(ds->dims.size(), 0);
     s->metric_data.resize(ds->metrics.size(), nullptr);
   }

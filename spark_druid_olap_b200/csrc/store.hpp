@@ -69,6 +69,7 @@ struct Segment {
   int partition = 0;
   int64_t n_rows = 0;
   std::vector<void*> dim_data;     // device, per datasource dim (nullptr if absent)
+  std::vector<void*> dim_hll;      // device uint16 sketch column per dim (HLL++ idx << 6 | rho of each row), built on first use
   std::vector<int> dim_width;      // width the data is currently encoded with
   std::vector<void*> metric_data;  // device, 8 bytes per row
   // run index over the sorted, truncated time column
