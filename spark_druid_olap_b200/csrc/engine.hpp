@@ -8,6 +8,7 @@
 #include <memory>
 #include <mutex>
 #include <set>
+#include <shared_mutex>
 #include <string>
 #include <vector>
 
@@ -79,6 +80,7 @@ struct ScanState {
   int launches = 0;
   size_t h2d_bytes = 0, d2h_bytes = 0;
   float scan_ms = 0;
+  double plan_ms = 0;         // host: parse + plan
   bool jit = false;           // the scan ran on a run-time specialised kernel
   double jit_compile_ms = 0;  // > 0 when this query paid for the compilation
   // sparse rows after compaction / merging (multi-GPU)
@@ -135,7 +137,10 @@ class Engine {
   void release_ctx(QueryCtx* c);
   void ensure_pinned(void** p, size_t* cur, size_t need);
   void check_cancel(const std::string& qid);
-  void run_scan(QueryCtx* ctx, Plan& plan, ScanState* st);
+  void run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st);
+  std::shared_ptr<const Plan> plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out);
+  std::mutex plan_mu_;
+  std::map<std::string, std::shared_ptr<const Plan>> plan_cache_;
   void compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st);
   Result* finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
   void free_state(QueryCtx* ctx, ScanState* st);

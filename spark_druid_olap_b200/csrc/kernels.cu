@@ -79,6 +79,21 @@ void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, 
   fill_slots_kernel<<<grid, 256, 0, st>>>(table, n, n_slots, p);
   SDO_CUDA(cudaGetLastError());
 }
+// empty hash table: every bucket = [HASH_EMPTY | slot_init[0..ns) | 0 ...]
+__global__ void fill_hash_kernel(unsigned long long* table, uint64_t cap, uint32_t stride, int ns, const __grid_constant__ ScanParams p) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x, n = cap * stride;
+  for (; i < n; i += step) {
+    const uint32_t w = (uint32_t)(i & (stride - 1));  // stride is a power of two
+    table[i] = w == 0 ? HASH_EMPTY : (w <= (uint32_t)ns ? p.slot_init[w - 1] : 0ull);
+  }
+}
+void launch_fill_hash(unsigned long long* table, uint64_t cap, uint32_t stride, int n_slots, const ScanParams& p, cudaStream_t st) {
+  if (!cap) return;
+  int grid = (int)std::min<uint64_t>((cap * stride + 255) / 256, 148 * 16);
+  fill_hash_kernel<<<grid, 256, 0, st>>>(table, cap, stride, n_slots, p);
+  SDO_CUDA(cudaGetLastError());
+}
 __global__ void fill_u64_kernel(unsigned long long* dst, uint64_t n, unsigned long long v) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
@@ -128,15 +143,17 @@ void launch_reduce_partials(const unsigned long long* partials, int n_blocks, ui
 // ---------------------------------------------------------------------------------------------
 // compaction of occupied groups
 // ---------------------------------------------------------------------------------------------
+// dense: group i = table[i * ns ..], occupied when its row count (slot 0) is non-zero;
+// hash: bucket i = table[i * stride ..] = [key | slots], occupied when the key is set
 template <bool HASH>
-__global__ void compact_kernel(const unsigned long long* __restrict__ hkeys, const unsigned long long* __restrict__ table, uint64_t n,
-                               int ns, unsigned long long* __restrict__ out_keys, unsigned long long* __restrict__ out_slots,
+__global__ void compact_kernel(const unsigned long long* __restrict__ table, uint64_t n, int ns, uint32_t stride,
+                               unsigned long long* __restrict__ out_keys, unsigned long long* __restrict__ out_slots,
                                unsigned long long* __restrict__ out_src, unsigned long long* counter) {
   __shared__ unsigned long long s_base;
   __shared__ unsigned int s_warp[8];
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   bool occ = false;
-  if (i < n) occ = HASH ? (hkeys[i] != HASH_EMPTY) : (table[i * ns] != 0ull);
+  if (i < n) occ = HASH ? (table[i * stride] != HASH_EMPTY) : (table[i * ns] != 0ull);
   const unsigned int bal = __ballot_sync(0xffffffffu, occ);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (lane == 0) s_warp[warp] = __popc(bal);
@@ -149,21 +166,22 @@ __global__ void compact_kernel(const unsigned long long* __restrict__ hkeys, con
   __syncthreads();
   if (!occ) return;
   const unsigned long long o = s_base + s_warp[warp] + __popc(bal & ((1u << lane) - 1u));
-  out_keys[o] = HASH ? hkeys[i] : i;
+  out_keys[o] = HASH ? table[i * stride] : i;
   if (out_src) out_src[o] = i;
-  for (int s = 0; s < ns; s++) out_slots[o * ns + s] = table[i * ns + s];
+  const unsigned long long* row = HASH ? table + i * stride + 1 : table + i * ns;
+  for (int s = 0; s < ns; s++) out_slots[o * ns + s] = row[s];
 }
 void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int n_slots, unsigned long long* out_keys,
                           unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st) {
   if (!n_keys) return;
-  compact_kernel<false><<<(unsigned)((n_keys + 255) / 256), 256, 0, st>>>(nullptr, table, n_keys, n_slots, out_keys, out_slots, out_src, counter);
+  compact_kernel<false><<<(unsigned)((n_keys + 255) / 256), 256, 0, st>>>(table, n_keys, n_slots, 0, out_keys, out_slots, out_src, counter);
   SDO_CUDA(cudaGetLastError());
 }
-void launch_compact_hash(const unsigned long long* hkeys, const unsigned long long* table, uint64_t cap, int n_slots,
+void launch_compact_hash(const unsigned long long* table, uint64_t cap, int n_slots, uint32_t stride,
                          unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
                          unsigned long long* counter, cudaStream_t st) {
   if (!cap) return;
-  compact_kernel<true><<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(hkeys, table, cap, n_slots, out_keys, out_slots, out_src, counter);
+  compact_kernel<true><<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(table, cap, n_slots, stride, out_keys, out_slots, out_src, counter);
   SDO_CUDA(cudaGetLastError());
 }
 __global__ void gather_hll_kernel(const uint8_t* __restrict__ hll, const unsigned long long* __restrict__ src, uint64_t n, int n_hll,
@@ -373,11 +391,11 @@ __global__ void merge_rows_kernel(const unsigned long long* __restrict__ keys, c
   const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
   const int ns = p.n_slots;
   for (; i < n; i += step) {
-    uint64_t h = hash_claim(p.hkeys, p.hmask, keys[i]);
+    uint64_t h = hash_claim(p.hkeys, p.hmask, p.hstride, keys[i]);
     if (h == HASH_EMPTY) { p.counters[1] = 1; continue; }
     for (int s = 0; s < ns; s++) {
       unsigned long long v = slots[i * ns + s];
-      unsigned long long* q = p.table + h * ns + s;
+      unsigned long long* q = p.table + h * p.hstride + 1 + s;
       const int op = p.slot_op[s];
       if (op == SLOT_SUM_I64) atomicAdd(q, v);
       else if (op == SLOT_SUM_F64) atomicAdd((double*)q, __longlong_as_double(v));

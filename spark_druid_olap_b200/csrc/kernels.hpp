@@ -126,8 +126,12 @@ struct ScanParams {
   uint64_t slot_init[MAX_SLOTS];
   unsigned long long* table;    // LANE: partials [grid][n_keys*n_slots]; BLOCK/GLOBAL: [n_keys*n_slots]; HASH: [cap*n_slots]
   uint8_t* hll;                 // [n_keys or cap][n_hll][512]
-  unsigned long long* hkeys;    // HASH: [cap]
+  // HASH: one bucket = hstride words: [key | slot 0 .. slot n_slots-1 | padding]; key and aggregates of a group share a
+  // 32-byte sector (hstride is a power of two), so claiming the bucket and updating it touch one sector
+  unsigned long long* hkeys;    // HASH: bucket array base (== table); bucket h starts at hkeys + h * hstride
   uint64_t hmask;               // HASH: cap - 1
+  uint32_t hstride;             // HASH: words per bucket
+  uint32_t pad1;
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 
@@ -152,12 +156,13 @@ void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem_bytes,
 void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, const uint64_t* slot_init_dev_or_null,
                        const ScanParams& p, cudaStream_t st);
 void launch_fill_u64(unsigned long long* dst, uint64_t n, unsigned long long v, cudaStream_t st);
+void launch_fill_hash(unsigned long long* table, uint64_t cap, uint32_t stride, int n_slots, const ScanParams& p, cudaStream_t st);
 void launch_reduce_partials(const unsigned long long* partials, int n_blocks, uint32_t n, int n_slots, const ScanParams& p,
                             unsigned long long* out, cudaStream_t st);
 // compaction of non-empty groups: dense tables (keyed by slot 0 > 0) and hash tables
 void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int n_slots, unsigned long long* out_keys,
                           unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st);
-void launch_compact_hash(const unsigned long long* hkeys, const unsigned long long* table, uint64_t cap, int n_slots,
+void launch_compact_hash(const unsigned long long* table, uint64_t cap, int n_slots, uint32_t stride,
                          unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
                          unsigned long long* counter, cudaStream_t st);
 void launch_gather_hll(const uint8_t* hll, const unsigned long long* src, uint64_t n, int n_hll, uint8_t* out, cudaStream_t st);

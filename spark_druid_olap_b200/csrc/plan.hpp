@@ -53,6 +53,7 @@ struct HostLeaf {
 struct Plan {
   QuerySpec spec;
   std::shared_ptr<DataSource> ds;
+  uint64_t ds_version = 0;          // datasource version this plan was made against
   std::vector<int> seg_index;       // used segments -> index in ds->segments
   std::vector<DevSpan> spans;       // + sentinel appended at upload
   std::vector<uint32_t> coarse;     // coarse span index (COARSE units per entry)

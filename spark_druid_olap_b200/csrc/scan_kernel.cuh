@@ -265,13 +265,14 @@ struct Acc<STRAT_HASH> : AtomicOps {
 };
 
 // find-or-claim the slot of `key` (linear probing).  Returns HASH_EMPTY if the table is full.
-__device__ __forceinline__ uint64_t hash_claim(unsigned long long* hkeys, uint64_t mask, uint64_t key) {
+__device__ __forceinline__ uint64_t hash_claim(unsigned long long* hkeys, uint64_t mask, uint32_t stride, uint64_t key) {
   uint64_t h = mix64(key) & mask;
   for (uint64_t probes = 0; probes <= mask; probes++) {
-    unsigned long long cur = *(volatile unsigned long long*)(hkeys + h);
+    unsigned long long* slot = hkeys + h * stride;
+    unsigned long long cur = *(volatile unsigned long long*)slot;
     if (cur == key) return h;
     if (cur == HASH_EMPTY) {
-      unsigned long long prev = atomicCAS(hkeys + h, HASH_EMPTY, (unsigned long long)key);
+      unsigned long long prev = atomicCAS(slot, HASH_EMPTY, (unsigned long long)key);
       if (prev == HASH_EMPTY || prev == key) return h;
     }
     h = (h + 1) & mask;
@@ -409,7 +410,7 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
 #pragma unroll
     for (int i = 0; i < N; i++) {
       if ((m >> i) & 1u) {
-        uint64_t h = hash_claim(p.hkeys, p.hmask, (uint64_t)key[i]);
+        uint64_t h = hash_claim(p.hkeys, p.hmask, p.hstride, (uint64_t)key[i]);
         if (h == HASH_EMPTY) { p.counters[1] = 1; m &= ~(1u << i); }
         key[i] = (key_t)h;
       }
@@ -607,6 +608,9 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
     const uint32_t n = (uint32_t)p.n_keys * ns;
     for (uint32_t x = tid; x < n; x += SCAN_THREADS) smem[x] = p.slot_init[x % ns];
     acc.base = smem;
+  } else if (STRAT == STRAT_HASH) {
+    acc.base = p.table + 1;  // word 0 of a bucket is its key
+    acc.ns = (int)p.hstride;
   } else {
     acc.base = p.table;
   }

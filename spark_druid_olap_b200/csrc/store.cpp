@@ -240,6 +240,7 @@ void Store::merge_dictionary(DataSource& ds, int di, const Dictionary& bd, std::
 void Store::extend_dimension(const std::string& name, const std::string& dim, const Dictionary* values, int64_t min_cardinality) {
   auto ds = get(name);
   std::unique_lock<std::shared_mutex> lk(ds->mu);
+  ds->version++;
   if (device_ >= 0) SDO_CUDA(cudaSetDevice(device_));
   int di = ds->dim_index(dim);
   if (di < 0) throw NotFound("unknown dimension '" + dim + "' in datasource '" + name + "'");
@@ -268,6 +269,7 @@ void Store::load(const std::string& name, int64_t n_rows, const std::vector<Load
   auto ds = get(name);
   std::unique_lock<std::shared_mutex> lk(ds->mu);
   if (n_rows < 0 || n_rows > 2147483647ll) throw Invalid("sdo_segment_load: n_rows must be in [0, 2^31)");
+  ds->version++;
   if (n_rows == 0) return;
   const bool dev = device_ >= 0;
   if (dev) SDO_CUDA(cudaSetDevice(device_));

@@ -87,6 +87,7 @@ struct DataSource {
   std::vector<std::unique_ptr<Segment>> segments;  // sorted by (start_ms, partition)
   int64_t n_rows = 0;
   mutable std::shared_mutex mu;  // loads take it exclusively, queries shared
+  uint64_t version = 0;          // bumped by every load / dimension change: cached plans of older versions are stale
 
   int dim_index(const std::string& n) const;
   int metric_index(const std::string& n) const;

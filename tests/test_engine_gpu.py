@@ -323,3 +323,27 @@ def test_large_result_columnar_path(gpu_engine):
             H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, json.loads(q.to_json())), what=strategy)
     finally:
         gpu_engine.drop_datasource(name)
+
+
+def test_cached_plan_is_dropped_when_the_datasource_changes(gpu_engine):
+    """Plans are cached by query text; a load or a dictionary change must invalidate them."""
+    from spark_druid_olap_b200 import tpch
+    name = "tpch_plan_cache"
+    try:
+        gpu_engine.drop_datasource(name)
+    except Exception:
+        pass
+    cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "count"]
+    t0 = tpch.load_into(gpu_engine, name, 0.01, cols, shards=(0,), n_shards=2, keep=True)
+    try:
+        q = json.loads(Q.q1_style().to_json())
+        q["dataSource"] = name
+        for _ in range(2):  # second run uses the cached plan
+            H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), orc.execute(H.oracle_table(t0), q))
+        t1 = tpch.load_into(gpu_engine, name, 0.01, cols, shards=(1,), n_shards=2, keep=True, create=False)
+        H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), orc.execute(H.oracle_table(t0 + t1), q))
+        gpu_engine.drop_datasource(name)
+        t2 = tpch.load_into(gpu_engine, name, 0.005, cols, keep=True)  # same name, new datasource object
+        H.assert_rows_equal(H.engine_rows(gpu_engine.execute(q)), orc.execute(H.oracle_table(t2), q))
+    finally:
+        gpu_engine.drop_datasource(name)

@@ -30,4 +30,4 @@ for i in range(iters):
     r = eng.execute(q)
     s = r.stats
     print(f"{name} sf={sf:g} {s['strategy']} rows={s['rowsScanned']} groups={s['groups']} scan={s['scanKernelMs']:.4f} ms dev={s['deviceMs']:.4f} ms total={s['totalMs']:.4f} ms "
-          f"alg={s['algorithmicBytes'] / 1e6:.1f} MB -> {s['algorithmicBytes'] / s['scanKernelMs'] / 1e6:.0f} GB/s launches={s['launches']}")
+          f"alg={s['algorithmicBytes'] / 1e6:.1f} MB -> {s['algorithmicBytes'] / s['scanKernelMs'] / 1e6:.0f} GB/s launches={s['launches']} plan={s.get('planMs', 0):.3f} assemble={s.get('assembleMs', 0):.3f}")
