@@ -255,7 +255,23 @@ def _execute(ct, q, threads, return_registers):
         ca = _Agg()
         ca.filter_leaf = fl
         t = a["type"]
-        if t in _AGG_KIND:
+        if t == "javascript" or "expression" in a:
+            # the argument expression becomes one more float64 column (numpy, IEEE per-row arithmetic)
+            if t == "javascript":
+                params, body = orc.js_subset.parse_function(a["fnAggregate"])
+                fold, arg = orc.js_subset.split_fold(params, body)
+                cols = [None] + [np.asarray(ct.metrics[f], dtype=np.float64) for f in a["fieldNames"]]
+            else:
+                params, arg = orc.js_subset.parse_expression(a["expression"])
+                fold = {"doubleSum": "sum", "doubleMin": "min", "doubleMax": "max"}.get(t)
+                if fold is None:
+                    raise _Unsupported()
+                cols = [np.asarray(ct.metrics[f], dtype=np.float64) for f in params]
+            col = np.ascontiguousarray(np.broadcast_to(orc.js_subset.evaluate_numeric(arg, cols), (len(ct.time),)), dtype=np.float64)
+            keep.append(col)
+            ca.kind = {"sum": 2, "min": 5, "max": 6}[fold]
+            ca.col, ca.col_is_f64 = col.ctypes.data, 1
+        elif t in _AGG_KIND:
             ca.kind = _AGG_KIND[t]
             if t != "count":
                 m = ct.metrics[a["fieldName"]]

@@ -29,6 +29,11 @@ import re
 
 import numpy as np
 
+try:
+    from . import js_subset
+except ImportError:  # imported as a top-level module
+    import js_subset
+
 M64 = (1 << 64) - 1
 P1, P2, P3, P4, P5 = 0x9E3779B185EBCA87, 0xC2B2AE3D27D4EB4F, 0x165667B19E3779F9, 0x85EBCA77C2B2AE63, 0x27D4EB2F165667C5
 HLL_P, HLL_M, HLL_SEED = 9, 512, 42
@@ -364,9 +369,91 @@ def filter_mask(tbl, f):
         ok = [rx.search(v) is not None for v in vals]
     elif t == "contains":
         ok = [f["value"] in v for v in vals]
+    elif t == "javascript":
+        # JavascriptFilterSpec (DruidQuerySpec.scala:218-236): Druid calls the function with the dimension value, null
+        # for the empty value, and keeps the row when the result is truthy
+        params, body = js_subset.parse_function(f["function"])
+        ok = [js_subset.truthy(js_subset.evaluate(body, [v if v != "" else None])) for v in vals]
     else:
         raise NotImplementedError(t)
     return np.asarray(ok, dtype=bool)[inv]
+
+
+_SDF_FIELDS = "yMdHmsS"
+
+
+def _parse_by_pattern(pat, v):
+    """SimpleDateFormat-style numeric pattern (TimeParsingExtractionFunctionSpec.timeFormat) -> epoch ms or None."""
+    rx, fields, i = "", [], 0
+    while i < len(pat):
+        c = pat[i]
+        if c == "'":
+            e = pat.index("'", i + 1)
+            rx += re.escape(pat[i + 1:e] or "'")
+            i = e + 1
+        elif c.isalpha():
+            run = len(pat[i:]) - len(pat[i:].lstrip(c))
+            if c not in _SDF_FIELDS:
+                raise NotImplementedError("pattern letter " + c)
+            nxt_field = i + run < len(pat) and pat[i + run].isalpha()
+            rx += "(\\d{%d})" % run if nxt_field else "(\\d+)"
+            fields.append((c, run))
+            i += run
+        else:
+            rx += re.escape(c)
+            i += 1
+    m = re.fullmatch(rx, v)
+    if not m:
+        return None
+    f = dict(y=1970, M=1, d=1, H=0, m=0, s=0, S=0)
+    for (c, run), g in zip(fields, m.groups()):
+        x = int(g)
+        if c == "y" and run == 2:
+            x += 2000 if x < 70 else 1900
+        f[c] = x
+    if not (1 <= f["M"] <= 12 and 1 <= f["d"] <= 31 and f["H"] <= 23 and f["m"] <= 59 and f["s"] <= 59):
+        return None
+    days = (_dt.date(f["y"], f["M"], 1) - _dt.date(1970, 1, 1)).days + f["d"] - 1
+    return days * 86400000 + f["H"] * 3600000 + f["m"] * 60000 + f["s"] * 1000 + f["S"]
+
+
+def extract_value(fn, v):
+    """Druid dimension extraction functions (DruidQuerySpec.scala:45-106) on one value; '' is null."""
+    t = fn["type"]
+    if t == "timeFormat":
+        return "" if v == "" else joda_format(fn.get("format", "yyyy-MM-dd'T'HH:mm:ss.SSS'Z'"), parse_instant(v), _tz_ms(fn.get("timeZone")))
+    if t == "time":
+        if v == "":
+            return ""
+        ms = _parse_by_pattern(fn["timeFormat"], v)
+        return v if ms is None else joda_format(fn["resultFormat"], ms, 0)
+    if t == "javascript":
+        params, body = js_subset.parse_function(fn["function"])
+        r = js_subset.evaluate(body, [v if v != "" else None])
+        return "" if r is None else js_subset.to_string(r)
+    if t == "lookup":
+        mp = fn["lookup"]["map"]
+        if v in mp:
+            return mp[v]
+        if fn.get("retainMissingValue"):
+            return v
+        return fn.get("replaceMissingValueWith") or ""
+    if t == "regex":
+        m = re.search(fn["expr"], v)
+        if m:
+            return m.group(1) if m.groups() else m.group(0)
+        return (fn.get("replaceMissingValueWith") or "") if fn.get("replaceMissingValue") else v
+    if t == "substring":
+        b = v.encode("utf-8")
+        i, n = int(fn.get("index", 0)), fn.get("length")
+        return (b[i:] if n is None else b[i:i + int(n)]).decode("utf-8", "replace")
+    if t == "upper":
+        return "".join(c.upper() if "a" <= c <= "z" else c for c in v)
+    if t == "lower":
+        return "".join(c.lower() if "A" <= c <= "Z" else c for c in v)
+    if t == "strlen":
+        return str(len(v.encode("utf-8")))
+    raise NotImplementedError(t)
 
 
 def _fsum_groups(values, gid, ng):
@@ -466,9 +553,18 @@ def execute(tbl, q, return_registers=False):
         decoders.append(("timestamp", lambda v: int(v)))
     for d in dims:
         name = d.get("outputName", d["dimension"])
-        if d.get("type", "default") == "extraction":
+        if d.get("type", "default") == "extraction" and d["dimension"] != "__time":
+            # extraction function on a dimension: a string -> string map of the distinct values (docs q8.json groups on
+            # timeFormat "yyyy" of o_orderdate); rows group on the mapped value, null = ""
+            vals, inv = tbl.dim_strings_of_unique(d["dimension"])
+            mapped = [extract_value(d["extractionFn"], v) for v in vals]
+            us = sorted(set(mapped), key=lambda s: s.encode("utf-8"))
+            rank = {s: i for i, s in enumerate(us)}
+            key_cols.append(np.array([rank[s] for s in mapped], dtype=np.int64)[inv][rows])
+            decoders.append((name, (lambda us_: lambda v: us_[int(v)])(us)))
+        elif d.get("type", "default") == "extraction":
             fn = d["extractionFn"]
-            assert fn["type"] == "timeFormat" and d["dimension"] == "__time"
+            assert fn["type"] == "timeFormat"
             tz = _tz_ms(fn.get("timeZone"))
             strs = [joda_format(fn["format"], int(t), tz) for t in ut]
             us = sorted(set(strs), key=lambda s: s.encode("utf-8"))
@@ -519,6 +615,24 @@ def execute(tbl, q, return_registers=False):
             regs = hll_registers(tbl, fld, sub_rows, sub_gid, ng)
             registers[name] = regs
             vals = [hll_estimate(regs[g]) for g in range(ng)]
+        elif t == "javascript" or "expression" in a:
+            # sum / min / max of an arithmetic expression over metrics, row value in IEEE double arithmetic
+            # (JavascriptAggregationSpec, DruidQuerySpec.scala:350-360; JSAggGenerator.scala:36-62)
+            if t == "javascript":
+                params, body = js_subset.parse_function(a["fnAggregate"])
+                fold, arg = js_subset.split_fold(params, body)
+                cols = [None] + [np.asarray(tbl.metrics[f])[sub_rows].astype(np.float64) for f in a["fieldNames"]]
+            else:
+                params, arg = js_subset.parse_expression(a["expression"])
+                fold = {"doubleSum": "sum", "doubleMin": "min", "doubleMax": "max"}[t]
+                cols = [np.asarray(tbl.metrics[f])[sub_rows].astype(np.float64) for f in params]
+            v = np.broadcast_to(js_subset.evaluate_numeric(arg, cols), (len(sub_rows),)).astype(np.float64)
+            if fold == "sum":
+                vals = _fsum_groups(v, sub_gid, ng)
+            else:
+                acc = np.full(ng, np.inf if fold == "min" else -np.inf)
+                (np.minimum if fold == "min" else np.maximum).at(acc, sub_gid, v)
+                vals = acc.tolist()
         else:
             col = np.asarray(tbl.metrics[a["fieldName"]])[sub_rows]
             if t == "longSum":

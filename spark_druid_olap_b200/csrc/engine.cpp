@@ -201,6 +201,16 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
       off_bits[i] = off;
       off = round_up(off + plan.leaves[i].bitset.size() * 4, 16);
     }
+  // id remaps of dimensions under an extraction function, in dev_dims order
+  std::vector<const PlanDim*> scan_dims;
+  for (auto& pd : plan.dims)
+    if (!pd.is_time) scan_dims.push_back(&pd);
+  std::vector<size_t> off_remap(scan_dims.size(), 0);
+  for (size_t i = 0; i < scan_dims.size(); i++)
+    if (!scan_dims[i]->remap.empty()) {
+      off_remap[i] = off;
+      off = round_up(off + scan_dims[i]->remap.size() * 4, 16);
+    }
   const size_t blob_bytes = off;
   ensure_pinned(&ctx->pinned_in, &ctx->pinned_in_bytes, blob_bytes);
   char* h = (char*)ctx->pinned_in;
@@ -224,6 +234,9 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   for (size_t i = 0; i < plan.leaves.size(); i++)
     if (plan.leaves[i].leaf.kind == LEAF_BITSET) memcpy(h + off_bits[i], plan.leaves[i].bitset.data(), plan.leaves[i].bitset.size() * 4);
 
+  for (size_t i = 0; i < scan_dims.size(); i++)
+    if (!scan_dims[i]->remap.empty()) memcpy(h + off_remap[i], scan_dims[i]->remap.data(), scan_dims[i]->remap.size() * 4);
+
   SDO_CUDA(cudaEventRecord(ctx->ev[0], s));
   SDO_CUDA(cudaMallocAsync(&st->blob, blob_bytes, s));
   SDO_CUDA(cudaMemcpyAsync(st->blob, h, blob_bytes, cudaMemcpyHostToDevice, s));
@@ -246,12 +259,17 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   p.n_ops = (int)plan.op_code.size();
   for (size_t i = 0; i < plan.op_code.size(); i++) { p.op_code[i] = plan.op_code[i]; p.op_arg[i] = plan.op_arg[i]; }
   p.n_dims = (int)plan.dev_dims.size();
-  for (size_t i = 0; i < plan.dev_dims.size(); i++) p.dims[i] = plan.dev_dims[i];
+  for (size_t i = 0; i < plan.dev_dims.size(); i++) {
+    p.dims[i] = plan.dev_dims[i];
+    if (!scan_dims[i]->remap.empty()) p.dims[i].remap = (const uint32_t*)(d + off_remap[i]);
+  }
   p.n_aggs = (int)plan.dev_aggs.size();
   for (size_t i = 0; i < plan.dev_aggs.size(); i++) {
     p.aggs[i] = plan.dev_aggs[i];
     if (p.aggs[i].op == AGG_HLL && p.aggs[i].hll_mode == HLL_LUT) p.aggs[i].hll_lut = ensure_hll_lut(ds, plan.hll_ds_dim[i], s);
   }
+  p.n_exprs = (int)plan.exprs.size();
+  for (size_t i = 0; i < plan.exprs.size(); i++) p.exprs[i] = plan.exprs[i];
   p.n_slots = plan.n_slots;
   p.n_hll = plan.n_hll;
   p.n_keys = plan.n_keys;
@@ -700,7 +718,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
           std::string val;
           const PlanDim& pd = plan.dims[0];
           if (pd.is_time) val = plan.time_keys[tk[r]].formatted[pd.time_fmt];
-          else if (plan.ds->dims[pd.ds_dim].enc == DimEncoding::Dict) val = plan.ds->dims[pd.ds_dim].dict->get(dim_ids[0][r]);
+          else if (auto dict = dim_dictionary(plan, pd)) val = dict->get(dim_ids[0][r]);
           else val = std::to_string(dim_ids[0][r]);
           int c = utf8_cmp(val.data(), val.size(), ps.data(), ps.size());
           if (desc ? c < 0 : c > 0) order[w++] = r;
@@ -791,9 +809,9 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
         }
         c.ids[i] = it->second;
       }
-    } else if (plan.ds->dims[pd.ds_dim].enc == DimEncoding::Dict) {
+    } else if (auto dict = dim_dictionary(plan, pd)) {
       c.type = SDO_RES_STRING;
-      c.dict = plan.ds->dims[pd.ds_dim].dict;
+      c.dict = dict;
       c.ids.resize(m);
       for (uint64_t i = 0; i < m; i++) c.ids[i] = dim_ids[d][order[i]];
     } else {
@@ -934,12 +952,11 @@ Result* Engine::finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st
     const int k = mp.n_dims++;
     mp.stride[k] = pd.stride;
     mp.card[k] = pd.card;
-    const DimMeta& dm = plan.ds->dims[pd.ds_dim];
-    if (dm.enc == DimEncoding::Dict) {
+    if (auto dict = dim_dictionary(plan, pd)) {
       mp.dim_is64[k] = 0;
       mp.dim_out[k] = dev_alloc(n * 4);
       add_column(pd.output_name, SDO_RES_STRING, mp.dim_out[k], n * 4);
-      res->columns.back().dict = dm.dict;
+      res->columns.back().dict = dict;
     } else {
       mp.dim_is64[k] = 1;
       mp.dim_out[k] = dev_alloc(n * 8);

@@ -107,6 +107,7 @@ std::string prelude(int strategy, const ScanParams& p) {
   s += "constexpr int n_dims = " + std::to_string(p.n_dims) + ";\n";
   s += table<int>("dim_width", p.n_dims, [&](int i) { return p.dims[i].width; });
   s += table<int>("dim_col", p.n_dims, [&](int i) { return p.dims[i].col; });
+  s += table<int>("dim_remap", p.n_dims, [&](int i) { return p.dims[i].remap != nullptr; });
   s += "constexpr int n_aggs = " + std::to_string(p.n_aggs) + ";\n";
   s += table<int>("agg_op", p.n_aggs, [&](int i) { return p.aggs[i].op; });
   s += table<int>("agg_col", p.n_aggs, [&](int i) { return p.aggs[i].col; });
@@ -117,6 +118,16 @@ std::string prelude(int strategy, const ScanParams& p) {
   s += table<int>("agg_hll_mode", p.n_aggs, [&](int i) { return p.aggs[i].hll_mode; });
   s += "constexpr int n_slots = " + std::to_string(p.n_slots) + ";\n";
   s += table<int>("slot_op", p.n_slots, [&](int i) { return p.slot_op[i]; });
+  s += table<int>("expr_n", p.n_exprs, [&](int i) { return p.exprs[i].n_ops; });
+  for (const char* which : {"expr_code", "expr_arg"}) {
+    s += std::string("constexpr int ") + which + "[" + std::to_string(p.n_exprs + 1) + "][" + std::to_string(MAX_EXPR_OPS) + "] = {";
+    for (int e = 0; e < p.n_exprs; e++) {
+      s += "{";
+      for (int k = 0; k < MAX_EXPR_OPS; k++) s += std::to_string(k < p.exprs[e].n_ops ? (which[5] == 'c' ? p.exprs[e].code[k] : p.exprs[e].arg[k]) : 0) + ",";
+      s += "},";
+    }
+    s += "{0}};\n";
+  }
   s += "constexpr int n_hll = " + std::to_string(p.n_hll) + ";\n";
   s += "constexpr int hll_place = " + std::to_string(p.hll_mode) + ";\n";
   s += "constexpr int ignore_key_base = " + std::to_string(p.ignore_key_base) + ";\n";

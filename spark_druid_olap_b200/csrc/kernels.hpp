@@ -23,6 +23,10 @@ constexpr int MAX_OPS = 32;
 constexpr int MAX_DIMS = 8;
 constexpr int MAX_AGGS = 16;
 constexpr int MAX_SLOTS = MAX_AGGS + 1;
+constexpr int MAX_EXPRS = 8;        // aggregations whose argument is an arithmetic expression over metrics
+constexpr int MAX_EXPR_OPS = 24;
+constexpr int MAX_EXPR_CONSTS = 8;
+constexpr int EXPR_STACK = 6;
 constexpr int SCAN_THREADS = 256;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int UNIT_ROWS = SCAN_THREADS * ROWS_PER_THREAD * 4;  // 4096 rows: one pass of a block (4 vectors per thread)
@@ -52,6 +56,7 @@ struct DevDim {
   int32_t col;
   int32_t width;
   uint64_t stride;
+  const uint32_t* remap;  // extraction function on the dimension: id -> id of the extracted value (else null)
 };
 
 // how a row value reaches its 8-byte slot
@@ -70,6 +75,26 @@ enum AggOp : int32_t {
   AGG_MAX_F64_I64 = 11,
   AGG_MIN_I64_F64 = 12,
   AGG_MAX_I64_F64 = 13,
+  AGG_SUM_EXPR = 14,    // doubleSum / doubleMin / doubleMax of an arithmetic expression over metric columns
+  AGG_MIN_EXPR = 15,    // (col = index into ScanParams::exprs)
+  AGG_MAX_EXPR = 16,
+};
+// postfix program over doubles: the argument of a JavascriptAggregationSpec's fnAggregate (JSAggGenerator.scala:36-62)
+// or of an aggregator's `expression` attribute.  Evaluated per row with IEEE round-to-nearest operations and no
+// multiply-add contraction, so a row's value is the one a CPU computes.
+enum ExprOp : uint8_t {
+  EX_COL_F64 = 0,  // arg = column slot in the segptr row
+  EX_COL_I64 = 1,  // int64 metric, converted to double (JavaScript numbers are doubles)
+  EX_CONST = 2,    // arg = index into consts
+  EX_ADD = 3, EX_SUB = 4, EX_MUL = 5, EX_DIV = 6, EX_NEG = 7, EX_ABS = 8, EX_MIN = 9, EX_MAX = 10, EX_FLOOR = 11,
+  EX_CEIL = 12, EX_SQRT = 13, EX_MOD = 14,
+};
+struct DevExpr {
+  int32_t n_ops;
+  int32_t pad;
+  uint8_t code[MAX_EXPR_OPS];
+  uint8_t arg[MAX_EXPR_OPS];
+  double consts[MAX_EXPR_CONSTS];
 };
 // how two partial slots merge (PostAggregate.scala:39-60: count/sum -> sum, min -> min, max -> max)
 enum SlotOp : int32_t { SLOT_SUM_I64 = 0, SLOT_SUM_F64 = 1, SLOT_MIN_I64 = 2, SLOT_MAX_I64 = 3 };
@@ -131,7 +156,8 @@ struct ScanParams {
   unsigned long long* hkeys;    // HASH: bucket array base (== table); bucket h starts at hkeys + h * hstride
   uint64_t hmask;               // HASH: cap - 1
   uint32_t hstride;             // HASH: words per bucket
-  uint32_t pad1;
+  int32_t n_exprs;
+  DevExpr exprs[MAX_EXPRS];
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 

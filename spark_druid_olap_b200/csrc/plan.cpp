@@ -4,6 +4,7 @@
 #include <cmath>
 #include <functional>
 #include <map>
+#include <numeric>
 #include <regex>
 #include <set>
 
@@ -211,6 +212,7 @@ struct Compiler {
         case FilterNode::In: return constant(std::find(f.values.begin(), f.values.end(), std::string()) != f.values.end());
         case FilterNode::Bound: return constant(bound_pred(f, "", 0));
         case FilterNode::Contains: return constant(f.value.empty());
+        case FilterNode::Javascript: return constant(minijs::truthy(minijs::eval(*f.js->body, {minijs::Value::null()})));
         case FilterNode::Regex: {
           std::regex re;
           try { re = std::regex(f.value, std::regex::ECMAScript); } catch (const std::regex_error&) { throw Invalid("bad regex '" + f.value + "'"); }
@@ -278,6 +280,14 @@ struct Compiler {
           return std::search(p, p + n, needle.begin(), needle.end()) != p + n;
         });
       }
+      case FilterNode::Javascript: {
+        // Druid hands the function the dimension value, null for the empty value (JavascriptFilterSpec,
+        // DruidQuerySpec.scala:218-236); one evaluation per dictionary entry, rows then test an id bitset
+        const minijs::Node* body = f.js->body.get();
+        return predicate_node(di, [body](const char* p, size_t n) {
+          return minijs::truthy(minijs::eval(*body, {n ? minijs::Value::string(std::string(p, n)) : minijs::Value::null()}));
+        });
+      }
       case FilterNode::Regex: {
         // Druid's regex filter is java.util.regex Pattern.matcher(v).find(); std::regex ECMAScript
         // covers the common subset (classes, anchors, alternation, quantifiers).
@@ -333,6 +343,135 @@ std::vector<Interval> normalise(std::vector<Interval> v) {
   return o;
 }
 
+// ---- extraction functions on dimensions ----------------------------------------------------------------------------
+// Parse `v` by a SimpleDateFormat-style pattern of numeric fields (y M d H m s S), quoted text and literal characters
+// (TimeParsingExtractionFunctionSpec.timeFormat, DruidQuerySpec.scala:82-88).  A run of n pattern letters reads n
+// digits, or as many as there are when the next pattern character is not a letter.
+bool parse_by_pattern(const std::string& pat, const char* v, size_t nv, int64_t* out_ms) {
+  int64_t f[7] = {1970, 1, 1, 0, 0, 0, 0};  // y M d H m s S
+  size_t i = 0, k = 0;
+  while (i < pat.size()) {
+    const char c = pat[i];
+    if (c == '\'') {
+      size_t e = pat.find('\'', i + 1);
+      if (e == std::string::npos) throw Invalid("time extraction: unterminated quote in '" + pat + "'");
+      const size_t n = e - i - 1;
+      if (n == 0) { if (k >= nv || v[k] != '\'') return false; k++; }
+      else { if (k + n > nv || memcmp(v + k, pat.data() + i + 1, n) != 0) return false; k += n; }
+      i = e + 1;
+      continue;
+    }
+    if (!isalpha((unsigned char)c)) {
+      if (k >= nv || v[k] != c) return false;
+      i++; k++;
+      continue;
+    }
+    size_t run = 1;
+    while (i + run < pat.size() && pat[i + run] == c) run++;
+    const char* which = strchr("yMdHmsS", c);
+    if (!which) throw Unsupported(std::string("time extraction: pattern letter '") + c + "'");
+    const bool next_is_field = i + run < pat.size() && isalpha((unsigned char)pat[i + run]);
+    size_t digits = 0;
+    int64_t val = 0;
+    while (k < nv && isdigit((unsigned char)v[k]) && (!next_is_field || digits < run)) { val = val * 10 + (v[k] - '0'); k++; digits++; }
+    if (!digits) return false;
+    if (c == 'y' && run == 2) val += val < 70 ? 2000 : 1900;
+    f[which - "yMdHmsS"] = val;
+    i += run;
+  }
+  if (k != nv || f[1] < 1 || f[1] > 12 || f[2] < 1 || f[2] > 31 || f[3] > 23 || f[4] > 59 || f[5] > 59) return false;
+  *out_ms = days_from_civil(f[0], (int)f[1], (int)f[2]) * MS_DAY + f[3] * 3600000ll + f[4] * 60000ll + f[5] * 1000ll + f[6];
+  return true;
+}
+
+// the value a dimension's extraction function yields for one dictionary value ("" = null)
+struct Extractor {
+  const ExtractionFn& fn;
+  int64_t tz = 0;
+  std::regex re;
+  explicit Extractor(const ExtractionFn& f) : fn(f) {
+    if (fn.kind == ExtractionFn::TimeFormat) tz = tz_offset_ms(fn.time_zone);
+    if (fn.kind == ExtractionFn::Regex) {
+      try { re = std::regex(fn.expr, std::regex::ECMAScript | std::regex::optimize); } catch (const std::regex_error&) { throw Invalid("bad regex '" + fn.expr + "'"); }
+    }
+  }
+  std::string operator()(const char* p, size_t n) const {
+    switch (fn.kind) {
+      case ExtractionFn::TimeFormat: {
+        // Druid reads the dimension value as an ISO-8601 instant; null stays null
+        if (!n) return std::string();
+        int64_t ms;
+        try { ms = parse_iso_instant(std::string(p, n)); } catch (const Invalid&) { throw Invalid("timeFormat extraction: dimension value '" + std::string(p, n) + "' is not an ISO-8601 instant"); }
+        return joda_format(fn.format, ms, tz);
+      }
+      case ExtractionFn::TimeParse: {
+        int64_t ms;
+        if (!n) return std::string();
+        if (!parse_by_pattern(fn.parse_format, p, n, &ms)) return std::string(p, n);  // Druid passes unparseable values through
+        return joda_format(fn.format, ms, 0);
+      }
+      case ExtractionFn::Javascript: {
+        minijs::Value v = minijs::eval(*fn.js->body, {n ? minijs::Value::string(std::string(p, n)) : minijs::Value::null()});
+        return v.kind == minijs::Value::Null ? std::string() : minijs::to_string(v);
+      }
+      case ExtractionFn::Lookup: {
+        for (auto& kv : fn.lookup)
+          if (kv.first.size() == n && memcmp(kv.first.data(), p, n) == 0) return kv.second;
+        if (fn.retain_missing) return std::string(p, n);
+        return fn.has_replace_missing ? fn.replace_missing : std::string();
+      }
+      case ExtractionFn::Regex: {
+        std::cmatch m;
+        if (std::regex_search(p, p + n, m, re)) return m.size() > 1 ? m[1].str() : m[0].str();
+        return fn.has_replace_missing ? fn.replace_missing : std::string(p, n);
+      }
+      case ExtractionFn::Substring: {
+        if ((size_t)fn.index >= n) return std::string();
+        size_t len = fn.length < 0 ? n - (size_t)fn.index : std::min<size_t>((size_t)fn.length, n - (size_t)fn.index);
+        return std::string(p + fn.index, len);
+      }
+      case ExtractionFn::Upper: case ExtractionFn::Lower: {
+        std::string o(p, n);  // ASCII letters
+        for (char& c : o) c = (char)(fn.kind == ExtractionFn::Upper ? (c >= 'a' && c <= 'z' ? c - 32 : c) : (c >= 'A' && c <= 'Z' ? c + 32 : c));
+        return o;
+      }
+      case ExtractionFn::Strlen: return std::to_string(n);
+      default: break;
+    }
+    return std::string(p, n);
+  }
+};
+
+void build_extraction(const DimMeta& dm, const ExtractionFn& fn, PlanDim* pd) {
+  const uint64_t card = (uint64_t)std::max<int64_t>(1, dm.cardinality);
+  if (dm.enc == DimEncoding::Direct && card > (1ull << 27))
+    throw Unsupported("extraction function on integer dimension '" + dm.name + "' with " + std::to_string(card) + " ids");
+  Extractor ex(fn);
+  std::vector<std::string> vals(card);
+  char buf[24];
+  for (uint64_t id = 0; id < card; id++) {
+    if (dm.enc == DimEncoding::Dict) vals[id] = id < (uint64_t)dm.dict->size() ? ex(dm.dict->data((int64_t)id), dm.dict->len((int64_t)id)) : std::string();
+    else {
+      int n = snprintf(buf, sizeof buf, "%llu", (unsigned long long)id);
+      vals[id] = ex(buf, (size_t)n);
+    }
+  }
+  std::vector<uint32_t> order(card);
+  std::iota(order.begin(), order.end(), 0u);
+  std::sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) {
+    int c = utf8_cmp(vals[a].data(), vals[a].size(), vals[b].data(), vals[b].size());
+    return c ? c < 0 : a < b;
+  });
+  pd->derived = std::make_shared<Dictionary>();
+  pd->remap.resize(card);
+  for (uint64_t k = 0; k < card; k++) {
+    const std::string& v = vals[order[k]];
+    if (k == 0 || v != vals[order[k - 1]]) pd->derived->push(v.data(), v.size());
+    pd->remap[order[k]] = (uint32_t)(pd->derived->size() - 1);
+  }
+  pd->card = (uint64_t)pd->derived->size();
+}
+
 }  // namespace
 
 Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const PlanOptions& opt) {
@@ -349,8 +488,18 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   for (auto& d : spec.dimensions) {
     PlanDim pd;
     pd.output_name = d.output_name;
+    if (d.fn.kind != ExtractionFn::None && d.dimension != "__time") {
+      // extraction function on a dimension (q8.json: timeFormat "yyyy" of o_orderdate): a string -> string map applied
+      // to the dictionary; rows then group on the id of the mapped value
+      pd.ds_dim = ds.dim_index(d.dimension);
+      if (pd.ds_dim < 0) throw NotFound("unknown dimension '" + d.dimension + "' in datasource '" + ds.name + "'");
+      build_extraction(ds.dims[pd.ds_dim], d.fn, &pd);
+      plan.dims.push_back(pd);
+      continue;
+    }
+    if (d.fn.kind != ExtractionFn::None && d.fn.kind != ExtractionFn::TimeFormat)
+      throw Unsupported("only the timeFormat extraction applies to __time");
     if (d.fn.kind == ExtractionFn::TimeFormat) {
-      if (d.dimension != "__time") throw Unsupported("timeFormat extraction on non-time dimension '" + d.dimension + "'");
       pd.is_time = true;
       pd.time_fmt = (int)time_fmts.size();
       time_fmts.emplace_back(d.fn.format, tz_offset_ms(d.fn.time_zone));
@@ -430,6 +579,50 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
       case AggregationSpec::LongSum: case AggregationSpec::DoubleSum:
       case AggregationSpec::LongMin: case AggregationSpec::LongMax:
       case AggregationSpec::DoubleMin: case AggregationSpec::DoubleMax: {
+        if (a.has_expr) {
+          // argument = arithmetic over metric columns (JSAggGenerator.scala:36-62 / `expression`): its postfix program
+          // goes to the kernel with parameters resolved to column slots
+          if (plan.exprs.size() >= (size_t)MAX_EXPRS) throw Unsupported("more than " + std::to_string(MAX_EXPRS) + " expression aggregations");
+          if (a.expr.code.size() > (size_t)MAX_EXPR_OPS || a.expr.consts.size() > (size_t)MAX_EXPR_CONSTS || a.expr.max_depth > EXPR_STACK)
+            throw Unsupported("aggregation '" + a.name + "': expression too long for the device evaluator");
+          DevExpr ex{};
+          ex.n_ops = (int32_t)a.expr.code.size();
+          for (size_t k = 0; k < a.expr.consts.size(); k++) ex.consts[k] = a.expr.consts[k];
+          for (size_t k = 0; k < a.expr.code.size(); k++) {
+            const uint8_t code = a.expr.code[k], arg = a.expr.arg[k];
+            if (code == minijs::N_PUSH_PARAM) {
+              if (arg >= a.fields.size()) throw Invalid("aggregation '" + a.name + "': expression parameter without a field");
+              const std::string& fld = a.fields[arg];
+              int mi = ds.metric_index(fld);
+              if (mi < 0) {
+                if (ds.dim_index(fld) >= 0) throw Unsupported("aggregation '" + a.name + "': dimension '" + fld + "' in an arithmetic expression");
+                throw NotFound("unknown metric '" + fld + "' in datasource '" + ds.name + "'");
+              }
+              ex.code[k] = ds.metrics[mi].is_float ? EX_COL_F64 : EX_COL_I64;
+              ex.arg[k] = (uint8_t)cc.column_slot(true, mi);
+            } else if (code == minijs::N_PUSH_CONST) {
+              ex.code[k] = EX_CONST;
+              ex.arg[k] = arg;
+            } else {
+              static const uint8_t map[] = {0, 0, EX_ADD, EX_SUB, EX_MUL, EX_DIV, EX_NEG, EX_ABS, EX_MIN, EX_MAX, EX_FLOOR, EX_CEIL, EX_SQRT, EX_MOD};
+              ex.code[k] = map[code];
+              ex.arg[k] = 0;
+            }
+          }
+          pa.out_float = true;
+          da.col = (int32_t)plan.exprs.size();
+          plan.exprs.push_back(ex);
+          if (a.kind == AggregationSpec::DoubleSum) {
+            da.op = AGG_SUM_EXPR;
+            pa.slot = da.slot = new_slot(SLOT_SUM_F64, 0);
+          } else {
+            const bool is_min = a.kind == AggregationSpec::DoubleMin;
+            da.op = is_min ? AGG_MIN_EXPR : AGG_MAX_EXPR;
+            pa.slot_is_f64_ord = true;
+            pa.slot = da.slot = new_slot(is_min ? SLOT_MIN_I64 : SLOT_MAX_I64, is_min ? (uint64_t)INT64_MAX : (uint64_t)INT64_MIN);
+          }
+          break;
+        }
         int mi = ds.metric_index(a.field);
         if (mi < 0) throw NotFound("unknown metric '" + a.field + "' in datasource '" + ds.name + "'");
         const MetricMeta& mm = ds.metrics[mi];
@@ -590,6 +783,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
     dd.col = cc.column_slot(false, pd.ds_dim);
     dd.width = ds.dims[pd.ds_dim].width;
     dd.stride = pd.stride;
+    dd.remap = nullptr;  // run_scan points it at the uploaded copy of pd.remap
     if ((int)plan.dev_dims.size() >= MAX_DIMS) throw Unsupported("more than 8 grouping dimensions");
     plan.dev_dims.push_back(dd);
   }

@@ -25,6 +25,10 @@ struct PlanDim {
   int time_fmt = -1;      // index into TimeKey::formatted (time)
   uint64_t card = 1;
   uint64_t stride = 1;
+  // extraction function on a dimension: rows group on remap[source id], an id of `derived` (sorted, like a datasource
+  // dictionary); both are built per query from the dictionary, not from rows
+  std::shared_ptr<Dictionary> derived;
+  std::vector<uint32_t> remap;
 };
 
 struct PlanAgg {
@@ -67,6 +71,7 @@ struct Plan {
   std::vector<DevDim> dev_dims;     // non-time dims
   std::vector<PlanAgg> aggs;        // in spec order
   std::vector<DevAgg> dev_aggs;
+  std::vector<DevExpr> exprs;       // argument programs of AGG_*_EXPR aggregations (DevAgg::col indexes this)
   std::vector<int> hll_ds_dim;      // per dev agg with AGG_HLL and HLL_LUT: datasource dim whose LUT is needed (-1 otherwise)
   std::vector<TimeKey> time_keys;   // index = time key id
   bool has_time_key = false;
@@ -93,6 +98,13 @@ struct PlanOptions {
   uint64_t hll_max_bytes = 8ull << 30;
   int64_t jit_min_rows = 2000000;               // scans at least this long get a shape-specialised kernel
 };
+
+// dictionary the ids of a non-time output dimension refer to; null for integer dimensions (id = value)
+inline std::shared_ptr<Dictionary> dim_dictionary(const Plan& p, const PlanDim& pd) {
+  if (pd.derived) return pd.derived;
+  const DimMeta& dm = p.ds->dims[pd.ds_dim];
+  return dm.enc == DimEncoding::Dict ? dm.dict : nullptr;
+}
 
 Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds, const PlanOptions& opt);
 std::string explain_json(const Plan& p);

@@ -48,6 +48,7 @@ namespace sdo {
 #define Q_N_DIMS jit::n_dims
 #define Q_DIM_WIDTH(d) jit::dim_width[d]
 #define Q_DIM_COL(d) jit::dim_col[d]
+#define Q_DIM_REMAP(d) jit::dim_remap[d]
 #define Q_N_AGGS jit::n_aggs
 #define Q_AGG_OP(a) jit::agg_op[a]
 #define Q_AGG_COL(a) jit::agg_col[a]
@@ -62,6 +63,9 @@ namespace sdo {
 #define Q_IGNORE_KEY_BASE jit::ignore_key_base
 #define Q_N_COLS jit::n_cols
 #define Q_SLOT_OP(s) jit::slot_op[s]
+#define Q_EXPR_N(e) jit::expr_n[e]
+#define Q_EXPR_CODE(e, k) jit::expr_code[e][k]
+#define Q_EXPR_ARG(e, k) jit::expr_arg[e][k]
 #else
 #define Q_UNROLL
 #define Q_N_OPS p.n_ops
@@ -73,6 +77,7 @@ namespace sdo {
 #define Q_N_DIMS p.n_dims
 #define Q_DIM_WIDTH(d) p.dims[d].width
 #define Q_DIM_COL(d) p.dims[d].col
+#define Q_DIM_REMAP(d) (p.dims[d].remap != nullptr)
 #define Q_N_AGGS p.n_aggs
 #define Q_AGG_OP(a) p.aggs[a].op
 #define Q_AGG_COL(a) p.aggs[a].col
@@ -87,6 +92,9 @@ namespace sdo {
 #define Q_IGNORE_KEY_BASE p.ignore_key_base
 #define Q_N_COLS p.n_cols
 #define Q_SLOT_OP(s) p.slot_op[s]
+#define Q_EXPR_N(e) p.exprs[e].n_ops
+#define Q_EXPR_CODE(e, k) p.exprs[e].code[k]
+#define Q_EXPR_ARG(e, k) p.exprs[e].arg[k]
 #endif
 
 constexpr int VECS = UNIT_ROWS / (SCAN_THREADS * ROWS_PER_THREAD);  // vectors per thread per unit
@@ -387,6 +395,51 @@ __device__ __forceinline__ long long warp_max(long long v) {
   return v;
 }
 
+// Argument expression `e` of an AGG_*_EXPR aggregation for N consecutive rows: a postfix program over metric columns and
+// constants.  Round-to-nearest intrinsics keep the compiler from contracting a * b + c into one fused operation, so each
+// row's value is bit-identical to the CPU's.  With the program spelled out as constants (JIT) the loop unrolls and the
+// stack lives in registers; the interpreter (AOT) indexes it dynamically.
+template <int N>
+__device__ __forceinline__ void eval_expr(const ScanParams& p, int e, const void* const* cols, uint32_t r0, double (&out)[N]) {
+  double st[EXPR_STACK][N];
+  int sp = 0;
+  Q_UNROLL
+  for (int k = 0; k < Q_EXPR_N(e); k++) {
+    const int op = Q_EXPR_CODE(e, k), arg = Q_EXPR_ARG(e, k);
+    if (op == EX_COL_F64) {
+      load_f64<N>(cols[arg], r0, st[sp]);
+      sp++;
+    } else if (op == EX_COL_I64) {
+      long long v[N];
+      load_i64<N>(cols[arg], r0, v);
+#pragma unroll
+      for (int i = 0; i < N; i++) st[sp][i] = (double)v[i];
+      sp++;
+    } else if (op == EX_CONST) {
+      const double c = p.exprs[e].consts[arg];
+#pragma unroll
+      for (int i = 0; i < N; i++) st[sp][i] = c;
+      sp++;
+    } else if (op == EX_NEG || op == EX_ABS || op == EX_FLOOR || op == EX_CEIL || op == EX_SQRT) {
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double x = st[sp - 1][i];
+        st[sp - 1][i] = op == EX_NEG ? -x : op == EX_ABS ? fabs(x) : op == EX_FLOOR ? floor(x) : op == EX_CEIL ? ceil(x) : __dsqrt_rn(x);
+      }
+    } else {
+      sp--;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double x = st[sp - 1][i], y = st[sp][i];
+        st[sp - 1][i] = op == EX_ADD ? __dadd_rn(x, y) : op == EX_SUB ? __dsub_rn(x, y) : op == EX_MUL ? __dmul_rn(x, y)
+                        : op == EX_DIV ? __ddiv_rn(x, y) : op == EX_MIN ? fmin(x, y) : op == EX_MAX ? fmax(x, y) : fmod(x, y);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < N; i++) out[i] = st[0][i];
+}
+
 // Aggregate N consecutive rows starting at r0 (N = 4: vector loads; N = 1: scalar loads); m = which rows.
 // WARP = called by all 32 lanes together (lanes without rows pass m = 0): lets a warp whose surviving
 // rows all share one key (time buckets, sorted low-cardinality keys) fold them with shuffles and
@@ -402,6 +455,11 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
   for (int d = 0; d < Q_N_DIMS; d++) {
     uint32_t ids[N];
     load_ids<N>(cols[Q_DIM_COL(d)], Q_DIM_WIDTH(d), r0, ids);
+    if (Q_DIM_REMAP(d)) {
+      const uint32_t* lut = p.dims[d].remap;
+#pragma unroll
+      for (int i = 0; i < N; i++) ids[i] = __ldg(lut + ids[i]);
+    }
     const key_t stride = (key_t)p.dims[d].stride;
 #pragma unroll
     for (int i = 0; i < N; i++) key[i] += (key_t)ids[i] * stride;
@@ -454,7 +512,7 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
       if (!WARP && !ma) continue;
     }
     const int so = Q_AGG_SLOT(a) * Acc<STRAT>::SLOT_STRIDE;
-    const void* col = cols[Q_AGG_COL(a)];
+    const void* col = Q_AGG_OP(a) >= AGG_SUM_EXPR ? nullptr : cols[Q_AGG_COL(a)];  // *_EXPR: col is an expression index
 #define SDO_ROWS(EXPR)                                     \
   _Pragma("unroll") for (int i = 0; i < N; i++) {          \
     if ((ma >> i) & 1u) {                                  \
@@ -505,6 +563,9 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
       case AGG_SUM_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_SUMI((long long)v[i]) break; }
       case AGG_MIN_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MINI((long long)v[i]) break; }
       case AGG_MAX_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MAXI((long long)v[i]) break; }
+      case AGG_SUM_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_SUMF(v[i]) break; }
+      case AGG_MIN_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
+      case AGG_MAX_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
       case AGG_HLL: {
         uint32_t ids[N];
         load_ids<N>(col, Q_AGG_WIDTH(a), r0, ids);

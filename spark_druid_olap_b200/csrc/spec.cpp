@@ -1,5 +1,8 @@
 #include "spec.hpp"
 
+#include <algorithm>
+#include <limits>
+
 namespace sdo {
 namespace {
 
@@ -75,8 +78,17 @@ FilterNode parse_filter(const Json& j) {
     f.fields.push_back(parse_filter(*c));
   } else if (t == "noop") {
     f.kind = FilterNode::True;
-  } else if (t == "javascript" || t == "spatial") {
-    // JavascriptFilterSpec :218-236, SpatialFilterSpec :270-281 -- out of scope; the caller falls back to Spark
+  } else if (t == "javascript") {
+    // JavascriptFilterSpec :218-236.  The expression subset of minijs.hpp is evaluated once per dictionary entry at
+    // plan time; functions outside it raise Unsupported and the caller falls back to Spark.
+    f.kind = FilterNode::Javascript;
+    f.dimension = req_str(j, "dimension", "javascript filter");
+    f.value = req_str(j, "function", "javascript filter");
+    auto fn = std::make_shared<minijs::Function>(minijs::parse_function(f.value));
+    if (fn->params.size() != 1) throw Invalid("javascript filter: the function must take exactly one parameter");
+    f.js = fn;
+  } else if (t == "spatial") {
+    // SpatialFilterSpec :270-281 -- out of scope; the caller falls back to Spark
     throw Unsupported("filter type '" + t + "' is not supported by the GPU engine");
   } else {
     throw Unsupported("unknown filter type '" + t + "'");
@@ -97,11 +109,51 @@ DimensionSpec parse_dimension(const Json& j) {
     const Json* fn = j.find("extractionFn");
     if (!fn) throw Invalid("extraction dimension: 'extractionFn' missing");
     std::string ft = fn->get_str("type");
-    if (ft != "timeFormat") throw Unsupported("extraction function '" + ft + "' is not supported");
-    d.fn.kind = ExtractionFn::TimeFormat;
-    d.fn.format = fn->get_str("format", "yyyy-MM-dd'T'HH:mm:ss.SSS'Z'");
-    d.fn.time_zone = fn->get_str("timeZone", "");
-    d.fn.locale = fn->get_str("locale", "");
+    if (ft == "timeFormat") {
+      d.fn.kind = ExtractionFn::TimeFormat;
+      d.fn.format = fn->get_str("format", "yyyy-MM-dd'T'HH:mm:ss.SSS'Z'");
+      d.fn.time_zone = fn->get_str("timeZone", "");
+      d.fn.locale = fn->get_str("locale", "");
+    } else if (ft == "time") {
+      // TimeParsingExtractionFunctionSpec, DruidQuerySpec.scala:82-88
+      d.fn.kind = ExtractionFn::TimeParse;
+      d.fn.parse_format = req_str(*fn, "timeFormat", "time extraction");
+      d.fn.format = req_str(*fn, "resultFormat", "time extraction");
+    } else if (ft == "javascript") {
+      // JavaScriptExtractionFunctionSpec, DruidQuerySpec.scala:90-96
+      d.fn.kind = ExtractionFn::Javascript;
+      auto f = std::make_shared<minijs::Function>(minijs::parse_function(req_str(*fn, "function", "javascript extraction")));
+      if (f->params.size() != 1) throw Invalid("javascript extraction: the function must take exactly one parameter");
+      d.fn.js = f;
+    } else if (ft == "lookup") {
+      const Json* lk = fn->find("lookup");
+      const Json* mp = lk ? lk->find("map") : nullptr;
+      if (!mp || !mp->is_obj()) throw Invalid("lookup extraction: lookup.map missing");
+      d.fn.kind = ExtractionFn::Lookup;
+      for (auto& kv : mp->obj) d.fn.lookup.emplace_back(kv.first, kv.second.is_str() ? kv.second.str : std::string());
+      d.fn.retain_missing = fn->get_bool("retainMissingValue", false);
+      if (fn->has("replaceMissingValueWith") && !fn->find("replaceMissingValueWith")->is_null()) {
+        d.fn.has_replace_missing = true;
+        d.fn.replace_missing = fn->get_str("replaceMissingValueWith");
+      }
+      if (d.fn.retain_missing && d.fn.has_replace_missing) throw Invalid("lookup extraction: retainMissingValue and replaceMissingValueWith exclude each other");
+    } else if (ft == "regex") {
+      d.fn.kind = ExtractionFn::Regex;
+      d.fn.expr = req_str(*fn, "expr", "regex extraction");
+      if (fn->get_bool("replaceMissingValue", false)) {
+        d.fn.has_replace_missing = true;
+        d.fn.replace_missing = fn->get_str("replaceMissingValueWith", "");
+      }
+    } else if (ft == "substring") {
+      d.fn.kind = ExtractionFn::Substring;
+      d.fn.index = (int64_t)fn->get_num("index", 0);
+      d.fn.length = fn->has("length") && !fn->find("length")->is_null() ? (int64_t)fn->get_num("length", 0) : -1;
+      if (d.fn.index < 0 || (fn->has("length") && d.fn.length < 0 && !fn->find("length")->is_null())) throw Invalid("substring extraction: negative index or length");
+    } else if (ft == "upper" || ft == "lower" || ft == "strlen") {
+      d.fn.kind = ft == "upper" ? ExtractionFn::Upper : ft == "lower" ? ExtractionFn::Lower : ExtractionFn::Strlen;
+    } else {
+      throw Unsupported("extraction function '" + ft + "' is not supported");
+    }
     return d;
   }
   throw Unsupported("dimension spec type '" + t + "' is not supported");
@@ -135,9 +187,56 @@ AggregationSpec parse_aggregation(const Json& j) {
   for (auto& f : fn)
     if (t == f.n) {
       a.kind = f.k;
+      if (j.has("expression")) {
+        // sum / min / max of an arithmetic expression over metrics (the attribute later Druid versions give these
+        // aggregators); same numeric program as a javascript aggregator
+        if (f.k != AggregationSpec::DoubleSum && f.k != AggregationSpec::DoubleMin && f.k != AggregationSpec::DoubleMax)
+          throw Unsupported("aggregation '" + a.name + "': 'expression' is supported on doubleSum / doubleMin / doubleMax");
+        minijs::Function fn = minijs::parse_expression(req_str(j, "expression", "aggregation"));
+        if (fn.params.empty()) throw Unsupported("aggregation '" + a.name + "': the expression mentions no column");
+        a.has_expr = true;
+        a.expr = minijs::compile_numeric(*fn.body);
+        a.fields = fn.params;
+        return a;
+      }
       a.field = req_str(j, "fieldName", "aggregation");
       return a;
     }
+  if (t == "javascript") {
+    // JavascriptAggregationSpec, DruidQuerySpec.scala:350-360; what JSAggGenerator.scala:36-119 emits for
+    // SUM / MIN / MAX of an expression: fnAggregate(current, f1, f2, ...) folds an arithmetic expression of the fields
+    // into `current`, fnCombine and fnReset are the matching merge and identity.
+    const Json* fs = j.find("fieldNames");
+    if (!fs || !fs->is_arr() || fs->arr.empty()) throw Invalid("javascript aggregation: 'fieldNames' missing");
+    minijs::Function agg = minijs::parse_function(req_str(j, "fnAggregate", "javascript aggregation"));
+    if (agg.params.size() != fs->arr.size() + 1) throw Invalid("javascript aggregation '" + a.name + "': fnAggregate must take `current` plus one parameter per field");
+    minijs::Fold fold;
+    std::unique_ptr<minijs::Node> arg = minijs::split_fold(&agg, &fold);
+    a.kind = fold == minijs::Fold::Sum ? AggregationSpec::DoubleSum : fold == minijs::Fold::Min ? AggregationSpec::DoubleMin : AggregationSpec::DoubleMax;
+    // fnCombine / fnReset must be the merge and identity of the same fold
+    minijs::Function comb = minijs::parse_function(req_str(j, "fnCombine", "javascript aggregation"));
+    minijs::Function reset = minijs::parse_function(req_str(j, "fnReset", "javascript aggregation"));
+    if (comb.params.size() != 2 || !reset.params.empty()) throw Invalid("javascript aggregation '" + a.name + "': fnCombine takes two partials, fnReset none");
+    const double inf = std::numeric_limits<double>::infinity();
+    struct Probe { double a, b; } probes[] = {{3.5, -2.25}, {-7.0, 11.0}};
+    for (auto& pr : probes) {
+      double got = minijs::to_number(minijs::eval(*comb.body, {minijs::Value::number(pr.a), minijs::Value::number(pr.b)}));
+      double want = fold == minijs::Fold::Sum ? pr.a + pr.b : fold == minijs::Fold::Min ? std::min(pr.a, pr.b) : std::max(pr.a, pr.b);
+      if (got != want) throw Unsupported("javascript aggregation '" + a.name + "': fnCombine is not the merge of fnAggregate's fold");
+    }
+    double r0 = minijs::to_number(minijs::eval(*reset.body, {}));
+    if (r0 != (fold == minijs::Fold::Sum ? 0.0 : fold == minijs::Fold::Min ? inf : -inf))
+      throw Unsupported("javascript aggregation '" + a.name + "': fnReset is not the identity of fnAggregate's fold");
+    a.has_expr = true;
+    a.expr = minijs::compile_numeric(*arg);
+    for (auto& f : fs->arr) {
+      if (!f.is_str()) throw Invalid("javascript aggregation: fieldNames must be strings");
+      a.fields.push_back(f.str);
+    }
+    for (size_t k = 0; k < a.expr.code.size(); k++)
+      if (a.expr.code[k] == minijs::N_PUSH_PARAM) a.expr.arg[k] = (uint8_t)(a.expr.arg[k] - 1);  // parameter 0 is `current`
+    return a;
+  }
   if (t == "cardinality") {
     // CardinalityAggregationSpec, DruidQuerySpec.scala:316-325
     a.kind = AggregationSpec::Cardinality;

@@ -8,27 +8,39 @@
 #include <vector>
 
 #include "json.hpp"
+#include "minijs.hpp"
 #include "timeutil.hpp"
 
 namespace sdo {
 
 // ---- filters (DruidQuerySpec.scala:152-281) -----------------------------------------------
 struct FilterNode {
-  enum Kind { Selector, Bound, In, Regex, Contains, And, Or, Not, True, False } kind = True;
+  enum Kind { Selector, Bound, In, Regex, Contains, Javascript, And, Or, Not, True, False } kind = True;
   std::string dimension;
   std::string value;              // Selector / Regex pattern / Contains
   std::vector<std::string> values;  // In
   bool has_lower = false, has_upper = false, lower_strict = false, upper_strict = false, alpha_numeric = false;
   std::string lower, upper;       // Bound
   std::vector<FilterNode> fields; // And / Or / Not(1)
+  std::shared_ptr<const minijs::Function> js;  // Javascript: function(value) -> truthy keeps the row
 };
 
 // ---- dimensions (DruidQuerySpec.scala:108-138) --------------------------------------------
+// timeFormat applies to __time (key = formatted bucket) and to string dimensions holding ISO dates (q8.json groups by
+// the year of o_orderdate this way).  On a dimension every function is a string -> string map, applied once per
+// dictionary entry at plan time; rows group on the id of the mapped value.  A null result is the empty value.
 struct ExtractionFn {
-  enum Kind { None, TimeFormat } kind = None;
-  std::string format;
-  std::string time_zone;  // empty = UTC
+  enum Kind { None, TimeFormat, TimeParse, Javascript, Lookup, Regex, Substring, Upper, Lower, Strlen } kind = None;
+  std::string format;       // TimeFormat: Joda output pattern; TimeParse: resultFormat
+  std::string time_zone;    // empty = UTC
   std::string locale;
+  std::string parse_format; // TimeParse: input pattern (TimeParsingExtractionFunctionSpec.timeFormat)
+  std::shared_ptr<const minijs::Function> js;  // Javascript (JavaScriptExtractionFunctionSpec)
+  std::vector<std::pair<std::string, std::string>> lookup;  // Lookup: map entries
+  bool retain_missing = false, has_replace_missing = false;
+  std::string replace_missing;  // Lookup / Regex: replaceMissingValueWith
+  std::string expr;         // Regex: pattern, first capture group (whole match if it has none)
+  int64_t index = 0, length = -1;  // Substring
 };
 struct DimensionSpec {
   std::string dimension, output_name;
@@ -44,6 +56,10 @@ struct AggregationSpec {
   bool by_row = true;
   bool has_filter = false;           // FilteredAggregationSpec wraps a selector
   FilterNode filter;
+  // DoubleSum / DoubleMin / DoubleMax of an arithmetic expression over metrics instead of one metric: from a
+  // JavascriptAggregationSpec (:350-360) or an `expression` attribute.  N_PUSH_PARAM's arg indexes `fields`.
+  bool has_expr = false;
+  minijs::NumProgram expr;
 };
 
 // ---- post-aggregations (DruidQuerySpec.scala:379-430) -------------------------------------

@@ -63,6 +63,22 @@ class TimeFormatExtractionFunctionSpec(_Spec):
         super().__init__("timeFormat", format, timeZone, locale)
 
 
+class TimeParsingExtractionFunctionSpec(_Spec):
+    """DruidQuerySpec.scala:82-88"""
+    _fields = ("type", "timeFormat", "resultFormat")
+
+    def __init__(self, timeFormat, resultFormat):
+        super().__init__("time", timeFormat, resultFormat)
+
+
+class JavaScriptExtractionFunctionSpec(_Spec):
+    """DruidQuerySpec.scala:90-96"""
+    _fields = ("type", "function", "injective")
+
+    def __init__(self, function, injective=False):
+        super().__init__("javascript", function, injective)
+
+
 class LookUpMap(_Spec):
     _fields = ("type", "map")
 

@@ -154,7 +154,79 @@ def filter_cases():
         ("or_mix", Or(SelectorFilterSpec("l_returnflag", "A"), And(SelectorFilterSpec("l_linestatus", "O"), StringContainsSpec("l_shipmode", "AI")))),
         ("unknown_dim_null", SelectorFilterSpec("no_such_dim", "")),
         ("unknown_dim_value", SelectorFilterSpec("no_such_dim", "x")),
+    ] + js_filter_cases()
+
+
+def js_filter_cases():
+    """JavascriptFilterSpec functions in the expression subset the engine evaluates per dictionary entry."""
+    return [
+        # docs/benchmark/druid/queries/q3.json, TPCHQueries.scala:119-121
+        ("js_lt_date", JavascriptFilterSpec("o_orderdate", "function(x) { return(x < '1995-03-15') }")),
+        # docs/benchmark/druid/queries/q5.json: two javascript bounds under an and
+        ("js_date_window", And(JavascriptFilterSpec("o_orderdate", "function(x) { return(x >= '1994-01-01') }"),
+                               JavascriptFilterSpec("o_orderdate", "function(x) { return(x < '1995-01-01') }"))),
+        # the text JSCodeGenerator emits: FilterPlanningTest.scala "jsUpper" / "jsCoalesce" (:131-157)
+        ("js_lower", JavascriptFilterSpec("c_mktsegment", "function (c_mktsegment) {\n            \n            \n            \n\n            "
+                                                          "return(((c_mktsegment).toLowerCase())  ==  (\"building\"));\n            }")),
+        ("js_coalesce", JavascriptFilterSpec("l_shipmode", "function (l_shipmode) {\n\n            return((((l_shipmode) || (\"no-mode\")))  ==  (\"AIR\"));\n            }")),
+        ("js_numeric", JavascriptFilterSpec("p_size", "function(x) { return parseInt(x) % 7 == 3 || x > 45; }")),
+        ("js_string_ops", JavascriptFilterSpec("p_brand", "function(b) { return b.substr(0, 6).concat('x') != 'Brand#x' ? false : (b.charAt(6) >= '3' && b.length == 8) }")),
+        ("js_unknown_dim", JavascriptFilterSpec("no_such_dim", "function(x) { return x == null }")),
     ]
+
+
+def extraction_dims():
+    """(name, ExtractionDimensionSpec) on dimensions other than __time."""
+    return [
+        # docs/benchmark/druid/queries/q8.json: year of the o_orderdate string dimension
+        ("year_of_orderdate", ExtractionDimensionSpec("o_orderdate", "o_year", TimeFormatExtractionFunctionSpec("yyyy"))),
+        ("month_name_tz", ExtractionDimensionSpec("o_orderdate", "m", TimeFormatExtractionFunctionSpec("MMM yyyy", "+05:30"))),
+        ("time_parse", ExtractionDimensionSpec("o_orderdate", "q", TimeParsingExtractionFunctionSpec("yyyy-MM-dd", "MM/yy"))),
+        ("js_brand_group", ExtractionDimensionSpec("p_brand", "brand_group", JavaScriptExtractionFunctionSpec("function(b) { return b.substr(0, 7).toLowerCase() }"))),
+        ("js_int_bucket", ExtractionDimensionSpec("p_size", "size_bucket", JavaScriptExtractionFunctionSpec("function(x) { return Math.floor(x / 10) * 10 }"))),
+        ("js_null", ExtractionDimensionSpec("l_shipmode", "air_or_null", JavaScriptExtractionFunctionSpec("function(x) { return x == 'AIR' || x == 'REG AIR' ? 'by air' : null }"))),
+        ("lookup", ExtractionDimensionSpec("l_returnflag", "flag", {"type": "lookup", "lookup": {"type": "map", "map": {"A": "accepted", "R": "returned"}}, "retainMissingValue": True})),
+        ("lookup_replace", ExtractionDimensionSpec("c_mktsegment", "seg", {"type": "lookup", "lookup": {"type": "map", "map": {"BUILDING": "b"}}, "replaceMissingValueWith": "other"})),
+        ("regex", ExtractionDimensionSpec("p_type", "material", {"type": "regex", "expr": " ([A-Z]+)$"})),
+        ("substring", ExtractionDimensionSpec("s_nation", "n3", {"type": "substring", "index": 1, "length": 3})),
+        ("strlen", ExtractionDimensionSpec("p_type", "len", {"type": "strlen"})),
+        ("upper", ExtractionDimensionSpec("l_shipmode", "u", {"type": "lower"})),
+    ]
+
+
+def with_extraction(dim, other="l_linestatus", strategy=None, f=None):
+    dims = [dim] + ([DefaultDimensionSpec(other)] if other else [])
+    return GroupByQuerySpec(DS, dims, None, None, "all", f, [agg("count", "n", "count"), agg("doubleSum", "price", "l_extendedprice"),
+                                                             CardinalityAggregationSpec("custs", ["o_custkey"])], None, ALL_TIME, ctx(strategy))
+
+
+REVENUE_JS = ("function(current, l_extendedprice, l_discount) { return current + (l_extendedprice * (1 - l_discount)); }",
+              "function(partialA, partialB) { return partialA + partialB; }", "function()                   { return 0; }")
+
+
+def js_aggs():
+    """Aggregations whose argument is arithmetic over metrics: the javascript form the reference generates
+    (JSAggGenerator.scala:36-119, tpch_index_task.json.template:138-156) and the `expression` attribute."""
+    return [
+        agg("count", "n", "count"),
+        JavascriptAggregationSpec("javascript", "revenue", ["l_extendedprice", "l_discount"], *REVENUE_JS),
+        JavascriptAggregationSpec("javascript", "charge", ["l_extendedprice", "l_discount", "l_tax"],
+                                  "function(current, l_extendedprice, l_discount, l_tax) { return current + (l_extendedprice *(1 - l_discount) * (1 + l_tax)); }",
+                                  "function(partialA, partialB) { return (partialA + partialB); }", "function() { return 0; }"),
+        # what JSAggGenerator emits for MIN / MAX over ((l) op (r)) trees, an integer metric on one side
+        JavascriptAggregationSpec("javascript", "min_unit", ["l_extendedprice", "l_quantity"],
+                                  "function (current, l_extendedprice, l_quantity) { return Math.min(current, ((l_extendedprice) / (l_quantity)));}",
+                                  "function (partialA, partialB) {return Math.min(partialA, partialB);}", "function() { return Number.POSITIVE_INFINITY; }"),
+        JavascriptAggregationSpec("javascript", "max_stock_value", ["ps_availqty", "ps_supplycost"],
+                                  "function (current, ps_availqty, ps_supplycost) { return Math.max(current, ((ps_availqty) * (ps_supplycost)));}",
+                                  "function (partialA, partialB) {return Math.max(partialA, partialB);}", "function() { return Number.NEGATIVE_INFINITY; }"),
+        {"type": "doubleSum", "name": "disc_amount", "expression": "l_extendedprice * l_discount"},
+        {"type": "doubleMax", "name": "max_abs_margin", "expression": "Math.abs(l_extendedprice - ps_supplycost * l_quantity) / 2"},
+    ]
+
+
+def js_agg_query(dims=("l_returnflag", "l_linestatus"), f=None, strategy=None, granularity="all"):
+    return GroupByQuerySpec(DS, [DefaultDimensionSpec(d) for d in dims], None, None, granularity, f, js_aggs(), None, ALL_TIME, ctx(strategy))
 
 
 def with_filter(f, strategy=None):

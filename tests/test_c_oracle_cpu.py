@@ -33,7 +33,8 @@ CASES = [("q1", lambda: Q.q1_style(), False), ("basic_agg", lambda: Q.basic_agg(
          ("proj_filt", lambda: Q.proj_filt_range(), False), ("q3", lambda: Q.q3(), False), ("q3_limit", lambda: Q.q3(10), True), ("q5", lambda: Q.q5(), False),
          ("q5_topn", lambda: Q.q5_topn(), True), ("q8", lambda: Q.q8(), False), ("ts_day", lambda: Q.timeseries("P1D"), False),
          ("ts_month", lambda: Q.timeseries("P1M"), False), ("by_orderkey", lambda: Q.by_orderkey(), False), ("agg_zoo", lambda: Q.agg_zoo(), False),
-         ("having", lambda: Q.having_query(), True)] + [("filter_" + n, (lambda f_: lambda: Q.with_filter(f_))(f), False) for n, f in Q.filter_cases() if n != "ts_null_guard"]
+         ("having", lambda: Q.having_query(), True), ("js_aggs", lambda: Q.js_agg_query(), False),
+         ("js_aggs_by_nation", lambda: Q.js_agg_query(("s_nation",), Q.SelectorFilterSpec("c_region", "ASIA")), False)] + [("filter_" + n, (lambda f_: lambda: Q.with_filter(f_))(f), False) for n, f in Q.filter_cases() if n != "ts_null_guard"]
 
 
 @pytest.mark.parametrize("name,mk,ordered", CASES, ids=[c[0] for c in CASES])

@@ -70,26 +70,25 @@ def test_metadata_and_segments_shape(planning):
 
 def test_reference_serialised_specs_parse_and_plan(planning):
     """Every spec the reference serialises (docs/benchmark/druid/queries, SparklineSQLTest) goes through the parser;
-    javascript filters are refused with SDO_UNSUPPORTED (north_star: javascript-free), the rest plan."""
+    the javascript date comparisons of q3 / q5 / q8 are inside the expression subset that is evaluated per dictionary
+    entry at plan time (the scan itself stays javascript-free), so every spec plans."""
     import spark_druid_olap_b200 as sdo
     eng, _, tbl = planning
     specs = json.load(open(os.path.join(ROOT, "tests", "golden", "reference_specs.json")))
     assert len(specs) >= 10
     outcome = {}
     for name, spec in specs.items():
-        has_js = "JavascriptFilterSpec" in json.dumps(spec)
         try:
-            e = eng.explain(spec)
-            outcome[name] = e
-            assert not has_js, name
-        except sdo.UnsupportedQuery as ex:
-            assert has_js and "javascript" in str(ex), (name, str(ex))
-            outcome[name] = "unsupported"
+            outcome[name] = eng.explain(spec)
         except sdo.DruidDataSourceException as ex:
             # the test index renames metrics (sum_ps_availqty, sum_l_quantity: BaseTest.scala:29-38)
             assert ex.status == 4 and "sum_" in str(ex), (name, str(ex))
             outcome[name] = "renamed-metric"
-    assert outcome["docs/q3"] == outcome["docs/q8"] == "unsupported"
+    for name in ("docs/q3", "docs/q5", "docs/q8"):
+        assert "JavascriptFilterSpec" in json.dumps(specs[name]) and outcome[name]["filter"]["leaves"], name
+    # q3: function(x) { return(x < '1995-03-15T08:00:00.000Z') } over day strings = the ids below 1995-03-16
+    q3 = outcome["docs/q3"]
+    assert q3["strategy"] in ("global", "hash") and len(q3["filter"]["leaves"]) == 2
     q1 = outcome["docs/q1"]
     assert q1["strategy"] == "lane" and q1["keySpace"] == 6 and q1["hll"] == 1
     a, b = orc.parse_interval(specs["docs/q1"]["intervals"][0])  # "-08:00" offsets are honoured
@@ -99,6 +98,25 @@ def test_reference_serialised_specs_parse_and_plan(planning):
     sdr = outcome["docs/shipDteRange"]
     a, b = orc.parse_interval(specs["docs/shipDteRange"]["intervals"][0])
     assert sdr["rowsScanned"] == int(((tbl.time >= a) & (tbl.time < b)).sum()) and sdr["filter"]["ops"] == []
+
+
+def test_extraction_dimension_planning(planning):
+    """An extraction function on a dimension is folded into a per-query id remap: the key space is the number of
+    distinct extracted values, not the dictionary size."""
+    eng, tabs, _ = planning
+    dims = dict(Q.extraction_dims())
+    e = eng.explain(Q.with_extraction(dims["year_of_orderdate"]))
+    years = {s[:4] for s in tabs[0].dicts["o_orderdate"]} | {s[:4] for s in tabs[1].dicts["o_orderdate"]}
+    assert e["keySpace"] == len(years) * 2 and e["strategy"] in ("lane", "block")
+    e = eng.explain(Q.with_extraction(dims["lookup_replace"], None))
+    assert e["keySpace"] == 2  # "b" and "other"
+    e = eng.explain(Q.with_extraction(dims["js_int_bucket"], None))
+    assert e["keySpace"] == 6  # p_size 1..50 -> 0, 10, ..., 50
+    import spark_druid_olap_b200 as sdo
+    with pytest.raises(sdo.UnsupportedQuery):
+        eng.explain(Q.with_extraction(Q.ExtractionDimensionSpec("__time", "t", {"type": "strlen"})))
+    with pytest.raises(sdo.UnsupportedQuery):
+        eng.explain(Q.with_extraction(Q.ExtractionDimensionSpec("p_brand", "t", {"type": "cascade", "extractionFns": []})))
 
 
 def _sorted_dict(tab, col):
@@ -186,7 +204,23 @@ def test_error_statuses(planning):
     with pytest.raises(sdo.UnsupportedQuery):
         eng.explain({"queryType": "search", "dataSource": "tpch"})
     with pytest.raises(sdo.UnsupportedQuery):
-        eng.explain(Q.with_filter(Q.JavascriptFilterSpec("s_name", "function (s_name) { return s_name == 'S1' }")))
+        # what JSCodeGenerator emits for date arithmetic (FilterPlanningTest.scala:85-104): statements and Java interop
+        eng.explain(Q.with_filter(Q.JavascriptFilterSpec("o_orderdate", "function (o_orderdate) {\n var v1 = new org.joda.time.DateTimeZone.forID(\"UTC\");"
+                                                                         "return(v1 != null); }")))
+    with pytest.raises(sdo.UnsupportedQuery):
+        eng.explain(Q.with_filter(Q.JavascriptFilterSpec("s_nation", "function (x) { return x.match('^A') }")))
+    with pytest.raises(sdo.InvalidQuery):
+        eng.explain(Q.with_filter(Q.JavascriptFilterSpec("s_nation", "function (x) { return (x < 'B' }")))
+    with pytest.raises(sdo.UnsupportedQuery):  # a javascript aggregate that is not a sum / min / max fold
+        eng.explain(Q.GroupByQuerySpec(Q.DS, [], None, None, "all", None, [Q.JavascriptAggregationSpec(
+            "javascript", "c", ["l_tax"], "function(current, a) { return current * a; }", "function(a, b) { return a * b; }", "function() { return 1; }")],
+            None, Q.ALL_TIME, None))
+    with pytest.raises(sdo.UnsupportedQuery):  # fnCombine must be the merge of the same fold
+        eng.explain(Q.GroupByQuerySpec(Q.DS, [], None, None, "all", None, [Q.JavascriptAggregationSpec(
+            "javascript", "c", ["l_tax"], "function(current, a) { return current + a; }", "function(a, b) { return Math.max(a, b); }", "function() { return 0; }")],
+            None, Q.ALL_TIME, None))
+    with pytest.raises(sdo.UnsupportedQuery):  # dimensions cannot appear in arithmetic
+        eng.explain(Q.GroupByQuerySpec(Q.DS, [], None, None, "all", None, [{"type": "doubleSum", "name": "x", "expression": "l_tax * p_size"}], None, Q.ALL_TIME, None))
     with pytest.raises(sdo.UnsupportedQuery):
         q = json.loads(Q.q7().to_json())
         q["dimensions"][2]["extractionFn"]["timeZone"] = "America/Los_Angeles"

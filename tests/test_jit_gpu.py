@@ -32,8 +32,11 @@ CASES = [("q1_lane", lambda: Q.q1_style(), False), ("q1_block", lambda: Q.q1_sty
          ("q3_limit", lambda: Q.q3(10), True), ("q5_topn", lambda: Q.q5_topn(), True), ("q7_timeformat", lambda: Q.q7(), False), ("q8", lambda: Q.q8(), False),
          ("ts_day_hll", lambda: Q.timeseries("P1D"), False), ("ts_month_hll", lambda: Q.timeseries("P1M"), False), ("by_orderkey", lambda: Q.by_orderkey(), False),
          ("by_orderkey_hash", lambda: Q.by_orderkey("hash"), False), ("agg_zoo", lambda: Q.agg_zoo(), False), ("agg_zoo_hash", lambda: Q.agg_zoo("hash"), False),
-         ("month_grain", lambda: Q.q1_month_grain(), True)] + \
-        [("filter_" + n, (lambda f_: lambda: Q.with_filter(f_))(f), False) for n, f in Q.filter_cases() if n in ("in_many", "not_in", "bound_int_lex", "regex", "or_mix")]
+         ("month_grain", lambda: Q.q1_month_grain(), True), ("js_aggs_lane", lambda: Q.js_agg_query(("l_returnflag",)), False),
+         ("js_aggs_block", lambda: Q.js_agg_query(("s_nation", "l_shipmode")), False), ("js_aggs_hash", lambda: Q.js_agg_query(("o_orderkey",), None, "hash"), False),
+         ("extract_year", lambda: Q.with_extraction(Q.extraction_dims()[0][1]), False), ("extract_js_hash", lambda: Q.with_extraction(Q.extraction_dims()[3][1], "o_orderkey", "hash"), False),
+         ("js_aggs_month", lambda: Q.js_agg_query((), Q.js_filter_cases()[0][1], None, {"type": "period", "period": "P1M"}), False)] + \
+        [("filter_" + n, (lambda f_: lambda: Q.with_filter(f_))(f), False) for n, f in Q.filter_cases() if n in ("in_many", "not_in", "bound_int_lex", "regex", "or_mix", "js_date_window")]
 
 
 @pytest.mark.parametrize("name,mk,ordered", CASES, ids=[c[0] for c in CASES])

@@ -3,6 +3,7 @@ import json
 import math
 
 import numpy as np
+import pytest
 
 import helpers as H
 import queries as Q
@@ -152,3 +153,63 @@ def test_generator_is_deterministic_and_shard_invariant():
     share = {(r["l_returnflag"], r["l_linestatus"]): r["n"] / t.n for r in rows}
     assert abs(share[("A", "F")] - 0.247) < 0.01 and abs(share[("R", "F")] - 0.247) < 0.01 and abs(share[("N", "O")] - 0.50) < 0.01
     assert 0.002 < share[("N", "F")] < 0.012
+
+
+def test_js_subset_known_answers():
+    """The oracle's reading of the JavaScript expression subset against answers ECMAScript fixes (ToBoolean / ToNumber /
+    ToString, abstract equality and relational comparison, || and && returning operands)."""
+    from oracle import js_subset as J
+
+    def run(src, *args):
+        params, body = J.parse_function(src)
+        return J.evaluate(body, list(args))
+
+    assert run("function(x) { return(x < '1995-03-15T08:00:00.000Z') }", "1995-03-15") is True
+    assert run("function(x) { return(x < '1995-03-15') }", "1995-03-15") is False
+    assert run("function(x) { return x < '10' }", "9") is False          # both strings: lexicographic
+    assert run("function(x) { return x < 10 }", "9") is True             # string vs number: numeric
+    assert run("function(x) { return x == 9 }", "9.0") is True and run("function(x) { return x === 9 }", "9") is False
+    assert run("function(x) { return x == null }", None) is True and run("function(x) { return x == 0 }", None) is False
+    assert run("function(x) { return x < 1 }", None) is True             # null -> 0 in relational comparison
+    assert run("function(x) { return (x) || (\"d\") }", None) == "d" and run("function(x) { return x && x.length }", "abc") == 3.0
+    assert run("function(x) { return 'a' + 1 + 2 }", None) == "a12" and run("function(x) { return 1 + 2 + 'a' }", None) == "3a"
+    assert run("function(x) { return '' + 0.1 * 3 }", None) == "0.30000000000000004" and run("function(x) { return '' + 1e21 }", None) == "1e+21"
+    assert run("function(x) { return '' + 1/3 }", None) == "0.3333333333333333" and run("function(x) { return '' + 100 }", None) == "100"
+    assert run("function(x) { return parseInt('42px') + parseFloat('1.5e1x') }", None) == 57.0
+    assert math.isnan(run("function(x) { return Number('42px') }", None)) and run("function(x) { return Number('') + Number(' 12 ') }", None) == 12.0
+    assert run("function(x) { return x.substr(1, 2) + x.substring(3, 1) + x.slice(-2) + x.charAt(0) }", "abcdef") == "bcbcefa"
+    assert run("function(x) { return x.toUpperCase().concat('-', 1) }", "aé") == "Aé-1"
+    assert run("function(x) { return !x ? 'empty' : 'full' }", "") == "empty"
+    assert run("function(x) { return -x + 5 % 3 - 2 * 3 }", "4") == -8.0
+    assert run("function(x) { return Math.max(1, '7', 3) - Math.min(2, 1) }", None) == 6.0
+    assert run("function f(a, b) { ; return a.indexOf(b); ; }", "hello", "ll") == 2.0
+    for bad in ("function(x) { var y = 1; return y }", "function(x) { return new Date() }", "function(x) { return x.foo() }", "function(x) { return y }"):
+        with pytest.raises((J.Unsupported, TypeError)):
+            params, body = J.parse_function(bad)
+            J.evaluate(body, ["v"])
+    # numeric trees over columns
+    params, body = J.parse_function("function(current, a, b) { return current + (a *(1 - b)); }")
+    fold, arg = J.split_fold(params, body)
+    a, b = np.array([10.0, 0.1]), np.array([0.25, 0.3])
+    assert fold == "sum" and np.array_equal(J.evaluate_numeric(arg, [None, a, b]), a * (1 - b))
+    params, body = J.parse_expression("Math.abs(p - q * 2) / 4")
+    assert params == ["p", "q"] and np.array_equal(J.evaluate_numeric(body, [a, b]), np.abs(a - b * 2) / 4)
+
+
+def test_extraction_function_known_answers():
+    ex = orc.extract_value
+    assert ex({"type": "timeFormat", "format": "yyyy"}, "1995-03-15") == "1995"
+    assert ex({"type": "timeFormat", "format": "yyyy-MM-dd HH", "timeZone": "-08:00"}, "1995-03-15T08:00:00.000Z") == "1995-03-15 00"
+    assert ex({"type": "timeFormat", "format": "yyyy"}, "") == ""
+    assert ex({"type": "time", "timeFormat": "yyyy-MM-dd", "resultFormat": "dd/MM/yyyy"}, "1998-12-01") == "01/12/1998"
+    assert ex({"type": "time", "timeFormat": "yyyyMMdd", "resultFormat": "yyyy-MM"}, "19981201") == "1998-12"
+    assert ex({"type": "time", "timeFormat": "yyyy-MM-dd", "resultFormat": "yyyy"}, "not a date") == "not a date"
+    assert ex({"type": "javascript", "function": "function(x) { return x.length > 3 ? x.substr(0, 3) : null }"}, "abcdef") == "abc"
+    assert ex({"type": "javascript", "function": "function(x) { return x.length > 3 ? x.substr(0, 3) : null }"}, "ab") == ""
+    assert ex({"type": "javascript", "function": "function(x) { return Math.floor(x / 10) * 10 }"}, "37") == "30"
+    lk = {"type": "lookup", "lookup": {"type": "map", "map": {"a": "1"}}}
+    assert ex(lk, "a") == "1" and ex(lk, "b") == "" and ex(dict(lk, retainMissingValue=True), "b") == "b" and ex(dict(lk, replaceMissingValueWith="?"), "b") == "?"
+    assert ex({"type": "regex", "expr": "^(\\w+) "}, "PROMO PLATED TIN") == "PROMO" and ex({"type": "regex", "expr": "^(\\d+)"}, "x") == "x"
+    assert ex({"type": "regex", "expr": "^(\\d+)", "replaceMissingValue": True, "replaceMissingValueWith": "n/a"}, "x") == "n/a"
+    assert ex({"type": "substring", "index": 2, "length": 3}, "abcdef") == "cde" and ex({"type": "substring", "index": 4}, "abcdef") == "ef"
+    assert ex({"type": "substring", "index": 9}, "abc") == "" and ex({"type": "upper"}, "aBc") == "ABC" and ex({"type": "strlen"}, "abcd") == "4"
