@@ -26,7 +26,7 @@ METRIC = "tpch_flat_rows_scanned_per_s"
 UNIT = "rows/s"
 Q5T_COLUMNS = ["s_region", "o_orderdate", "s_nation", "l_extendedprice"]
 Q5T_TRAFFIC_BYTES = 277343232  # ncu capture of scan_kernel on SF10 Q5T (profiles/r01_ncu_q5t_*): 273.58 MB read + 3.77 MB written
-EXTRA_COLUMNS = ["c_mktsegment", "o_orderkey", "o_shippriority", "l_returnflag", "l_linestatus", "l_quantity", "l_discount", "o_custkey"]
+EXTRA_COLUMNS = ["c_mktsegment", "o_orderkey", "o_shippriority", "l_returnflag", "l_linestatus", "l_quantity", "l_discount", "l_tax", "o_custkey"]
 
 
 def peaks():
@@ -78,6 +78,25 @@ def cpu_baseline_q5t(sf_sample, threads=None):
     import queries as Q
     from oracle import cpu_engine
     return cpu_engine.time_query(json.loads(Q.q5_topn().to_json()), sf_sample, Q5T_COLUMNS, threads)
+
+
+def q1_tpch():
+    """TPC-H Q1 as written (TpchBenchMark.scala:135-150): sum_disc_price and sum_charge are expressions over metrics,
+    which the reference can only push down as javascript aggregators (JSAggGenerator.scala)."""
+    import queries as Q
+    q = json.loads(Q.q1_style().to_json())
+    q["aggregations"] += [
+        {"type": "javascript", "name": "sum_disc_price", "fieldNames": ["l_extendedprice", "l_discount"],
+         "fnAggregate": "function(current, l_extendedprice, l_discount) { return current + ((l_extendedprice) * ((1) - (l_discount))); }",
+         "fnCombine": "function(partialA, partialB) { return (partialA + partialB); }", "fnReset": "function() { return 0; }"},
+        {"type": "javascript", "name": "sum_charge", "fieldNames": ["l_extendedprice", "l_discount", "l_tax"],
+         "fnAggregate": "function(current, l_extendedprice, l_discount, l_tax) { return current + (((l_extendedprice) * ((1) - (l_discount))) * ((1) + (l_tax))); }",
+         "fnCombine": "function(partialA, partialB) { return (partialA + partialB); }", "fnReset": "function() { return 0; }"}]
+
+    class _Q:
+        def to_json(self):
+            return json.dumps(q)
+    return _Q()
 
 
 def run_reference(args):
@@ -249,8 +268,10 @@ def main():
             line["cpu_baseline"] = {"error": repr(ex)}
     if args.extra and world == 1:
         extra = {}
-        for name, q in (("q1_style", Q.q1_style()), ("q3_limit10", Q.q3(10)), ("timeseries_day_hll", Q.timeseries("P1D")),
-                        ("timeseries_month_hll", Q.timeseries("P1M")), ("by_orderkey_hash", Q.by_orderkey("hash")), ("by_orderkey", Q.by_orderkey())):
+        shapes = [("q1_style", Q.q1_style()), ("q1_tpch_expressions", q1_tpch()), ("q3_limit10", Q.q3(10)), ("timeseries_day_hll", Q.timeseries("P1D")),
+                  ("timeseries_month_hll", Q.timeseries("P1M")), ("year_of_orderdate_extraction", Q.with_extraction(Q.extraction_dims()[0][1], "s_nation")),
+                  ("by_orderkey_hash", Q.by_orderkey("hash")), ("by_orderkey", Q.by_orderkey())]
+        for name, q in shapes:
             qb = q.to_json().encode()
             for _ in range(3):
                 eng.execute(qb)
@@ -261,6 +282,37 @@ def main():
             extra[name] = {"strategy": st["strategy"], "rows_scanned": st["rowsScanned"], "groups": st["groups"], "scan_ms_avg": sum(sc) / 6,
                            "scan_ms_min": min(sc), "total_ms_avg": sum(tt) / 6, "total_ms_min": min(tt), "total_ms_max": max(tt),
                            "achieved_gbs": st["algorithmicBytes"] / (sum(sc) / 6 / 1000) / 1e9, "launches": st["launches"]}
+        # BASELINE config 5's shape at this scale: the suite from concurrent callers on one engine handle
+        # (docs/bi-benchmark/snap-sales-demo.jmx runs 4 thread groups; DruidPlanner.scala:83-90 allows 100 connections)
+        suite = [(n, q.to_json().encode()) for n, q in shapes[:6]] + [("q5_topn", q5t)]
+        for n_threads in (1, 4, 16):
+            lat = {n: [] for n, _ in suite}
+            rows = [0]
+            lock = threading.Lock()
+            gate = threading.Barrier(n_threads + 1)
+
+            def caller(t):
+                gate.wait()
+                for r in range(4):
+                    for k in range(len(suite)):
+                        n, qb = suite[(k + t) % len(suite)]
+                        t0 = time.perf_counter()
+                        res = eng.execute(qb)
+                        dt = (time.perf_counter() - t0) * 1e3
+                        with lock:
+                            lat[n].append(dt)
+                            rows[0] += res.stats["rowsScanned"]
+
+            ths = [threading.Thread(target=caller, args=(t,)) for t in range(n_threads)]
+            for th in ths:
+                th.start()
+            gate.wait()
+            t0 = time.perf_counter()
+            for th in ths:
+                th.join()
+            wall = time.perf_counter() - t0
+            extra[f"concurrent_suite_{n_threads}_callers"] = {"queries": sum(len(v) for v in lat.values()), "wall_s": wall, "rows_scanned_per_s": rows[0] / wall,
+                                                             "latency_ms_mean": {n: sum(v) / len(v) for n, v in lat.items()}}
         line["extra"] = extra
     print(json.dumps(line))
     if world > 1:

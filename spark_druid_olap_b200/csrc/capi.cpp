@@ -149,7 +149,14 @@ int sdo_result_column_get(const sdo_result* r, int i, sdo_result_column* out) {
 }
 const uint8_t* sdo_result_hll_registers(const sdo_result* r, int i) {
   if (!r || i < 0 || i >= (int)r->r->columns.size()) return nullptr;
-  const ResultColumn& c = r->r->columns[i];
+  ResultColumn& c = r->r->columns[i];
+  if (c.hll.empty() && c.hll_rows && !c.hll_pick.empty()) {
+    // first request: put the sketches into result order (a result is read by the one task that owns it)
+    c.hll.resize(c.hll_pick.size() * 512);
+    for (size_t k = 0; k < c.hll_pick.size(); k++) memcpy(&c.hll[k * 512], c.hll_rows + c.hll_pick[k] * 512, 512);
+    c.hll_rows = nullptr;
+    c.hll_pick.clear();
+  }
   return c.hll.empty() ? nullptr : c.hll.data();
 }
 const char* sdo_result_stats_json(const sdo_result* r) { return r ? r->r->stats.c_str() : ""; }

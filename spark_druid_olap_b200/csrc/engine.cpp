@@ -38,7 +38,10 @@ double hll_estimate(const uint8_t* regs) {
     z3 += pow2.inv[regs[j + 3] & 63];
     zeros += (regs[j] == 0) + (regs[j + 1] == 0) + (regs[j + 2] == 0) + (regs[j + 3] == 0);
   }
-  const double zinv = (z0 + z1) + (z2 + z3), V = zeros;
+  return hll_estimate_from((z0 + z1) + (z2 + z3), zeros);
+}
+double hll_estimate_from(double zinv, double V) {
+  const double m = HLL_M;
   const double alpha_m2 = (0.7213 / (1.0 + 1.079 / m)) * m * m;
   const double E = alpha_m2 / zinv;
   double est = E;
@@ -353,9 +356,19 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   p.hll_mode = HLL_IN_GLOBAL;
   if (plan.n_hll && strat != STRAT_HASH) {
     // keep the sketches in shared memory when they fit next to the aggregate table
-    if (plan.n_keys * (uint64_t)plan.n_hll * HLL_M + smem <= 96 * 1024) p.hll_mode = HLL_IN_SMEM_ALL;
-    else if (plan.dev_dims.empty() && (size_t)plan.n_hll * HLL_M + smem <= 200 * 1024) p.hll_mode = HLL_IN_SMEM_SPAN;
-    smem += scan_hll_smem_bytes(p.hll_mode, plan.n_keys, plan.n_hll);
+    const std::string& force = plan.spec.gpu_hll_place;
+    const uint64_t all_bytes = plan.n_keys * (uint64_t)plan.n_hll * HLL_M;
+    // Sketches per block cost a warm-up of every register in every block, and shared memory costs occupancy: all groups
+    // go to shared memory only while 4 blocks per SM still fit (measured on SF10: 84 month sketches 0.28 ms shared vs
+    // 0.47 ms global; 175 sketches 1.00 ms shared vs 0.65 ms global).  One word per register when that fits too.
+    const uint64_t budget = (force == "shared" ? 200 : 56) * 1024;
+    // No grouping dimension (timeseries): the key is constant over a span, so one cached sketch per block is enough.
+    if (force == "global") {
+    } else if (plan.dev_dims.empty() && force.empty() && (size_t)plan.n_hll * HLL_M * 4 + smem <= 200 * 1024) { p.hll_mode = HLL_IN_SMEM_SPAN; p.hll_wide = 1; }
+    else if (all_bytes * 4 + smem <= budget) { p.hll_mode = HLL_IN_SMEM_ALL; p.hll_wide = 1; }
+    else if (all_bytes + smem <= budget) p.hll_mode = HLL_IN_SMEM_ALL;
+    else if (plan.dev_dims.empty() && (size_t)plan.n_hll * HLL_M * 4 + smem <= 200 * 1024) { p.hll_mode = HLL_IN_SMEM_SPAN; p.hll_wide = 1; }
+    if (p.hll_mode != HLL_IN_GLOBAL) smem = round_up(smem, 16) + scan_hll_smem_bytes(p.hll_mode, p.hll_wide != 0, plan.n_keys, plan.n_hll);
   }
   // run-time specialised kernel for this query shape (large scans, or when the query asks for it)
   const JitKernel* jk = nullptr;
@@ -427,11 +440,11 @@ void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
 void Engine::free_state(QueryCtx* ctx, ScanState* st) {
   if (device_ < 0) return;
   cudaStream_t s = ctx->stream;
-  void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll_in_table ? nullptr : (void*)st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll};
+  void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll_in_table ? nullptr : (void*)st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll, st->hll_stats};
   for (void* p : ptrs)
     if (p) cudaFreeAsync(p, s);
   st->blob = nullptr; st->table = nullptr; st->hkeys = nullptr; st->hll = nullptr; st->partials = nullptr;
-  st->rows_keys = nullptr; st->rows_slots = nullptr; st->rows_hll = nullptr;
+  st->rows_keys = nullptr; st->rows_slots = nullptr; st->rows_hll = nullptr; st->hll_stats = nullptr;
 }
 
 namespace {
@@ -440,7 +453,12 @@ struct HostRows {
   uint64_t n = 0;
   int ns = 1;
   std::vector<uint64_t> keys, slots;
-  std::vector<uint8_t> hll;
+  uint8_t* hll = nullptr;          // [sketch][512] in a pooled pinned buffer, handed to the result
+  size_t hll_bytes = 0, hll_cap = 0;
+  PinnedPool* pool = nullptr;
+  ~HostRows() { if (hll && pool) pool->put(hll, hll_cap); }
+  std::vector<uint64_t> hll_set;   // per row: index of its first sketch in hll / hll_stats (sketches of a row are adjacent)
+  std::vector<double> hll_stats;   // per sketch: sum of 2^-register, zero registers
 };
 
 inline double ord_to_f64(int64_t raw) {
@@ -523,6 +541,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   const int ns = plan.n_slots;
   HostRows rows;
   rows.ns = ns;
+  rows.pool = &pinned_pool_;
   bool device_topk = false;
   float ms_h2d = 0, ms_scan = 0, ms_dev = 0;
 
@@ -531,21 +550,34 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
     if (dense && st->table_rows <= 65536 && (uint64_t)st->table_rows * std::max(1, plan.n_hll) * HLL_M <= (64u << 20)) {
       // small dense table: bring it back whole and drop empty groups on the host
       const size_t tb = (size_t)st->table_rows * ns * 8;
-      const size_t hb = plan.n_hll ? (size_t)st->table_rows * plan.n_hll * HLL_M : 0;
-      ensure_pinned(&ctx->pinned_out, &ctx->pinned_out_bytes, tb + hb);
+      const size_t n_sets = plan.n_hll ? (size_t)st->table_rows * plan.n_hll : 0;
+      const size_t hb = n_sets * HLL_M, sb = n_sets * 16;
+      ensure_pinned(&ctx->pinned_out, &ctx->pinned_out_bytes, tb + sb);
       SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
       SDO_CUDA(cudaMemcpyAsync(ctx->pinned_out, st->table, tb, cudaMemcpyDeviceToHost, s));
-      if (hb) SDO_CUDA(cudaMemcpyAsync((char*)ctx->pinned_out + tb, st->hll, hb, cudaMemcpyDeviceToHost, s));
+      if (hb) {
+        // estimator inputs are computed on the device; the registers themselves go straight into the result's backing
+        SDO_CUDA(cudaMallocAsync((void**)&st->hll_stats, sb, s));
+        launch_hll_stats(st->hll, n_sets, st->hll_stats, s);
+        st->launches += 1;
+        SDO_CUDA(cudaMemcpyAsync((char*)ctx->pinned_out + tb, st->hll_stats, sb, cudaMemcpyDeviceToHost, s));
+        rows.hll = (uint8_t*)pinned_pool_.get(hb, &rows.hll_cap);
+        rows.hll_bytes = hb;
+        SDO_CUDA(cudaMemcpyAsync(rows.hll, st->hll, hb, cudaMemcpyDeviceToHost, s));
+      }
       SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
       SDO_CUDA(cudaStreamSynchronize(s));
-      st->d2h_bytes += tb + hb;
+      st->d2h_bytes += tb + hb + sb;
       const uint64_t* t = (const uint64_t*)ctx->pinned_out;
-      const uint8_t* hr = (const uint8_t*)ctx->pinned_out + tb;
+      if (hb) {
+        const double* hs = (const double*)((const char*)ctx->pinned_out + tb);
+        rows.hll_stats.assign(hs, hs + n_sets * 2);
+      }
       for (uint64_t k = 0; k < st->table_rows; k++) {
         if (t[k * ns] == 0) continue;
         rows.keys.push_back(k);
         rows.slots.insert(rows.slots.end(), t + k * ns, t + (k + 1) * ns);
-        if (hb) rows.hll.insert(rows.hll.end(), hr + k * plan.n_hll * HLL_M, hr + (k + 1) * plan.n_hll * HLL_M);
+        if (hb) rows.hll_set.push_back(k * plan.n_hll);
       }
       rows.n = rows.keys.size();
     } else {
@@ -616,13 +648,22 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
           SDO_CUDA(cudaMemcpyAsync(rows.keys.data(), st->rows_keys, (size_t)n * 8, cudaMemcpyDeviceToHost, s));
           SDO_CUDA(cudaMemcpyAsync(rows.slots.data(), st->rows_slots, (size_t)n * ns * 8, cudaMemcpyDeviceToHost, s));
           if (plan.n_hll) {
-            rows.hll.assign((size_t)n * plan.n_hll * HLL_M, 0);
-            SDO_CUDA(cudaMemcpyAsync(rows.hll.data(), st->rows_hll, rows.hll.size(), cudaMemcpyDeviceToHost, s));
+            const size_t n_sets = (size_t)n * plan.n_hll;
+            rows.hll_bytes = n_sets * HLL_M;
+            rows.hll = (uint8_t*)pinned_pool_.get(rows.hll_bytes, &rows.hll_cap);
+            rows.hll_stats.assign(n_sets * 2, 0.0);
+            SDO_CUDA(cudaMallocAsync((void**)&st->hll_stats, n_sets * 16, s));
+            launch_hll_stats(st->rows_hll, n_sets, st->hll_stats, s);
+            st->launches += 1;
+            SDO_CUDA(cudaMemcpyAsync(rows.hll_stats.data(), st->hll_stats, n_sets * 16, cudaMemcpyDeviceToHost, s));
+            SDO_CUDA(cudaMemcpyAsync(rows.hll, st->rows_hll, rows.hll_bytes, cudaMemcpyDeviceToHost, s));
+            rows.hll_set.resize(n);
+            for (uint64_t r = 0; r < n; r++) rows.hll_set[r] = r * plan.n_hll;
           }
         }
         SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
         SDO_CUDA(cudaStreamSynchronize(s));
-        st->d2h_bytes += (size_t)n * (ns + 1) * 8 + rows.hll.size();
+        st->d2h_bytes += (size_t)n * (ns + 1) * 8 + rows.hll_bytes + rows.hll_stats.size() * 8;
         rows.n = n;
       }
     }
@@ -645,7 +686,8 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
     else as.agg_i[a].resize(n);
     for (uint64_t r = 0; r < n; r++) {
       if (pa.hll_index >= 0) {
-        as.agg_f[a][r] = hll_estimate(&rows.hll[(r * plan.n_hll + pa.hll_index) * HLL_M]);
+        const uint64_t set = rows.hll_set[r] + pa.hll_index;
+        as.agg_f[a][r] = hll_estimate_from(rows.hll_stats[set * 2], rows.hll_stats[set * 2 + 1]);
         continue;
       }
       uint64_t raw = rows.slots[r * ns + pa.slot];
@@ -783,6 +825,11 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   std::unique_ptr<Result> res(new Result());
   const uint64_t m = order.size();
   res->n_rows = (int64_t)m;
+  res->pool = &pinned_pool_;
+  res->hll_backing = rows.hll;  // the result now owns the sketches
+  res->hll_backing_bytes = rows.hll_cap;
+  const uint8_t* hll_rows = rows.hll;
+  rows.hll = nullptr;
   if (plan.has_bucket) {
     ResultColumn c;
     c.name = "timestamp";
@@ -830,8 +877,10 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
       c.f64.resize(m);
       for (uint64_t i = 0; i < m; i++) c.f64[i] = as.agg_f[a][order[i]];
       if (pa.hll_index >= 0) {
-        c.hll.resize(m * HLL_M);
-        for (uint64_t i = 0; i < m; i++) memcpy(&c.hll[i * HLL_M], &rows.hll[(order[i] * plan.n_hll + pa.hll_index) * HLL_M], HLL_M);
+        // registers are gathered into result order only if sdo_result_hll_registers asks for them
+        c.hll_rows = hll_rows;
+        c.hll_pick.resize(m);
+        for (uint64_t i = 0; i < m; i++) c.hll_pick[i] = rows.hll_set[order[i]] + pa.hll_index;
       }
     } else {
       c.type = SDO_RES_INT64;

@@ -37,7 +37,9 @@ struct ResultColumn {
   std::vector<double> f64;
   std::vector<uint32_t> ids;
   std::shared_ptr<Dictionary> dict;  // STRING
-  std::vector<uint8_t> hll;          // cardinality columns: n_rows * 512 registers
+  std::vector<uint8_t> hll;          // cardinality columns: n_rows * 512 registers, gathered on first request from:
+  const uint8_t* hll_rows = nullptr; // every group's sketches as they came off the device (Result::hll_backing)
+  std::vector<uint64_t> hll_pick;    // per result row: index of its sketch in hll_rows
   void* raw = nullptr;               // large results: column values in a pooled pinned buffer instead of the vectors
   size_t raw_bytes = 0;
 };
@@ -47,9 +49,12 @@ struct Result {
   std::vector<ResultColumn> columns;
   std::string stats;
   PinnedPool* pool = nullptr;  // owner of the raw buffers (the engine must outlive its results)
+  void* hll_backing = nullptr;  // pooled pinned buffer behind the columns' hll_rows
+  size_t hll_backing_bytes = 0;
   ~Result() {
     for (auto& c : columns)
       if (c.raw && pool) pool->put(c.raw, c.raw_bytes);
+    if (hll_backing && pool) pool->put(hll_backing, hll_backing_bytes);
   }
 };
 
@@ -87,6 +92,7 @@ struct ScanState {
   unsigned long long* rows_keys = nullptr;
   unsigned long long* rows_slots = nullptr;
   uint8_t* rows_hll = nullptr;
+  double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
   bool rows_valid = false;
 };
@@ -149,5 +155,6 @@ class Engine {
 };
 
 double hll_estimate(const uint8_t* regs);
+double hll_estimate_from(double zinv, double zeros);
 
 }  // namespace sdo

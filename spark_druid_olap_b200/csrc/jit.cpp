@@ -130,6 +130,7 @@ std::string prelude(int strategy, const ScanParams& p) {
   }
   s += "constexpr int n_hll = " + std::to_string(p.n_hll) + ";\n";
   s += "constexpr int hll_place = " + std::to_string(p.hll_mode) + ";\n";
+  s += "constexpr int hll_wide = " + std::to_string(p.hll_wide) + ";\n";
   s += "constexpr int ignore_key_base = " + std::to_string(p.ignore_key_base) + ";\n";
   s += "constexpr int n_cols = " + std::to_string(p.n_cols) + ";\n";
   s += "}}\n#include \"scan_kernel.cuh\"\n";

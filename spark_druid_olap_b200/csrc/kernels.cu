@@ -20,9 +20,10 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_cons
   scan_body<STRAT>(p, coarse);
 }
 
-size_t scan_hll_smem_bytes(int hll_mode, uint64_t n_keys, int n_hll) {
-  if (hll_mode == HLL_IN_SMEM_ALL) return (size_t)n_keys * n_hll * HLL_M;
-  if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * HLL_M;
+size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll) {
+  const size_t per_set = wide ? (size_t)HLL_M * 4 : (size_t)HLL_M;
+  if (hll_mode == HLL_IN_SMEM_ALL) return (size_t)n_keys * n_hll * per_set;
+  if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * per_set;
   return 0;
 }
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots) {
@@ -193,6 +194,40 @@ __global__ void gather_hll_kernel(const uint8_t* __restrict__ hll, const unsigne
   const uint32_t* s = (const uint32_t*)(hll + src[row] * (uint64_t)n_hll * HLL_M);
   uint32_t* d = (uint32_t*)(out + row * (uint64_t)n_hll * HLL_M);
   for (uint32_t w = threadIdx.x; w < words; w += blockDim.x) d[w] = s[w];
+}
+// Per sketch: sum of 2^-register and the number of zero registers, the two inputs of the HLL++ estimator
+// (Spark HyperLogLogPlusPlusHelper.query).  One warp per sketch, 16 registers per lane.  Every term is a power of two
+// and the partial sums of a real sketch stay inside 53 bits, so the sum is exact in any order.
+__global__ void hll_stats_kernel(const uint8_t* __restrict__ regs, uint64_t n_sets, double* __restrict__ out) {
+  const uint64_t set = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (set >= n_sets) return;
+  const int lane = threadIdx.x & 31;
+  const uint4 v = __ldg((const uint4*)(regs + set * HLL_M) + lane);
+  const unsigned w[4] = {v.x, v.y, v.z, v.w};
+  double z = 0.0;
+  int zeros = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++)
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+      const unsigned r = (w[k] >> (8 * b)) & 63u;
+      z += __longlong_as_double((long long)(1023u - r) << 52);  // 2^-r
+      zeros += r == 0u;
+    }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    z += __shfl_xor_sync(0xffffffffu, z, off);
+    zeros += __shfl_xor_sync(0xffffffffu, zeros, off);
+  }
+  if (lane == 0) {
+    out[set * 2] = z;
+    out[set * 2 + 1] = (double)zeros;
+  }
+}
+void launch_hll_stats(const uint8_t* regs, uint64_t n_sets, double* out, cudaStream_t st) {
+  if (!n_sets) return;
+  hll_stats_kernel<<<(unsigned)((n_sets + 7) / 8), 256, 0, st>>>(regs, n_sets, out);
+  SDO_CUDA(cudaGetLastError());
 }
 void launch_gather_hll(const uint8_t* hll, const unsigned long long* src, uint64_t n, int n_hll, uint8_t* out, cudaStream_t st) {
   if (!n) return;

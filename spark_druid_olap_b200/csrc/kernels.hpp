@@ -158,6 +158,8 @@ struct ScanParams {
   uint32_t hstride;             // HASH: words per bucket
   int32_t n_exprs;
   DevExpr exprs[MAX_EXPRS];
+  int32_t hll_wide;  // shared-memory sketches keep one 32-bit word per register (native atomicMax) instead of one byte
+  int32_t pad2;
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 
@@ -176,7 +178,7 @@ void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut
 
 // scan
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots);
-size_t scan_hll_smem_bytes(int hll_mode, uint64_t n_keys, int n_hll);
+size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll);
 int scan_grid_size(int strategy, size_t smem_bytes, int sm_count);
 void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem_bytes, cudaStream_t st);
 void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, const uint64_t* slot_init_dev_or_null,
@@ -191,6 +193,8 @@ void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int 
 void launch_compact_hash(const unsigned long long* table, uint64_t cap, int n_slots, uint32_t stride,
                          unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
                          unsigned long long* counter, cudaStream_t st);
+// out[2 * set] = sum over the sketch's registers of 2^-register, out[2 * set + 1] = count of zero registers
+void launch_hll_stats(const uint8_t* regs, uint64_t n_sets, double* out, cudaStream_t st);
 void launch_gather_hll(const uint8_t* hll, const unsigned long long* src, uint64_t n, int n_hll, uint8_t* out, cudaStream_t st);
 // top-k of (metric, key) rows: ord = order-preserving u64 of the metric (descending = larger first)
 void launch_topk(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int slot, int slot_is_f64,

@@ -60,6 +60,7 @@ namespace sdo {
 #define Q_N_SLOTS jit::n_slots
 #define Q_N_HLL jit::n_hll
 #define Q_HLL_PLACE jit::hll_place
+#define Q_HLL_WIDE jit::hll_wide
 #define Q_IGNORE_KEY_BASE jit::ignore_key_base
 #define Q_N_COLS jit::n_cols
 #define Q_SLOT_OP(s) jit::slot_op[s]
@@ -89,6 +90,7 @@ namespace sdo {
 #define Q_N_SLOTS p.n_slots
 #define Q_N_HLL p.n_hll
 #define Q_HLL_PLACE p.hll_mode
+#define Q_HLL_WIDE p.hll_wide
 #define Q_IGNORE_KEY_BASE p.ignore_key_base
 #define Q_N_COLS p.n_cols
 #define Q_SLOT_OP(s) p.slot_op[s]
@@ -186,12 +188,26 @@ __device__ __forceinline__ void hll_update_sm(unsigned int* words, uint32_t pack
     old = prev;
   }
 }
-// merge `n_words` shared-memory sketch words into the HBM registers (byte-wise max) and clear them
+// wide layout: one 32-bit word per register, so an update is a single native shared-memory atomicMax (no read, no
+// compare-and-swap loop); costs 4x the shared memory of the packed layout
+__device__ __forceinline__ void hll_update_sm_wide(unsigned int* regs, uint32_t packed) { atomicMax(regs + (packed >> 6), packed & 63u); }
+// merge `n_words` packed words (4 registers each) of shared-memory sketches into the HBM registers (byte-wise max) and
+// clear them; WIDE: the shared-memory copy holds one word per register
+template <bool WIDE>
 __device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned int* global_words, uint32_t n_words) {
   for (uint32_t w = threadIdx.x; w < n_words; w += SCAN_THREADS) {
-    const unsigned int mine = sm_words[w];
-    if (!mine) continue;
-    sm_words[w] = 0u;
+    unsigned int mine;
+    if (WIDE) {
+      uint4* q = (uint4*)sm_words + w;
+      const uint4 r = *q;
+      mine = r.x | (r.y << 8) | (r.z << 16) | (r.w << 24);
+      if (!mine) continue;
+      *q = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+      mine = sm_words[w];
+      if (!mine) continue;
+      sm_words[w] = 0u;
+    }
     unsigned int old = *(volatile unsigned int*)(global_words + w);
     for (;;) {
       const unsigned int nw = __vmaxu4(old, mine);
@@ -578,7 +594,8 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
               hll_update(regs, packed);
             } else {
               const uint32_t set = (Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (uint32_t)key[i] * (uint32_t)Q_N_HLL : 0u) + (uint32_t)Q_AGG_HLL_INDEX(a);
-              hll_update_sm(acc.hll_sm + set * (HLL_M / 4), packed);
+              if (Q_HLL_WIDE) hll_update_sm_wide(acc.hll_sm + set * HLL_M, packed);
+              else hll_update_sm(acc.hll_sm + set * (HLL_M / 4), packed);
             }
           }
         break;
@@ -653,11 +670,13 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   Acc<STRAT> acc;
   acc.ns = ns;
   // shared-memory HLL sketches sit behind the aggregate table
-  const uint32_t hll_sm_words = Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (uint32_t)p.n_keys * Q_N_HLL * (HLL_M / 4)
-                                : (Q_HLL_PLACE == HLL_IN_SMEM_SPAN ? (uint32_t)Q_N_HLL * (HLL_M / 4) : 0u);
+  // hll_words = packed words (4 registers each) the block's sketches merge into; the shared copy is 4x that when wide
+  const uint32_t hll_words = Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (uint32_t)p.n_keys * Q_N_HLL * (HLL_M / 4)
+                             : (Q_HLL_PLACE == HLL_IN_SMEM_SPAN ? (uint32_t)Q_N_HLL * (HLL_M / 4) : 0u);
+  const uint32_t hll_sm_words = Q_HLL_WIDE ? hll_words * 4u : hll_words;
   {
     size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS : (STRAT == STRAT_BLOCK ? (size_t)p.n_keys * ns : 0);
-    acc.hll_sm = (unsigned int*)(smem + table_words);
+    acc.hll_sm = (unsigned int*)(smem + ((table_words + 1) & ~(size_t)1));  // 16-byte aligned (the host pads likewise)
     for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
   }
   uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (block-uniform)
@@ -701,7 +720,11 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
       if (Q_HLL_PLACE == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
         // the cached sketch belongs to another group: merge it into HBM, start an empty one
         __syncthreads();
-        if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M), hll_sm_words);
+        if (hll_key != ~0ull) {
+          unsigned int* dst = (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M);
+          if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words);
+          else hll_flush_sm<false>(acc.hll_sm, dst, hll_words);
+        }
         hll_key = sp.key_base;
         __syncthreads();
       }
@@ -710,8 +733,11 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   }
   if (hll_sm_words) {
     __syncthreads();
-    if (Q_HLL_PLACE == HLL_IN_SMEM_ALL) hll_flush_sm(acc.hll_sm, (unsigned int*)p.hll, hll_sm_words);
-    else if (hll_key != ~0ull) hll_flush_sm(acc.hll_sm, (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M), hll_sm_words);
+    unsigned int* dst = Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (unsigned int*)p.hll : (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M);
+    if (Q_HLL_PLACE == HLL_IN_SMEM_ALL || hll_key != ~0ull) {
+      if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words);
+      else hll_flush_sm<false>(acc.hll_sm, dst, hll_words);
+    }
   }
 
   if (STRAT == STRAT_LANE) {

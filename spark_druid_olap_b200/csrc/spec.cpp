@@ -419,6 +419,8 @@ QuerySpec parse_query_spec(const Json& j) {
     q.query_id = c->get_str("queryId", "");
     q.skip_empty_buckets = c->get_bool("skipEmptyBuckets", true);
     q.gpu_strategy = c->get_str("gpuStrategy", "");
+    q.gpu_hll_place = c->get_str("gpuHllPlace", "");
+    if (!q.gpu_hll_place.empty() && q.gpu_hll_place != "global" && q.gpu_hll_place != "shared") throw Invalid("context.gpuHllPlace must be 'global' or 'shared'");
     if (c->has("gpuJit")) q.gpu_jit = c->get_bool("gpuJit", false) ? 1 : 0;
     if (const Json* tb = c->find("gpuTimeBoundary")) {
       if (!tb->is_arr() || tb->arr.size() != 2 || !tb->arr[0].is_num() || !tb->arr[1].is_num()) throw Invalid("context.gpuTimeBoundary must be [minMs, maxMs]");

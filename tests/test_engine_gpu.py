@@ -116,6 +116,23 @@ def test_timeseries_granularity_hll(loaded, period):
     assert np.array_equal(res.hll["custs"][order], regs["custs"])
 
 
+@pytest.mark.parametrize("place", ["global", "shared"])
+@pytest.mark.parametrize("shape", ["ts_month", "ts_day", "year_nation", "agg_zoo", "basic_agg"])
+def test_hll_register_placement(loaded, shape, place):
+    """Sketches in HBM, or per block in shared memory (one cached sketch per span, every group's sketches packed 4
+    registers per word, or one word per register): the registers are identical."""
+    eng, tbl = loaded
+    spec = {"ts_month": lambda: Q.timeseries("P1M"), "ts_day": lambda: Q.timeseries("P1D"), "agg_zoo": lambda: Q.agg_zoo("block"),
+            "year_nation": lambda: Q.with_extraction(Q.extraction_dims()[0][1], "s_nation"), "basic_agg": lambda: Q.basic_agg("block")}[shape]()
+    q = json.loads(spec.to_json())
+    q["context"] = dict(q.get("context") or {}, gpuHllPlace=place)
+    res = eng.execute(q)
+    want, regs = orc.execute(tbl, q, return_registers=True)
+    H.assert_rows_equal(H.engine_rows(res), want, what=f"{shape} {place}")
+    for name, r in regs.items():
+        assert sorted(map(bytes, res.hll[name])) == sorted(map(bytes, r)), name
+
+
 def test_timeseries_simple_granularity_strings(loaded):
     eng, tbl = loaded
     for g in ("day", "month", "year"):
