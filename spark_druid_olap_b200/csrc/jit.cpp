@@ -97,7 +97,9 @@ std::string table(const char* name, int n, F f) {
 }
 
 std::string prelude(int strategy, const ScanParams& p) {
-  std::string s = "#define SDO_JIT 1\nnamespace sdo { namespace jit {\n";
+  static const char* nv_env = getenv("SDO_JIT_NV");  // experiment knob: vectors per dense-path accumulate call
+  static const char* wt_env = getenv("SDO_JIT_WARP_TICKETS");  // experiment knob: 0 = block tickets
+  std::string s = std::string("#define SDO_JIT 1\n") + "#define SDO_WARP_TICKETS " + (wt_env && *wt_env == '0' ? "0" : "1") + "\n#define SDO_DENSE_NV " + std::string(nv_env && *nv_env ? nv_env : "1") + "\nnamespace sdo { namespace jit {\n";
   s += "constexpr int n_ops = " + std::to_string(p.n_ops) + ";\n";
   s += table<int>("op_code", p.n_ops, [&](int i) { return p.op_code[i]; });
   s += table<int>("op_arg", p.n_ops, [&](int i) { return p.op_arg[i]; });
@@ -131,10 +133,17 @@ std::string prelude(int strategy, const ScanParams& p) {
   s += "constexpr int n_hll = " + std::to_string(p.n_hll) + ";\n";
   s += "constexpr int hll_place = " + std::to_string(p.hll_mode) + ";\n";
   s += "constexpr int hll_wide = " + std::to_string(p.hll_wide) + ";\n";
+  s += "constexpr unsigned ticket_shift = " + std::to_string(p.ticket_shift) + ";\n";
   s += "constexpr int ignore_key_base = " + std::to_string(p.ignore_key_base) + ";\n";
   s += "constexpr int n_cols = " + std::to_string(p.n_cols) + ";\n";
   s += "}}\n#include \"scan_kernel.cuh\"\n";
-  s += "extern \"C\" __global__ void __launch_bounds__(256, 4) sdo_scan_jit(const __grid_constant__ sdo::ScanParams p, const uint32_t* __restrict__ coarse) {\n";
+  static const char* mb_env = getenv("SDO_JIT_MINBLOCKS");  // experiment knob: resident blocks per SM the compiler aims for
+  // Registers per thread follow from the blocks per SM the compiler is told to fit (measured on SF10): wide shapes
+  // (seven aggregates, six of them expressions) are fastest at 3 blocks / 85 registers -- 0.71 ms vs 0.86 at 4 and 1.17
+  // at 6, the rest being spills; narrow ones (one or two aggregates, no sketch) gain a few percent at 6 blocks / 40 registers.
+  const int weight = p.n_aggs + 2 * p.n_exprs + p.n_dims;
+  const std::string min_blocks = mb_env && *mb_env ? mb_env : (weight >= 8 ? "3" : (weight >= 3 || p.n_hll > 0) ? "4" : "6");
+  s += "extern \"C\" __global__ void __launch_bounds__(256, " + min_blocks + ") sdo_scan_jit(const __grid_constant__ sdo::ScanParams p, const uint32_t* __restrict__ coarse) {\n";
   s += "  sdo::scan_body<" + std::to_string(strategy) + ">(p, coarse);\n}\n";
   return s;
 }

@@ -23,7 +23,7 @@ __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_cons
 size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll) {
   const size_t per_set = wide ? (size_t)HLL_M * 4 : (size_t)HLL_M;
   if (hll_mode == HLL_IN_SMEM_ALL) return (size_t)n_keys * n_hll * per_set;
-  if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * per_set;
+  if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * per_set * (SCAN_THREADS / 32);  // one cached group per warp
   return 0;
 }
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots) {

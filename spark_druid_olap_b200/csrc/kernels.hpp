@@ -31,6 +31,10 @@ constexpr int SCAN_THREADS = 256;
 constexpr int ROWS_PER_THREAD = 4;
 constexpr int UNIT_ROWS = SCAN_THREADS * ROWS_PER_THREAD * 4;  // 4096 rows: one pass of a block (4 vectors per thread)
 constexpr uint64_t HASH_EMPTY = 0xFFFFFFFFFFFFFFFFull;
+// ScanParams::counters: word 0 = block-ticket counter, word 1 = hash overflow flag, words 4-5 = compaction cursor,
+// word 32 * (g + 1) = ticket counter of region g (128 bytes apart: one L2 atomic unit is not a bottleneck for the others)
+constexpr int TICKET_REGIONS = 16;
+constexpr int COUNTER_BYTES = 128 * (TICKET_REGIONS + 1);
 
 // A span is a run of rows of one segment that shares its time-derived key part; interval pruning
 // and time bucketing are resolved to spans on the host, so kernels never read a time column.
@@ -159,7 +163,7 @@ struct ScanParams {
   int32_t n_exprs;
   DevExpr exprs[MAX_EXPRS];
   int32_t hll_wide;  // shared-memory sketches keep one 32-bit word per register (native atomicMax) instead of one byte
-  int32_t pad2;
+  int32_t ticket_shift;  // log2 of the rows a warp draws per ticket (9 .. 12)
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 

@@ -61,6 +61,7 @@ namespace sdo {
 #define Q_N_HLL jit::n_hll
 #define Q_HLL_PLACE jit::hll_place
 #define Q_HLL_WIDE jit::hll_wide
+#define Q_TICKET_SHIFT jit::ticket_shift
 #define Q_IGNORE_KEY_BASE jit::ignore_key_base
 #define Q_N_COLS jit::n_cols
 #define Q_SLOT_OP(s) jit::slot_op[s]
@@ -91,6 +92,7 @@ namespace sdo {
 #define Q_N_HLL p.n_hll
 #define Q_HLL_PLACE p.hll_mode
 #define Q_HLL_WIDE p.hll_wide
+#define Q_TICKET_SHIFT p.ticket_shift
 #define Q_IGNORE_KEY_BASE p.ignore_key_base
 #define Q_N_COLS p.n_cols
 #define Q_SLOT_OP(s) p.slot_op[s]
@@ -100,7 +102,25 @@ namespace sdo {
 #endif
 
 constexpr int VECS = UNIT_ROWS / (SCAN_THREADS * ROWS_PER_THREAD);  // vectors per thread per unit
-constexpr uint32_t VEC_STRIDE = SCAN_THREADS * ROWS_PER_THREAD;     // rows between a thread's vectors
+// Work distribution.  Warp tickets (default): every warp draws its own tickets of 1024 rows (a quarter unit) and walks
+// them in passes of 512 rows -- 32 lanes x 4 vectors x 4 rows, the vectors 128 rows apart -- so the main loop has no
+// block-wide barrier and warps drift apart freely.  Block tickets (SDO_WARP_TICKETS 0): the block draws chunks of two
+// units and all 256 threads walk a unit together, vectors 1024 rows apart.
+#ifndef SDO_WARP_TICKETS
+#define SDO_WARP_TICKETS 1
+#endif
+constexpr bool WARP_TICKETS = SDO_WARP_TICKETS != 0;
+constexpr uint32_t VEC_STRIDE = (WARP_TICKETS ? 32 : SCAN_THREADS) * ROWS_PER_THREAD;  // rows between a thread's vectors
+constexpr uint32_t PASS_ROWS = VEC_STRIDE * VECS;            // rows one pass of a warp (or of the block) covers
+// rows per ticket = 1 << ticket_shift (512 .. 4096), chosen per query shape by the host: long tickets where a warp pays
+// per ticket (flushing its cached sketch), short ones where work per row varies (selective filters, hash inserts)
+constexpr uint32_t UNIT_SHIFT = 12;
+static_assert((1u << UNIT_SHIFT) == UNIT_ROWS, "unit size");
+constexpr uint32_t TICKET_BATCH = 8;                         // consecutive tickets that belong to one region
+#ifndef SDO_DENSE_NV
+#define SDO_DENSE_NV 1
+#endif
+constexpr int DENSE_NV = SDO_DENSE_NV;  // vectors handed to one accumulate call on the dense path (1, 2 or 4)
 constexpr int SPARSE_MAX = 5;           // densest lane has at most this many survivors -> row-by-row path
 constexpr uint32_t COARSE_UNITS = 64;   // units per coarse span-index entry (plan.cpp builds it)
 
@@ -193,9 +213,12 @@ __device__ __forceinline__ void hll_update_sm(unsigned int* words, uint32_t pack
 __device__ __forceinline__ void hll_update_sm_wide(unsigned int* regs, uint32_t packed) { atomicMax(regs + (packed >> 6), packed & 63u); }
 // merge `n_words` packed words (4 registers each) of shared-memory sketches into the HBM registers (byte-wise max) and
 // clear them; WIDE: the shared-memory copy holds one word per register
+// (threads `first`, `first + step`, ... of the group that owns the sketches share the words)
 template <bool WIDE>
-__device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned int* global_words, uint32_t n_words) {
-  for (uint32_t w = threadIdx.x; w < n_words; w += SCAN_THREADS) {
+__device__ __forceinline__ void hll_flush_sm(unsigned int* sm_words, unsigned int* global_words, uint32_t n_words, uint32_t first, uint32_t step) {
+  // a warp flushing its own sketch makes 4 rounds per register set: unrolled so the 4 global reads overlap
+#pragma unroll 4
+  for (uint32_t w = first; w < n_words; w += step) {
     unsigned int mine;
     if (WIDE) {
       uint4* q = (uint4*)sm_words + w;
@@ -456,33 +479,86 @@ __device__ __forceinline__ void eval_expr(const ScanParams& p, int e, const void
   for (int i = 0; i < N; i++) out[i] = st[0][i];
 }
 
-// Aggregate N consecutive rows starting at r0 (N = 4: vector loads; N = 1: scalar loads); m = which rows.
+// Row set of one accumulate call: NV vectors of N consecutive rows each; row (v, i) = r0[v] + i.  Handing several
+// vectors to one call puts all their loads in flight together and folds a uniform-key warp once for all of them.
+template <int NV>
+struct RowSet { uint32_t r0[NV]; };
+template <int N, int NV>
+__device__ __forceinline__ void load_ids_m(const void* base, int width, const RowSet<NV>& rs, uint32_t (&out)[N * NV]) {
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    uint32_t t[N];
+    load_ids<N>(base, width, rs.r0[v], t);
+#pragma unroll
+    for (int i = 0; i < N; i++) out[v * N + i] = t[i];
+  }
+}
+template <int N, int NV>
+__device__ __forceinline__ void load_f64_m(const void* base, const RowSet<NV>& rs, double (&out)[N * NV]) {
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    double t[N];
+    load_f64<N>(base, rs.r0[v], t);
+#pragma unroll
+    for (int i = 0; i < N; i++) out[v * N + i] = t[i];
+  }
+}
+template <int N, int NV>
+__device__ __forceinline__ void load_i64_m(const void* base, const RowSet<NV>& rs, long long (&out)[N * NV]) {
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    long long t[N];
+    load_i64<N>(base, rs.r0[v], t);
+#pragma unroll
+    for (int i = 0; i < N; i++) out[v * N + i] = t[i];
+  }
+}
+template <int N, int NV>
+__device__ __forceinline__ uint32_t leaf_test_m(const ScanParams& p, int l, const void* const* cols, const RowSet<NV>& rs) {
+  uint32_t m = 0;
+#pragma unroll
+  for (int v = 0; v < NV; v++) m |= leaf_test<N>(p, l, cols, rs.r0[v]) << (v * N);
+  return m;
+}
+template <int N, int NV>
+__device__ __forceinline__ void eval_expr_m(const ScanParams& p, int e, const void* const* cols, const RowSet<NV>& rs, double (&out)[N * NV]) {
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+    double t[N];
+    eval_expr<N>(p, e, cols, rs.r0[v], t);
+#pragma unroll
+    for (int i = 0; i < N; i++) out[v * N + i] = t[i];
+  }
+}
+
+// Aggregate the rows of `r0` (N = 4: vector loads; N = 1: scalar loads); bit v * N + i of m = row (v, i) takes part.
 // WARP = called by all 32 lanes together (lanes without rows pass m = 0): lets a warp whose surviving
 // rows all share one key (time buckets, sorted low-cardinality keys) fold them with shuffles and
 // issue one atomic per aggregate instead of one per row.
-template <int STRAT, int N, bool WARP>
+template <int STRAT, int N, int NV, bool WARP>
 __device__ __forceinline__ void accumulate(const ScanParams& p, const void* const* cols, const Acc<STRAT>& acc, uint64_t key_base,
-                                           uint32_t r0, uint32_t m) {
+                                           const RowSet<NV>& r0, uint32_t m) {
+  constexpr int R = N * NV;  // rows handled by this call
   typedef typename Acc<STRAT>::key_t key_t;
-  key_t key[N];
+  key_t key[R];
 #pragma unroll
-  for (int i = 0; i < N; i++) key[i] = (key_t)key_base;
+  for (int i = 0; i < R; i++) key[i] = (key_t)key_base;
   Q_UNROLL
   for (int d = 0; d < Q_N_DIMS; d++) {
-    uint32_t ids[N];
-    load_ids<N>(cols[Q_DIM_COL(d)], Q_DIM_WIDTH(d), r0, ids);
+    uint32_t ids[R];
+    load_ids_m<N, NV>(cols[Q_DIM_COL(d)], Q_DIM_WIDTH(d), r0, ids);
     if (Q_DIM_REMAP(d)) {
       const uint32_t* lut = p.dims[d].remap;
 #pragma unroll
-      for (int i = 0; i < N; i++) ids[i] = __ldg(lut + ids[i]);
+      for (int i = 0; i < R; i++) ids[i] = __ldg(lut + ids[i]);
     }
     const key_t stride = (key_t)p.dims[d].stride;
 #pragma unroll
-    for (int i = 0; i < N; i++) key[i] += (key_t)ids[i] * stride;
+    for (int i = 0; i < R; i++) key[i] += (key_t)ids[i] * stride;
   }
   if (STRAT == STRAT_HASH) {
 #pragma unroll
-    for (int i = 0; i < N; i++) {
+    for (int i = 0; i < R; i++) {
       if ((m >> i) & 1u) {
         uint64_t h = hash_claim(p.hkeys, p.hmask, p.hstride, (uint64_t)key[i]);
         if (h == HASH_EMPTY) { p.counters[1] = 1; m &= ~(1u << i); }
@@ -491,19 +567,19 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
     }
   }
   // row pointers: slot s of row i lives at row[i] + s * Acc::SLOT_STRIDE
-  unsigned long long* row[N];
+  unsigned long long* row[R];
 #pragma unroll
-  for (int i = 0; i < N; i++) row[i] = acc.at(key[i]);
+  for (int i = 0; i < R; i++) row[i] = acc.at(key[i]);
   bool uni = false, is_leader = false;
   unsigned long long* rowL = row[0];
   if (WARP && STRAT != STRAT_LANE) {
     key_t lk = key[0];
 #pragma unroll
-    for (int i = N - 1; i >= 0; i--)
+    for (int i = R - 1; i >= 0; i--)
       if ((m >> i) & 1u) { lk = key[i]; rowL = row[i]; }
     bool same = true;
 #pragma unroll
-    for (int i = 0; i < N; i++)
+    for (int i = 0; i < R; i++)
       if (((m >> i) & 1u) && key[i] != lk) same = false;
     const unsigned have = __ballot_sync(0xffffffffu, m != 0u);
     const int leader = __ffs(have) - 1;
@@ -516,7 +592,7 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
     if (is_leader) acc.countn(rowL, c);
   } else {
 #pragma unroll
-    for (int i = 0; i < N; i++)
+    for (int i = 0; i < R; i++)
       if ((m >> i) & 1u) acc.count1(row[i]);  // slot 0: row count of the group
   }
 
@@ -524,13 +600,13 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
   for (int a = 0; a < Q_N_AGGS; a++) {
     uint32_t ma = m;
     if (Q_AGG_LEAF(a) >= 0) {
-      ma &= leaf_test<N>(p, Q_AGG_LEAF(a), cols, r0);
+      ma &= leaf_test_m<N, NV>(p, Q_AGG_LEAF(a), cols, r0);
       if (!WARP && !ma) continue;
     }
     const int so = Q_AGG_SLOT(a) * Acc<STRAT>::SLOT_STRIDE;
     const void* col = Q_AGG_OP(a) >= AGG_SUM_EXPR ? nullptr : cols[Q_AGG_COL(a)];  // *_EXPR: col is an expression index
 #define SDO_ROWS(EXPR)                                     \
-  _Pragma("unroll") for (int i = 0; i < N; i++) {          \
+  _Pragma("unroll") for (int i = 0; i < R; i++) {          \
     if ((ma >> i) & 1u) {                                  \
       unsigned long long* q = row[i] + so;                 \
       EXPR;                                                \
@@ -540,53 +616,53 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
 #define SDO_SUMF(VAL)                                                                   \
   if (uni) {                                                                            \
     double t = 0.0;                                                                     \
-    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t += (VAL);       \
+    _Pragma("unroll") for (int i = 0; i < R; i++) if ((ma >> i) & 1u) t += (VAL);       \
     t = warp_add(t);                                                                    \
     if (is_leader) acc.add_f64(rowL + so, t);                                           \
   } else { SDO_ROWS(acc.add_f64(q, (VAL))) }
 #define SDO_SUMI(VAL)                                                                   \
   if (uni) {                                                                            \
     long long t = 0;                                                                    \
-    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t += (VAL);       \
+    _Pragma("unroll") for (int i = 0; i < R; i++) if ((ma >> i) & 1u) t += (VAL);       \
     t = warp_add(t);                                                                    \
     if (is_leader) acc.add_i64(rowL + so, t);                                           \
   } else { SDO_ROWS(acc.add_i64(q, (VAL))) }
 #define SDO_MINI(VAL)                                                                   \
   if (uni) {                                                                            \
     long long t = 0x7FFFFFFFFFFFFFFFll;                                                 \
-    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t = min(t, (long long)(VAL)); \
+    _Pragma("unroll") for (int i = 0; i < R; i++) if ((ma >> i) & 1u) t = min(t, (long long)(VAL)); \
     t = warp_min(t);                                                                    \
     if (is_leader) acc.min_i64(rowL + so, t);                                           \
   } else { SDO_ROWS(acc.min_i64(q, (VAL))) }
 #define SDO_MAXI(VAL)                                                                   \
   if (uni) {                                                                            \
     long long t = (long long)0x8000000000000000ull;                                     \
-    _Pragma("unroll") for (int i = 0; i < N; i++) if ((ma >> i) & 1u) t = max(t, (long long)(VAL)); \
+    _Pragma("unroll") for (int i = 0; i < R; i++) if ((ma >> i) & 1u) t = max(t, (long long)(VAL)); \
     t = warp_max(t);                                                                    \
     if (is_leader) acc.max_i64(rowL + so, t);                                           \
   } else { SDO_ROWS(acc.max_i64(q, (VAL))) }
     switch (Q_AGG_OP(a)) {
-      case AGG_SUM_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_SUMF(v[i]) break; }
-      case AGG_SUM_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_SUMI(v[i]) break; }
+      case AGG_SUM_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_SUMF(v[i]) break; }
+      case AGG_SUM_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_SUMI(v[i]) break; }
       case AGG_COUNT_IF: { SDO_SUMI(1ll) break; }
-      case AGG_MIN_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
-      case AGG_MAX_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
-      case AGG_MIN_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_MINI(v[i]) break; }
-      case AGG_MAX_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_MAXI(v[i]) break; }
-      case AGG_SUM_F64_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_SUMF((double)v[i]) break; }
-      case AGG_MIN_F64_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_MINI(f64_to_ord((double)v[i])) break; }
-      case AGG_MAX_F64_I64: { long long v[N]; load_i64<N>(col, r0, v); SDO_MAXI(f64_to_ord((double)v[i])) break; }
-      case AGG_SUM_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_SUMI((long long)v[i]) break; }
-      case AGG_MIN_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MINI((long long)v[i]) break; }
-      case AGG_MAX_I64_F64: { double v[N]; load_f64<N>(col, r0, v); SDO_MAXI((long long)v[i]) break; }
-      case AGG_SUM_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_SUMF(v[i]) break; }
-      case AGG_MIN_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
-      case AGG_MAX_EXPR: { double v[N]; eval_expr<N>(p, Q_AGG_COL(a), cols, r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
+      case AGG_MIN_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
+      case AGG_MAX_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
+      case AGG_MIN_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_MINI(v[i]) break; }
+      case AGG_MAX_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_MAXI(v[i]) break; }
+      case AGG_SUM_F64_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_SUMF((double)v[i]) break; }
+      case AGG_MIN_F64_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_MINI(f64_to_ord((double)v[i])) break; }
+      case AGG_MAX_F64_I64: { long long v[R]; load_i64_m<N, NV>(col, r0, v); SDO_MAXI(f64_to_ord((double)v[i])) break; }
+      case AGG_SUM_I64_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_SUMI((long long)v[i]) break; }
+      case AGG_MIN_I64_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_MINI((long long)v[i]) break; }
+      case AGG_MAX_I64_F64: { double v[R]; load_f64_m<N, NV>(col, r0, v); SDO_MAXI((long long)v[i]) break; }
+      case AGG_SUM_EXPR: { double v[R]; eval_expr_m<N, NV>(p, Q_AGG_COL(a), cols, r0, v); SDO_SUMF(v[i]) break; }
+      case AGG_MIN_EXPR: { double v[R]; eval_expr_m<N, NV>(p, Q_AGG_COL(a), cols, r0, v); SDO_MINI(f64_to_ord(v[i])) break; }
+      case AGG_MAX_EXPR: { double v[R]; eval_expr_m<N, NV>(p, Q_AGG_COL(a), cols, r0, v); SDO_MAXI(f64_to_ord(v[i])) break; }
       case AGG_HLL: {
-        uint32_t ids[N];
-        load_ids<N>(col, Q_AGG_WIDTH(a), r0, ids);
+        uint32_t ids[R];
+        load_ids_m<N, NV>(col, Q_AGG_WIDTH(a), r0, ids);
 #pragma unroll
-        for (int i = 0; i < N; i++)
+        for (int i = 0; i < R; i++)
           if ((ma >> i) & 1u) {
             const uint32_t packed = hll_value(Q_AGG_HLL_MODE(a), p.aggs[a].hll_lut, ids[i]);
             if (Q_HLL_PLACE == HLL_IN_GLOBAL) {
@@ -610,10 +686,10 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
   }
 }
 
-// One unit.  Must be called by all 256 threads of the block (uses full-warp collectives).
+// One pass: 16 rows per thread starting at `base` (this thread's first row), vectors VEC_STRIDE rows apart.  Must be
+// called by all 32 lanes of a warp together (uses full-warp collectives).
 template <int STRAT>
-__device__ __forceinline__ void process_unit(const ScanParams& p, const DevSpan& sp, uint32_t unit_in_span, const Acc<STRAT>& acc) {
-  const uint32_t base = (sp.row_begin & ~3u) + unit_in_span * UNIT_ROWS + threadIdx.x * ROWS_PER_THREAD;
+__device__ __forceinline__ void process_pass(const ScanParams& p, const DevSpan& sp, uint32_t base, const Acc<STRAT>& acc) {
   uint32_t m = 0, vmask = 0;
   if (base < sp.row_end) {
     const uint32_t left = sp.row_end - base;  // rows from this thread's first row to the span end
@@ -637,17 +713,21 @@ __device__ __forceinline__ void process_unit(const ScanParams& p, const DevSpan&
       if (m) {
         const int b = __ffs(m) - 1;
         m &= m - 1;
-        accumulate<STRAT, 1, false>(p, cols, acc, key_base, base + (uint32_t)(b >> 2) * VEC_STRIDE + (uint32_t)(b & 3), 1u);
+        RowSet<1> one;
+        one.r0[0] = base + (uint32_t)(b >> 2) * VEC_STRIDE + (uint32_t)(b & 3);
+        accumulate<STRAT, 1, 1, false>(p, cols, acc, key_base, one, 1u);
       }
     }
   } else {
 #pragma unroll 1
-    for (int j = 0; j < VECS; j++) {
-      const uint32_t mj = (m >> (4 * j)) & 0xFu;
+    for (int j = 0; j < VECS; j += DENSE_NV) {
+      const uint32_t mj = (m >> (4 * j)) & ((1u << (4 * DENSE_NV)) - 1u);
       if (!__any_sync(0xffffffffu, mj != 0u)) continue;
-      // lanes whose vector j lies outside the span join with m = 0 and read a harmless in-span address
-      const uint32_t r0 = ((vmask >> j) & 1u) ? base + j * VEC_STRIDE : (sp.row_begin & ~3u);
-      accumulate<STRAT, 4, true>(p, cols, acc, key_base, r0, mj);
+      // lanes whose vector lies outside the span join with m = 0 and read a harmless in-span address
+      RowSet<DENSE_NV> rs;
+#pragma unroll
+      for (int v = 0; v < DENSE_NV; v++) rs.r0[v] = ((vmask >> (j + v)) & 1u) ? base + (j + v) * VEC_STRIDE : (sp.row_begin & ~3u);
+      accumulate<STRAT, 4, DENSE_NV, true>(p, cols, acc, key_base, rs, mj);
     }
   }
 }
@@ -666,20 +746,26 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   extern __shared__ __align__(16) unsigned long long smem[];
   __shared__ uint32_t s_chunk, s_span;
   const int tid = threadIdx.x;
+  const uint32_t lane = tid & 31u, warp = tid >> 5;
   const int ns = Q_N_SLOTS;
   Acc<STRAT> acc;
   acc.ns = ns;
   // shared-memory HLL sketches sit behind the aggregate table
   // hll_words = packed words (4 registers each) the block's sketches merge into; the shared copy is 4x that when wide
+  // HLL_IN_SMEM_SPAN caches the sketches of one group at a time: per warp with warp tickets, per block otherwise
   const uint32_t hll_words = Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (uint32_t)p.n_keys * Q_N_HLL * (HLL_M / 4)
                              : (Q_HLL_PLACE == HLL_IN_SMEM_SPAN ? (uint32_t)Q_N_HLL * (HLL_M / 4) : 0u);
-  const uint32_t hll_sm_words = Q_HLL_WIDE ? hll_words * 4u : hll_words;
+  const uint32_t hll_copies = Q_HLL_PLACE == HLL_IN_SMEM_SPAN && WARP_TICKETS ? SCAN_THREADS / 32 : 1;
+  const uint32_t hll_copy_words = Q_HLL_WIDE ? hll_words * 4u : hll_words;
+  const uint32_t hll_sm_words = hll_copy_words * hll_copies;
   {
     size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS : (STRAT == STRAT_BLOCK ? (size_t)p.n_keys * ns : 0);
     acc.hll_sm = (unsigned int*)(smem + ((table_words + 1) & ~(size_t)1));  // 16-byte aligned (the host pads likewise)
     for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
+    if (hll_copies > 1) acc.hll_sm += warp * hll_copy_words;
   }
-  uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (block-uniform)
+  const uint32_t flush_first = hll_copies > 1 ? lane : (uint32_t)tid, flush_step = hll_copies > 1 ? 32u : (uint32_t)SCAN_THREADS;
+  uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (uniform over the warp / block)
   if (STRAT == STRAT_LANE) {
     const uint32_t n = (uint32_t)p.n_keys * ns;
     for (uint32_t x = 0; x < n; x++) smem[(size_t)x * SCAN_THREADS + tid] = p.slot_init[x % ns];
@@ -696,6 +782,65 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   }
   __syncthreads();
 
+  if (WARP_TICKETS) {
+    // Ticket draws of ~6000 warps would serialise on one address, so there are TICKET_REGIONS counters.  Region g owns
+    // the batches (runs of TICKET_BATCH consecutive tickets) whose index is g modulo TICKET_REGIONS: all regions advance
+    // through the rows at the same pace, so the GPU as a whole still walks one moving window (L2 locality of the group
+    // tables).  A warp starts at its block's region and moves on, never back, when a region runs dry.
+    const uint32_t ticket_rows = 1u << Q_TICKET_SHIFT, unit_ticket_shift = UNIT_SHIFT - Q_TICKET_SHIFT;
+    const uint32_t n_tickets = p.n_units << unit_ticket_shift;
+    const uint32_t round = TICKET_BATCH * TICKET_REGIONS, full = n_tickets / round, rem = n_tickets % round;
+    uint32_t region = blockIdx.x % TICKET_REGIONS, dry = 0;
+    DevSpan sp = p.spans[0];
+    uint32_t next_begin = 0;  // units [sp.unit_begin, next_begin) belong to the cached span
+    for (;;) {
+      uint32_t t = 0xFFFFFFFFu;
+      if (lane == 0) {
+        while (dry < TICKET_REGIONS) {
+          unsigned int* c = p.counters + 32 * (region + 1);
+          const uint32_t tail = rem > region * TICKET_BATCH ? min(TICKET_BATCH, rem - region * TICKET_BATCH) : 0u;
+          const uint32_t lim = full * TICKET_BATCH + tail;  // tickets this region owns
+          if (*(volatile unsigned int*)c < lim) {
+            const uint32_t k = atomicAdd(c, 1u);
+            if (k < lim) { t = ((k / TICKET_BATCH) * TICKET_REGIONS + region) * TICKET_BATCH + k % TICKET_BATCH; break; }
+          }
+          region = (region + 1) % TICKET_REGIONS;
+          dry++;
+        }
+      }
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (t == 0xFFFFFFFFu) break;
+      const uint32_t u = t >> unit_ticket_shift;
+      if (u < sp.unit_begin || u >= next_begin) {
+        // the span that holds unit u: the coarse index narrows it to a window, the lanes test 32 candidates at a time
+        const uint32_t lo = coarse[u / COARSE_UNITS], hi = coarse[u / COARSE_UNITS + 1];
+        uint32_t s = lo;
+        for (uint32_t s0 = lo; s0 <= hi; s0 += 32) {
+          const uint32_t c = s0 + lane;
+          const bool hit = c <= hi && c < p.n_spans && p.spans[c].unit_begin <= u && u < p.spans[c + 1].unit_begin;
+          const unsigned found = __ballot_sync(0xffffffffu, hit);
+          if (found) { s = s0 + (uint32_t)__ffs(found) - 1u; break; }
+        }
+        sp = p.spans[s];
+        next_begin = p.spans[s + 1].unit_begin;
+      }
+      const uint32_t row0 = (sp.row_begin & ~3u) + (u - sp.unit_begin) * UNIT_ROWS + (t & ((1u << unit_ticket_shift) - 1u)) * ticket_rows;
+      if (row0 >= sp.row_end) continue;  // the span ends before this quarter of its last unit
+      if (Q_HLL_PLACE == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
+        // the warp's cached sketch belongs to another group: merge it into HBM, start an empty one
+        __syncwarp();
+        if (hll_key != ~0ull) {
+          unsigned int* dst = (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M);
+          if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
+          else hll_flush_sm<false>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
+        }
+        hll_key = sp.key_base;
+        __syncwarp();
+      }
+#pragma unroll 1
+      for (uint32_t r = row0; r < row0 + ticket_rows && r < sp.row_end; r += PASS_ROWS) process_pass<STRAT>(p, sp, r + lane * ROWS_PER_THREAD, acc);
+    }
+  } else
   for (;;) {
     if (tid == 0) s_chunk = atomicAdd(&p.counters[0], 1u);
     __syncthreads();
@@ -722,21 +867,21 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
         __syncthreads();
         if (hll_key != ~0ull) {
           unsigned int* dst = (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M);
-          if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words);
-          else hll_flush_sm<false>(acc.hll_sm, dst, hll_words);
+          if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
+          else hll_flush_sm<false>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
         }
         hll_key = sp.key_base;
         __syncthreads();
       }
-      process_unit<STRAT>(p, sp, u - sp.unit_begin, acc);
+      process_pass<STRAT>(p, sp, (sp.row_begin & ~3u) + (u - sp.unit_begin) * UNIT_ROWS + tid * ROWS_PER_THREAD, acc);
     }
   }
   if (hll_sm_words) {
     __syncthreads();
     unsigned int* dst = Q_HLL_PLACE == HLL_IN_SMEM_ALL ? (unsigned int*)p.hll : (unsigned int*)(p.hll + hll_key * (uint64_t)Q_N_HLL * HLL_M);
     if (Q_HLL_PLACE == HLL_IN_SMEM_ALL || hll_key != ~0ull) {
-      if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words);
-      else hll_flush_sm<false>(acc.hll_sm, dst, hll_words);
+      if (Q_HLL_WIDE) hll_flush_sm<true>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
+      else hll_flush_sm<false>(acc.hll_sm, dst, hll_words, flush_first, flush_step);
     }
   }
 

@@ -419,6 +419,9 @@ QuerySpec parse_query_spec(const Json& j) {
     q.query_id = c->get_str("queryId", "");
     q.skip_empty_buckets = c->get_bool("skipEmptyBuckets", true);
     q.gpu_strategy = c->get_str("gpuStrategy", "");
+    q.gpu_ticket_rows = (int)c->get_num("gpuTicketRows", 0);
+    if (q.gpu_ticket_rows != 0 && q.gpu_ticket_rows != 512 && q.gpu_ticket_rows != 1024 && q.gpu_ticket_rows != 2048 && q.gpu_ticket_rows != 4096)
+      throw Invalid("context.gpuTicketRows must be 512, 1024, 2048 or 4096");
     q.gpu_hll_place = c->get_str("gpuHllPlace", "");
     if (!q.gpu_hll_place.empty() && q.gpu_hll_place != "global" && q.gpu_hll_place != "shared") throw Invalid("context.gpuHllPlace must be 'global' or 'shared'");
     if (c->has("gpuJit")) q.gpu_jit = c->get_bool("gpuJit", false) ? 1 : 0;

@@ -108,6 +108,7 @@ struct QuerySpec {
   std::string query_id;
   bool skip_empty_buckets = true;
   std::string gpu_strategy;  // context.gpuStrategy: force lane|block|global|hash (tests)
+  int gpu_ticket_rows = 0;   // context.gpuTicketRows: 512 | 1024 | 2048 | 4096 rows per warp ticket (tests, profiling); 0 = by shape
   std::string gpu_hll_place; // context.gpuHllPlace: force the HLL registers into global|shared memory (tests, profiling)
   int gpu_jit = -1;          // context.gpuJit: true / false force the run-time specialised kernel on / off (-1 = engine decides)
   // context.gpuTimeBoundary = [minMs, maxMs]: the datasource's time range over ALL shards, set by the

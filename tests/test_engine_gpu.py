@@ -133,6 +133,21 @@ def test_hll_register_placement(loaded, shape, place):
         assert sorted(map(bytes, res.hll[name])) == sorted(map(bytes, r)), name
 
 
+@pytest.mark.parametrize("rows", [512, 1024, 2048, 4096])
+@pytest.mark.parametrize("shape", ["q1", "q3_hash", "ts_day_hll", "by_orderkey", "q7"])
+def test_ticket_sizes(loaded, shape, rows):
+    """Warps draw tickets of 512 .. 4096 rows (the engine picks by shape; context.gpuTicketRows forces it): every row is
+    visited exactly once whatever the size, including the ragged last unit of each span."""
+    spec = {"q1": lambda: Q.q1_style(), "q3_hash": lambda: Q.q3(None, "hash"), "ts_day_hll": lambda: Q.timeseries("P1D"),
+            "by_orderkey": lambda: Q.by_orderkey(), "q7": lambda: Q.q7()}[shape]()
+    eng, tbl = loaded
+    q = json.loads(spec.to_json())
+    q["context"] = dict(q.get("context") or {}, gpuTicketRows=rows)
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, q), what=f"{shape} {rows}")
+    q["context"]["gpuJit"] = True
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, q), what=f"{shape} {rows} jit")
+
+
 def test_timeseries_simple_granularity_strings(loaded):
     eng, tbl = loaded
     for g in ("day", "month", "year"):
