@@ -353,7 +353,14 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
     p.hll = st->hll;
   }
 
-  size_t smem = scan_smem_bytes(strat, plan.n_keys, plan.n_slots);
+  if (strat == STRAT_BLOCK) {
+    // replicas of the shared table while they stay within 24 KB; an odd stride spreads the replicas over the banks
+    const uint32_t stride = (uint32_t)cells | 1u;
+    uint32_t rep = 32;
+    while (rep > 1 && (uint64_t)rep * stride * 8 > 24 * 1024) rep >>= 1;
+    if (rep > 1) { p.rep_mask = rep - 1; p.rep_stride = stride; }
+  }
+  size_t smem = scan_smem_bytes(strat, plan.n_keys, plan.n_slots, p.rep_mask + 1, p.rep_stride);
   p.hll_mode = HLL_IN_GLOBAL;
   if (plan.n_hll && strat != STRAT_HASH) {
     // keep the sketches in shared memory when they fit next to the aggregate table

@@ -5,6 +5,7 @@
 // multi-GPU partition / merge.
 #include <algorithm>
 #include <cstdio>
+#include <mutex>
 
 #include "common.hpp"
 #include "kernels.hpp"
@@ -26,16 +27,31 @@ size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll) 
   if (hll_mode == HLL_IN_SMEM_SPAN) return (size_t)n_hll * per_set * (SCAN_THREADS / 32);  // one cached group per warp
   return 0;
 }
-size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots) {
+size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots, uint32_t replicas, uint32_t rep_stride) {
   if (strategy == STRAT_LANE) return (size_t)n_keys * n_slots * SCAN_THREADS * 8;
-  if (strategy == STRAT_BLOCK) return (size_t)n_keys * n_slots * 8;
+  if (strategy == STRAT_BLOCK) return replicas > 1 ? (size_t)replicas * rep_stride * 8 : (size_t)n_keys * n_slots * 8;
   return 0;
 }
 
 template <int STRAT>
+static void opt_in_shared_memory() {
+  // Opt in to the largest dynamic shared memory once per device: the attribute belongs to the function, not to a
+  // launch, so setting it per query would let one host thread shrink it under another thread's pending launch.
+  static std::mutex mu;
+  static bool done[64] = {};
+  {
+    int dev = 0;
+    SDO_CUDA(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> lk(mu);
+    if (dev >= 0 && dev < 64 && !done[dev]) {
+      SDO_CUDA(cudaFuncSetAttribute(scan_kernel<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 64));
+      done[dev] = true;
+    }
+  }
+}
+template <int STRAT>
 static int occupancy(size_t smem) {
-  // static shared memory counts against the 48 KB default too, so opt in well before the edge
-  if (smem > 32 * 1024) SDO_CUDA(cudaFuncSetAttribute(scan_kernel<STRAT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  opt_in_shared_memory<STRAT>();
   int nb = 0;
   SDO_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, scan_kernel<STRAT>, SCAN_THREADS, smem));
   return nb;
@@ -57,10 +73,10 @@ void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem, cudaS
   // the coarse span index follows the n_spans + 1 span records in the same device blob
   const uint32_t* coarse = (const uint32_t*)(p.spans + p.n_spans + 1);
   switch (strategy) {
-    case STRAT_LANE: scan_kernel<STRAT_LANE><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
-    case STRAT_BLOCK: scan_kernel<STRAT_BLOCK><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
-    case STRAT_GLOBAL: scan_kernel<STRAT_GLOBAL><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
-    default: scan_kernel<STRAT_HASH><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    case STRAT_LANE: opt_in_shared_memory<STRAT_LANE>(); scan_kernel<STRAT_LANE><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    case STRAT_BLOCK: opt_in_shared_memory<STRAT_BLOCK>(); scan_kernel<STRAT_BLOCK><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    case STRAT_GLOBAL: opt_in_shared_memory<STRAT_GLOBAL>(); scan_kernel<STRAT_GLOBAL><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    default: opt_in_shared_memory<STRAT_HASH>(); scan_kernel<STRAT_HASH><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
   }
   SDO_CUDA(cudaGetLastError());
 }

@@ -164,6 +164,10 @@ struct ScanParams {
   DevExpr exprs[MAX_EXPRS];
   int32_t hll_wide;  // shared-memory sketches keep one 32-bit word per register (native atomicMax) instead of one byte
   int32_t ticket_shift;  // log2 of the rows a warp draws per ticket (9 .. 12)
+  // BLOCK: the shared-memory table is replicated; lane l works on replica l & rep_mask (rep_stride words apart), so lanes
+  // of a warp whose rows share a key rarely retry each other's 64-bit compare-and-swap adds.  Folded at block end.
+  uint32_t rep_mask;
+  uint32_t rep_stride;
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
 };
 
@@ -181,7 +185,7 @@ void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n
 void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut, int64_t n, uint16_t* out, cudaStream_t st);
 
 // scan
-size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots);
+size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots, uint32_t replicas = 1, uint32_t rep_stride = 0);
 size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll);
 int scan_grid_size(int strategy, size_t smem_bytes, int sm_count);
 void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem_bytes, cudaStream_t st);

@@ -759,7 +759,8 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   const uint32_t hll_copy_words = Q_HLL_WIDE ? hll_words * 4u : hll_words;
   const uint32_t hll_sm_words = hll_copy_words * hll_copies;
   {
-    size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS : (STRAT == STRAT_BLOCK ? (size_t)p.n_keys * ns : 0);
+    size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS
+                         : (STRAT == STRAT_BLOCK ? (p.rep_mask ? (size_t)(p.rep_mask + 1u) * p.rep_stride : (size_t)p.n_keys * ns) : 0);
     acc.hll_sm = (unsigned int*)(smem + ((table_words + 1) & ~(size_t)1));  // 16-byte aligned (the host pads likewise)
     for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
     if (hll_copies > 1) acc.hll_sm += warp * hll_copy_words;
@@ -772,8 +773,14 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
     acc.base = smem + tid;
   } else if (STRAT == STRAT_BLOCK) {
     const uint32_t n = (uint32_t)p.n_keys * ns;
-    for (uint32_t x = tid; x < n; x += SCAN_THREADS) smem[x] = p.slot_init[x % ns];
-    acc.base = smem;
+    if (p.rep_mask) {
+      const uint32_t total = (p.rep_mask + 1u) * p.rep_stride;
+      for (uint32_t x = tid; x < total; x += SCAN_THREADS) smem[x] = p.slot_init[(x % p.rep_stride) % ns];
+      acc.base = smem + (size_t)(lane & p.rep_mask) * p.rep_stride;
+    } else {
+      for (uint32_t x = tid; x < n; x += SCAN_THREADS) smem[x] = p.slot_init[x % ns];
+      acc.base = smem;
+    }
   } else if (STRAT == STRAT_HASH) {
     acc.base = p.table + 1;  // word 0 of a bucket is its key
     acc.ns = (int)p.hstride;
@@ -906,10 +913,11 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
     __syncthreads();
     const uint32_t n = (uint32_t)p.n_keys * ns;
     for (uint32_t x = tid; x < n; x += SCAN_THREADS) {
-      const unsigned long long v = smem[x];
       const int sl = x % ns;
-      if (v == p.slot_init[sl]) continue;
       const int op = p.slot_op[sl];
+      unsigned long long v = smem[x];
+      for (uint32_t r = 1; r <= p.rep_mask; r++) v = slot_merge(op, v, smem[(size_t)r * p.rep_stride + x]);
+      if (v == p.slot_init[sl]) continue;
       if (op == SLOT_SUM_I64) atomicAdd(p.table + x, v);
       else if (op == SLOT_SUM_F64) atomicAdd((double*)(p.table + x), __longlong_as_double((long long)v));
       else if (op == SLOT_MIN_I64) atomicMin((long long*)(p.table + x), (long long)v);
