@@ -25,7 +25,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 METRIC = "tpch_flat_rows_scanned_per_s"
 UNIT = "rows/s"
 Q5T_COLUMNS = ["s_region", "o_orderdate", "s_nation", "l_extendedprice"]
-Q5T_TRAFFIC_BYTES = 277343232  # ncu capture of scan_kernel on SF10 Q5T (profiles/r01_ncu_q5t_*): 273.58 MB read + 3.77 MB written
+Q5T_TRAFFIC_BYTES = 278798592  # ncu --set full capture of sdo_scan_jit on SF10 Q5T (profiles/r01_ncu_q5t_jit_v2_summary.txt): 275.67 MB read + 3.13 MB written
 EXTRA_COLUMNS = ["c_mktsegment", "o_orderkey", "o_shippriority", "l_returnflag", "l_linestatus", "l_quantity", "l_discount", "l_tax", "o_custkey"]
 
 
@@ -139,6 +139,7 @@ def main():
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--extra", action="store_true", help="also time the other config shapes (Q1, Q3L, timeseries, by-orderkey)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the CPU baseline leg (profiling runs)")
+    ap.add_argument("--load-shards", type=int, default=1, help="generate and load this rank's rows in this many pieces (bounds host memory at large --sf)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -162,10 +163,12 @@ def main():
     # weak scaling: dataset = SF x world, this rank holds shard `rank` of `world`
     t_load = time.perf_counter()
     eng.create_datasource("tpch")
-    tab = tpch.FlatTable(args.sf * world, cols, rank, world)
-    eng.load("tpch", tab.engine_columns(), partition=rank)
-    n_local = tab.n_rows
-    del tab
+    n_local = 0
+    for piece in range(args.load_shards):
+        tab = tpch.FlatTable(args.sf * world, cols, rank * args.load_shards + piece, world * args.load_shards)
+        eng.load("tpch", tab.engine_columns(), partition=rank * args.load_shards + piece)
+        n_local += tab.n_rows
+        del tab
     t_load = time.perf_counter() - t_load
 
     q5t = Q.q5_topn().to_json().encode()
@@ -270,7 +273,12 @@ def main():
         extra = {}
         shapes = [("q1_style", Q.q1_style()), ("q1_tpch_expressions", q1_tpch()), ("q3_limit10", Q.q3(10)), ("timeseries_day_hll", Q.timeseries("P1D")),
                   ("timeseries_month_hll", Q.timeseries("P1M")), ("year_of_orderdate_extraction", Q.with_extraction(Q.extraction_dims()[0][1], "s_nation")),
-                  ("by_orderkey_hash", Q.by_orderkey("hash")), ("by_orderkey", Q.by_orderkey())]
+                  ("by_orderkey_top10", Q.GroupByQuerySpec(Q.DS, [Q.DefaultDimensionSpec("o_orderkey")], Q.LimitSpec(10, [Q.OrderByColumnSpec("price", "descending")]),
+                                                           None, "all", None, [Q.agg("count", "n", "count"), Q.agg("doubleSum", "price", "l_extendedprice")], None, Q.ALL_TIME, None)),
+                  ("by_orderkey_top10_hash", Q.GroupByQuerySpec(Q.DS, [Q.DefaultDimensionSpec("o_orderkey")], Q.LimitSpec(10, [Q.OrderByColumnSpec("price", "descending")]),
+                                                                None, "all", None, [Q.agg("count", "n", "count"), Q.agg("doubleSum", "price", "l_extendedprice")], None, Q.ALL_TIME, Q.ctx("hash")))]
+        if args.sf <= 20:  # the full 1.5 M x SF-row result goes back to the host: bounded so a large --sf cannot exhaust host memory
+            shapes += [("by_orderkey_hash", Q.by_orderkey("hash")), ("by_orderkey", Q.by_orderkey())]
         for name, q in shapes:
             qb = q.to_json().encode()
             for _ in range(3):
@@ -284,7 +292,8 @@ def main():
                            "achieved_gbs": st["algorithmicBytes"] / (sum(sc) / 6 / 1000) / 1e9, "launches": st["launches"]}
         # BASELINE config 5's shape at this scale: the suite from concurrent callers on one engine handle
         # (docs/bi-benchmark/snap-sales-demo.jmx runs 4 thread groups; DruidPlanner.scala:83-90 allows 100 connections)
-        suite = [(n, q.to_json().encode()) for n, q in shapes[:6]] + [("q5_topn", q5t)]
+        suite = [(n, q.to_json().encode()) for n, q in shapes[:6]] + [("q5_topn", q5t)]  # Q1, Q1 with expressions, Q3, timeseries x2, year extraction, Q5
+        suite_rows = {n: eng.execute(qb).stats["rowsScanned"] for n, qb in suite}
         for n_threads in (1, 4, 16):
             lat = {n: [] for n, _ in suite}
             rows = [0]
@@ -296,12 +305,15 @@ def main():
                 for r in range(4):
                     for k in range(len(suite)):
                         n, qb = suite[(k + t) % len(suite)]
+                        # the C-ABI call itself (ctypes releases the GIL for its duration): building Python result
+                        # objects under the GIL would serialise the callers and measure the interpreter
                         t0 = time.perf_counter()
-                        res = eng.execute(qb)
+                        h = eng.execute_raw(qb)
                         dt = (time.perf_counter() - t0) * 1e3
+                        L.sdo_result_free(h)
                         with lock:
                             lat[n].append(dt)
-                            rows[0] += res.stats["rowsScanned"]
+                            rows[0] += suite_rows[n]
 
             ths = [threading.Thread(target=caller, args=(t,)) for t in range(n_threads)]
             for th in ths:

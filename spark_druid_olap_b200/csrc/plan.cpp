@@ -832,6 +832,13 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   if (plan.n_keys <= (1ull << 20) && cells <= opt.lane_max_cells) { strat = STRAT_LANE; why = "key space x slots = " + std::to_string(cells) + " cells fit lane-private shared memory"; }
   else if (plan.n_keys <= (1ull << 24) && cells * 8 <= opt.block_max_bytes) { strat = STRAT_BLOCK; why = "table of " + std::to_string(cells * 8) + " bytes fits shared memory"; }
   else if (plan.n_keys <= opt.global_max_keys) { strat = STRAT_GLOBAL; why = "dense key space of " + std::to_string(plan.n_keys) + " keys indexed directly in HBM"; }
+  else if (plan.n_hll == 0 && plan.n_keys <= opt.global_big_max_keys && plan.n_keys <= 4 * (uint64_t)std::max<int64_t>(plan.rows_scanned, 1) &&
+           cells * 8 <= opt.global_big_max_bytes) {
+    // a key space no sparser than a quarter of the scanned rows (group by o_orderkey at SF100: 150 M keys, 600 M rows):
+    // direct indexing costs memory HBM has, and runs 2.4x faster than hashing (SF10: 1.75 ms vs 4.29 ms)
+    strat = STRAT_GLOBAL;
+    why = "key space of " + std::to_string(plan.n_keys) + " keys is dense relative to " + std::to_string(plan.rows_scanned) + " rows: direct table of " + std::to_string(cells * 8) + " bytes in HBM";
+  }
   else { strat = STRAT_HASH; why = "key space of " + std::to_string(plan.n_keys) + " keys is sparse: open-addressing hash table"; }
   if (!spec.gpu_strategy.empty()) {
     const std::string& g = spec.gpu_strategy;

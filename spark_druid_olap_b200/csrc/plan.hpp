@@ -95,6 +95,8 @@ struct PlanOptions {
   uint64_t lane_max_cells = 48;                 // n_keys * n_slots for lane-private accumulators (96 KB of shared memory)
   uint64_t block_max_bytes = 160 * 1024;        // shared-memory table
   uint64_t global_max_keys = 1ull << 26;        // direct-indexed HBM table
+  uint64_t global_big_max_keys = 1ull << 31;    // ... and beyond that while the key space stays dense relative to the rows
+  uint64_t global_big_max_bytes = 24ull << 30;
   uint64_t hll_max_bytes = 8ull << 30;
   int64_t jit_min_rows = 2000000;               // scans at least this long get a shape-specialised kernel
 };
