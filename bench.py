@@ -177,17 +177,27 @@ def main():
     alg_bytes = plan["algorithmicBytes"]
 
     L = sdo.lib()
+    if world > 1:
+        import ctypes as C
+        sharded.init_comm(eng)                       # the engine's own NCCL communicator
+        q5t_all = sharded.prepare_query(eng, q5t)    # ids aligned across ranks, time keys on the global grid
 
     def step():
         """One Q5T query.  N = 1: the C-ABI call itself (query JSON in host memory in, columnar result in host memory out);
-        N > 1: partial scan on every rank, NCCL merge, result on rank 0.  Returns (stats JSON bytes, result rows) or None."""
+        N > 1: sdo_query_execute_sharded on every rank -- scan, NCCL all-gather of the partial tables and the fold on rank 0
+        queued by one C call; result on rank 0.  Returns (stats JSON bytes, result rows) or None."""
         if world == 1:
             h = eng.execute_raw(q5t)
             out = (L.sdo_result_stats_json(h), int(L.sdo_result_num_rows(h)))
             L.sdo_result_free(h)
             return out
-        r, info = sharded.execute_sharded(eng, q5t)
-        return (json.dumps(r.stats).encode(), r.n_rows) if r is not None else None
+        h = C.c_void_p()
+        sdo._check(L.sdo_query_execute_sharded(eng._h, q5t_all, len(q5t_all), 0, C.byref(h)))
+        if not h:
+            return None
+        out = (L.sdo_result_stats_json(h), int(L.sdo_result_num_rows(h)))
+        L.sdo_result_free(h)
+        return out
 
     def sync():
         torch.cuda.synchronize()

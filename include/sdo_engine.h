@@ -208,6 +208,24 @@ void* sdo_partial_stream(sdo_partial* p);
 int sdo_partial_finish(sdo_partial* p, sdo_result** out);
 void sdo_partial_free(sdo_partial* p);
 
+/* ---- sharded execution with the merge inside the library ---------------------------------------
+ * One engine per GPU, one process per engine.  Replaces the Spark-side re-aggregation of the per-historical partial
+ * results (SQD/DruidStrategy.scala:353-359, SQD/PostAggregate.scala:39-103) for dense key spaces whose table (and HLL
+ * registers) fit 4 MB: scan, one NCCL all-gather of the raw partial tables and the fold on `root` are queued on one
+ * stream by one call, without a round trip through the host language between them.
+ *
+ * sdo_comm_unique_id: on one rank; hand the 128 bytes to every rank (any channel).  `nccl_library` = path of
+ *   libnccl.so.2 to load if the process has none loaded yet (NULL: default search path).
+ * sdo_engine_comm_init: on every rank, collectively; the engine's device must be the calling thread's current one.
+ * sdo_query_execute_sharded: on every rank, collectively, with the same query (ids and time keys must mean the same on
+ *   every rank: same dictionaries, context.gpuTimeBoundary set -- what sharded.align_datasource arranges).  On `root`
+ *   *out is the merged result; elsewhere *out is NULL.  Shapes outside the dense / 4 MB case return SDO_UNSUPPORTED before
+ *   anything is queued (use sdo_query_partial and the host-side merge). */
+#define SDO_COMM_ID_BYTES 128
+int sdo_comm_unique_id(void* id_out, const char* nccl_library);
+int sdo_engine_comm_init(sdo_engine* e, const void* id, int rank, int world, const char* nccl_library);
+int sdo_query_execute_sharded(sdo_engine* e, const char* query_json, size_t len, int root, sdo_result** out);
+
 /* ---- allocation-free group-by ----------------------------------------------------------------
  * No counterpart in the reference (it has no native code and no notion of device memory).
  *

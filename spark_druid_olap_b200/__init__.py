@@ -105,6 +105,9 @@ def lib():
         "sdo_groupby_sum_noalloc": (C.c_int, [C.c_int, vp, vp, i64, C.c_int, vp, vp, vp]),
         "sdo_dimension_dictionary": (C.c_int, [vp, cp, cp, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), C.POINTER(i64)]),
         "sdo_dimension_extend": (C.c_int, [vp, cp, cp, i64, vp, vp, i64]),
+        "sdo_comm_unique_id": (C.c_int, [vp, cp]),
+        "sdo_engine_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int, cp]),
+        "sdo_query_execute_sharded": (C.c_int, [vp, cp, sz, C.c_int, C.POINTER(vp)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -121,9 +124,11 @@ EXPORTED_SYMBOLS = [
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
     "sdo_dimension_dictionary", "sdo_dimension_extend", "sdo_partial_export", "sdo_partial_merge_gathered",
+    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded",
 ]
 
 NOALLOC_MAX_KEYS = 24
+COMM_ID_BYTES = 128
 NOALLOC_MAX_ROWS = 1 << 32
 
 

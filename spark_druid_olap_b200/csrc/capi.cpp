@@ -236,4 +236,27 @@ void sdo_partial_free(sdo_partial* p) {
   delete p;
 }
 
+int sdo_comm_unique_id(void* id_out, const char* nccl_library) {
+  if (!id_out) return bad("sdo_comm_unique_id: NULL argument");
+  return guard([&] {
+    nccl_load(nccl_library);
+    nccl_unique_id(id_out);
+  });
+}
+int sdo_engine_comm_init(sdo_engine* e, const void* id, int rank, int world, const char* nccl_library) {
+  if (!e || !id) return bad("sdo_engine_comm_init: NULL argument");
+  return guard([&] {
+    nccl_load(nccl_library);
+    e->e->comm_init(id, rank, world);
+  });
+}
+int sdo_query_execute_sharded(sdo_engine* e, const char* query_json, size_t len, int root, sdo_result** out) {
+  if (!e || !query_json || !out) return bad("sdo_query_execute_sharded: NULL argument");
+  *out = nullptr;
+  return guard([&] {
+    Result* r = e->e->execute_sharded(query_json, len, root);
+    if (r) *out = new sdo_result{r};
+  });
+}
+
 }  // extern "C"

@@ -74,6 +74,7 @@ Engine::~Engine() {
   if (device_ >= 0) {
     cudaSetDevice(device_);
     cudaDeviceSynchronize();
+    if (comm_) nccl_comm_destroy(comm_);
     for (QueryCtx* c : free_ctx_) {
       if (c->stream) cudaStreamDestroy(c->stream);
       for (auto& e : c->ev)
@@ -1133,6 +1134,80 @@ std::string Engine::explain(const char* json, size_t len) {
 }
 
 // ---- sharded execution ---------------------------------------------------------------------------------
+void Engine::comm_init(const void* id, int rank, int world) {
+  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device");
+  if (world < 1 || rank < 0 || rank >= world) throw Invalid("sdo_engine_comm_init: rank / world out of range");
+  std::lock_guard<std::mutex> lk(comm_mu_);
+  if (comm_) throw Invalid("sdo_engine_comm_init: this engine already has a communicator");
+  SDO_CUDA(cudaSetDevice(device_));
+  comm_ = nccl_comm_init(id, rank, world);
+  comm_rank_ = rank;
+  comm_world_ = world;
+}
+
+// Scan the local segments, all-gather the raw partial tables (one contiguous blob per rank: aggregate slots + HLL
+// registers), fold them in rank order on `root`, finish there.  Everything is queued on one stream by this call.
+Result* Engine::execute_sharded(const char* json, size_t len, int root) {
+  if (!comm_) throw Invalid("sdo_query_execute_sharded: sdo_engine_comm_init has not been called on this engine");
+  if (root < 0 || root >= comm_world_) throw Invalid("sdo_query_execute_sharded: root out of range");
+  const double t0 = now_ms();
+  std::shared_lock<std::shared_mutex> lk;
+  std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk);
+  // every rank must produce the same table layout even when its own shard has no matching rows: scan zero units
+  Plan empty_variant;
+  const Plan* plan = plan_ptr.get();
+  if (plan->always_false) {
+    empty_variant = *plan;
+    empty_variant.spans.clear();
+    empty_variant.n_units = 0;
+    empty_variant.coarse.assign(2, 0);
+    empty_variant.rows_scanned = 0;
+    empty_variant.always_false = false;
+    plan = &empty_variant;
+  }
+  // the same decision on every rank, from the plan alone: dense table + registers within the gather limit
+  const uint64_t cells = plan->n_keys * (uint64_t)plan->n_slots;
+  const uint64_t blob = round_up(std::max<uint64_t>(cells, 1) * 8, 256) + (plan->n_hll ? plan->n_keys * (uint64_t)plan->n_hll * HLL_M : 0);
+  if (plan->strategy == STRAT_HASH || blob > (4ull << 20))
+    throw Unsupported("sdo_query_execute_sharded handles dense key spaces with at most 4 MB of partial state; use sdo_query_partial for this query");
+  QueryCtx* ctx = acquire_ctx();
+  ScanState st;
+  st.plan_ms = now_ms() - t0;
+  Result* r = nullptr;
+  void* gathered = nullptr;
+  try {
+    cudaStream_t s = ctx->stream;
+    run_scan(ctx, *plan, &st);
+    if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
+    SDO_CUDA(cudaMallocAsync(&gathered, blob * comm_world_, s));
+    {
+      std::lock_guard<std::mutex> g(comm_mu_);
+      nccl_all_gather_bytes(comm_, st.table, gathered, blob, s);
+    }
+    if (comm_rank_ == root) {
+      launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)plan->n_slots,
+                            plan->n_slots, st.params, st.table, s);
+      st.launches += 1;
+      SDO_CUDA(cudaFreeAsync(gathered, s));
+      gathered = nullptr;
+      r = finalize(ctx, *plan, &st, t0);
+    } else {
+      SDO_CUDA(cudaFreeAsync(gathered, s));
+      gathered = nullptr;
+      SDO_CUDA(cudaStreamSynchronize(s));
+    }
+  } catch (...) {
+    cudaStreamSynchronize(ctx->stream);
+    if (gathered) cudaFreeAsync(gathered, ctx->stream);
+    free_state(ctx, &st);
+    release_ctx(ctx);
+    throw;
+  }
+  free_state(ctx, &st);
+  release_ctx(ctx);
+  return r;
+}
+
 Partial* Engine::partial(const char* json, size_t len) {
   QuerySpec spec = parse_query_spec(json, len);
   auto ds = store_.get(spec.data_source);

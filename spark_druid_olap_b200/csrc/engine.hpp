@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 
+#include "comm.hpp"
 #include "plan.hpp"
 #include "store.hpp"
 
@@ -117,6 +118,9 @@ class Engine {
   Result* execute(const char* json, size_t len);
   std::string explain(const char* json, size_t len);
   void cancel(const std::string& query_id);
+  // sharded execution with the merge inside the library (dense key spaces, small tables)
+  void comm_init(const void* id, int rank, int world);
+  Result* execute_sharded(const char* json, size_t len, int root);
   Partial* partial(const char* json, size_t len);
   void partial_view(Partial* p, void* view_out);
   void partial_export(Partial* p, void* dst_dev, int64_t dst_bytes);
@@ -137,6 +141,9 @@ class Engine {
   std::set<std::string> cancelled_;
   std::mutex lut_mu_;
   PinnedPool pinned_pool_;
+  void* comm_ = nullptr;  // ncclComm_t of this engine's rank (sdo_engine_comm_init)
+  int comm_rank_ = 0, comm_world_ = 1;
+  std::mutex comm_mu_;    // collectives of one communicator must be issued in the same order on every rank
   Result* finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
 
   QueryCtx* acquire_ctx();

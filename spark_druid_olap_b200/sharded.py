@@ -14,9 +14,12 @@ The tensor-level functions work on any device/backend (the CPU tests drive them 
 execute_sharded binds them to an engine's device buffers without copies.
 """
 import json
+import os
 
 import torch
 import torch.distributed as dist
+
+import spark_druid_olap_b200 as sdo
 
 SLOT_SUM_I64, SLOT_SUM_F64, SLOT_MIN_I64, SLOT_MAX_I64 = 0, 1, 2, 3
 
@@ -144,16 +147,67 @@ def with_time_boundary(query, boundary):
     return query
 
 
+_comms = {}     # id(engine) -> (world, group id) of the communicator the engine owns
+_prepared = {}  # (id(engine), query text) -> query JSON bytes with the global time boundary set
+
+
+def _nccl_library():
+    """Path of the libnccl.so.2 PyTorch ships (the engine reuses the copy already loaded into the process if any)."""
+    import glob
+    import site
+    for sp in site.getsitepackages():
+        hits = glob.glob(os.path.join(sp, "nvidia", "nccl", "lib", "libnccl.so.2"))
+        if hits:
+            return hits[0].encode()
+    return None
+
+
+def init_comm(engine, group=None):
+    """Give `engine` its own NCCL communicator over the ranks of `group` (collective; once per engine), so that
+    sdo_query_execute_sharded can scan, gather and fold inside the library.  The unique id travels over `group`."""
+    import ctypes as C
+    if id(engine) in _comms:
+        return
+    rank, world = dist.get_rank(group), dist.get_world_size(group)
+    ident = C.create_string_buffer(sdo.COMM_ID_BYTES)
+    path = _nccl_library()
+    if rank == 0:
+        sdo._check(sdo.lib().sdo_comm_unique_id(ident, path))
+    box = [bytes(ident.raw)]
+    dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    sdo._check(sdo.lib().sdo_engine_comm_init(engine._h, box[0], rank, world, path))
+    _comms[id(engine)] = (world, id(group))
+
+
+def prepare_query(engine, query, group=None):
+    """Query JSON bytes every rank can run: dictionaries aligned, time keys on the global grid (cached per query)."""
+    text = query if isinstance(query, (bytes, str)) else (query.to_json() if hasattr(query, "to_json") else json.dumps(query, sort_keys=True))
+    key = (id(engine), text)
+    if key not in _prepared:
+        q = with_time_boundary(query, (0, 0))
+        align_datasource(engine, q["dataSource"], group)
+        _prepared[key] = json.dumps(with_time_boundary(q, global_time_boundary(engine, q["dataSource"], group))).encode()
+    return _prepared[key]
+
+
 def execute_sharded(engine, query, group=None, root=0, force_exchange=False):
     """Run `query` over every rank's local segments and return the merged Result on `root`
     (dense key spaces) or this rank's share of the groups (sparse key spaces; see `sparse` flag).
     Returns (result_or_None, info)."""
+    import ctypes as C
     world = dist.get_world_size(group)
     rank = dist.get_rank(group)
     if world > 1:
-        q = with_time_boundary(query, (0, 0))
-        align_datasource(engine, q["dataSource"], group)
-        query = with_time_boundary(q, global_time_boundary(engine, q["dataSource"], group))
+        query = prepare_query(engine, query, group)
+        if _comms.get(id(engine)) == (world, id(group)) and not force_exchange:
+            # merge inside the library: scan + NCCL all-gather + fold queued by one C call
+            out = C.c_void_p()
+            status = sdo.lib().sdo_query_execute_sharded(engine._h, query, len(query), root, C.byref(out))
+            if status == sdo.SDO_OK:
+                return (sdo.Result(out) if rank == root else None), {"dense": True, "native": True, "n_keys": -1, "n_slots": -1, "merge_bytes": -1}
+            if status != sdo.SDO_UNSUPPORTED or b"sdo_query_partial" not in sdo.lib().sdo_last_error():
+                sdo._check(status)
+            # a shape for the host-side merge below (every rank takes the same branch: the decision is made from the plan)
     part = engine.partial(query)
     try:
         v = part.view()

@@ -30,35 +30,40 @@ mine = tpch.FlatTable(sf, cols, rank, world)
 eng.load("tpch", mine.engine_columns(), partition=rank)
 whole = H.oracle_table([tpch.FlatTable(sf, cols, r, world) for r in range(world)])
 ok = True
-for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style("block"), False), ("ts_month_hll", Q.timeseries("P1M"), False),
-                            ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
-                            ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)]:
-    q = json.loads(spec.to_json())
-    print(f'[rank {rank}] {name} ...', flush=True)
-    res, info = sharded.execute_sharded(eng, q)
-    print(f'[rank {rank}] {name} engine done', flush=True)
-    want = orc.execute(whole, q)
-    try:
-        if info["dense"]:
-            if rank == 0:
-                H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered, what=name)
-        else:
-            # sparse: every rank holds a disjoint share; gather and compare the union
-            parts = [None] * world
-            rows_here = H.engine_rows(res)
-            cnt_col = [k for k in rows_here[0] if k in ('n',)] if rows_here else []
-            print(f'[rank {rank}] {name}: {len(rows_here)} result rows, sum n = {sum(r[cnt_col[0]] for r in rows_here) if cnt_col else None}, local rows {mine.n_rows}, info {info}', flush=True)
-            dist.all_gather_object(parts, rows_here)
-            if rank == 0:
-                allrows = [r for p in parts for r in p]
-                keys = [r.get('o_orderkey') for r in allrows]
-                print(f'union {len(allrows)} rows, distinct keys {len(set(keys))}, want {len(want)}', flush=True)
-                H.assert_rows_equal(allrows, want, what=name)
-        if rank == 0:
-            print(f"OK   {name:22s} dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
-    except AssertionError as e:
-        ok = False
-        print(f"FAIL {name} rank {rank}: {e}")
+# second pass: the same dense shapes with the merge inside the library (sdo_query_execute_sharded)
+passes = [("host-merge", False), ("native-merge", True)]
+for pass_name, native in passes:
+  if native:
+    sharded.init_comm(eng)
+  for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style("block"), False), ("ts_month_hll", Q.timeseries("P1M"), False),
+                              ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
+                              ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)]:
+      q = json.loads(spec.to_json())
+      print(f'[rank {rank}] {name} ...', flush=True)
+      res, info = sharded.execute_sharded(eng, q)
+      print(f'[rank {rank}] {name} engine done', flush=True)
+      want = orc.execute(whole, q)
+      try:
+          if info["dense"]:
+              if rank == 0:
+                  H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered, what=name)
+          else:
+              # sparse: every rank holds a disjoint share; gather and compare the union
+              parts = [None] * world
+              rows_here = H.engine_rows(res)
+              cnt_col = [k for k in rows_here[0] if k in ('n',)] if rows_here else []
+              print(f'[rank {rank}] {name}: {len(rows_here)} result rows, sum n = {sum(r[cnt_col[0]] for r in rows_here) if cnt_col else None}, local rows {mine.n_rows}, info {info}', flush=True)
+              dist.all_gather_object(parts, rows_here)
+              if rank == 0:
+                  allrows = [r for p in parts for r in p]
+                  keys = [r.get('o_orderkey') for r in allrows]
+                  print(f'union {len(allrows)} rows, distinct keys {len(set(keys))}, want {len(want)}', flush=True)
+                  H.assert_rows_equal(allrows, want, what=name)
+          if rank == 0:
+              print(f"OK   {name:22s} [{pass_name}{' in library' if info.get('native') else ''}] dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
+      except AssertionError as e:
+          ok = False
+          print(f"FAIL {name} rank {rank}: {e}")
 flag = torch.tensor([0 if ok else 1], device="cuda")
 dist.all_reduce(flag)
 if rank == 0:
