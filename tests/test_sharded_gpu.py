@@ -94,3 +94,30 @@ def test_sparse_partition_exchange_merge_on_one_rank(dist_engine, mk, ordered):
     res, info = sharded.execute_sharded(eng, q, force_exchange=True)
     assert not info["dense"]
     H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, q), ordered=ordered)
+
+
+def test_merge_inside_the_library_world1(dist_engine):
+    """sdo_query_execute_sharded with a one-rank communicator: scan, NCCL all-gather and fold queued by one C call give
+    what sdo_query_execute gives; sparse / large shapes are refused before anything is queued."""
+    import ctypes as C
+    import spark_druid_olap_b200 as sdo
+    from spark_druid_olap_b200 import sharded
+    eng, tbl, name = dist_engine
+    sharded.init_comm(eng)
+    sharded.init_comm(eng)  # idempotent
+    L = sdo.lib()
+    for mk, ordered in [(lambda: Q.q1_style(), False), (lambda: Q.q1_style("block"), False), (lambda: Q.timeseries("P1D"), False), (lambda: Q.q5_topn(), True),
+                        (lambda: Q.q1_style(), "no rows")]:
+        q = _with_ds(mk(), name)
+        if ordered == "no rows":  # a shard without a matching row still contributes an initialised table
+            q["filter"] = {"type": "selector", "dimension": "s_nation", "value": "ATLANTIS"}
+            ordered = False
+        qb = sharded.prepare_query(eng, q)
+        for _ in range(2):
+            h = C.c_void_p()
+            sdo._check(L.sdo_query_execute_sharded(eng._h, qb, len(qb), 0, C.byref(h)))
+            H.assert_rows_equal(H.engine_rows(sdo.Result(h)), orc.execute(tbl, q), ordered=ordered)
+    qb = sharded.prepare_query(eng, _with_ds(Q.by_orderkey("hash"), name))
+    h = C.c_void_p()
+    assert L.sdo_query_execute_sharded(eng._h, qb, len(qb), 0, C.byref(h)) == sdo.SDO_UNSUPPORTED and not h
+    assert L.sdo_query_execute_sharded(eng._h, qb, len(qb), 3, C.byref(h)) == sdo.SDO_INVALID
