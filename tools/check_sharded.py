@@ -37,7 +37,9 @@ for pass_name, native in passes:
     sharded.init_comm(eng)
   for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style("block"), False), ("ts_month_hll", Q.timeseries("P1M"), False),
                               ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
-                              ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)]:
+                              ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)] * int(os.environ.get("CHECK_REPEAT", "1")):
+      if os.environ.get("CHECK_ONLY") and name not in os.environ["CHECK_ONLY"].split(","):
+          continue
       q = json.loads(spec.to_json())
       print(f'[rank {rank}] {name} ...', flush=True)
       res, info = sharded.execute_sharded(eng, q)
@@ -63,7 +65,16 @@ for pass_name, native in passes:
               print(f"OK   {name:22s} [{pass_name}{' in library' if info.get('native') else ''}] dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
       except AssertionError as e:
           ok = False
-          print(f"FAIL {name} rank {rank}: {e}")
+          print(f"FAIL {name} [{pass_name}] rank {rank}: {e}")
+          if rank == 0 and info["dense"] and res is not None:
+              # what differs: groups only on one side, and groups whose exact columns differ
+              got_rows = H.engine_rows(res)
+              dim = [k for k in want[0] if isinstance(want[0][k], str)]
+              gk = {tuple(r[d] for d in dim): r for r in got_rows}
+              wk = {tuple(r[d] for d in dim): r for r in want}
+              only_g, only_w = sorted(set(gk) - set(wk))[:5], sorted(set(wk) - set(gk))[:5]
+              diff = [(k, gk[k], wk[k]) for k in sorted(set(gk) & set(wk)) if any(gk[k][c] != wk[k][c] for c in wk[k] if not isinstance(wk[k][c], float))][:5]
+              print(f"  rows got {len(got_rows)} want {len(want)}; only in result {only_g}; only in oracle {only_w}; exact-column mismatches {diff}", flush=True)
 flag = torch.tensor([0 if ok else 1], device="cuda")
 dist.all_reduce(flag)
 if rank == 0:
