@@ -429,7 +429,8 @@ void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   unsigned long long* src = nullptr;
   // upper bound on rows: table rows (dense) or capacity (hash); allocate exactly after a count
   // pass would cost another launch, so size by min(table rows, rows scanned)
-  uint64_t cap_rows = std::min<uint64_t>(st->table_rows, (uint64_t)std::max<int64_t>(plan.rows_scanned, 1));
+  // (a table merged with other ranks' partials can hold more groups than this rank scanned rows)
+  uint64_t cap_rows = st->merged ? st->table_rows : std::min<uint64_t>(st->table_rows, (uint64_t)std::max<int64_t>(plan.rows_scanned, 1));
   SDO_CUDA(cudaMallocAsync((void**)&st->rows_keys, std::max<uint64_t>(cap_rows, 1) * 8, s));
   SDO_CUDA(cudaMallocAsync((void**)&st->rows_slots, std::max<uint64_t>(cap_rows, 1) * ns * 8, s));
   if (plan.n_hll) SDO_CUDA(cudaMallocAsync((void**)&src, std::max<uint64_t>(cap_rows, 1) * 8, s));
@@ -1178,6 +1179,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root) {
   try {
     cudaStream_t s = ctx->stream;
     run_scan(ctx, *plan, &st);
+    st.merged = true;
     if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
     SDO_CUDA(cudaMallocAsync(&gathered, blob * comm_world_, s));
     {
@@ -1230,6 +1232,7 @@ Partial* Engine::partial(const char* json, size_t len) {
     }
     run_scan(p->ctx, p->plan, &p->st);
     if (p->st.strategy == STRAT_HASH) compact_rows(p->ctx, p->plan, &p->st);
+    p->st.merged = true;  // from here on the caller may fold other ranks' state into the table
     for (int i = 0; i < p->plan.n_slots; i++) p->slot_ops.push_back(p->plan.slot_op[i]);
   } catch (...) {
     if (p->ctx) {

@@ -93,6 +93,7 @@ struct ScanState {
   unsigned long long* rows_keys = nullptr;
   unsigned long long* rows_slots = nullptr;
   uint8_t* rows_hll = nullptr;
+  bool merged = false;            // the table may hold other ranks' groups too: local row counts no longer bound it
   double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
   bool rows_valid = false;

@@ -26,9 +26,22 @@ cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_disc
         "c_mktsegment", "s_region", "s_nation", "count"]
 eng = sdo.Engine(local)
 eng.create_datasource("tpch")
-mine = tpch.FlatTable(sf, cols, rank, world)
-eng.load("tpch", mine.engine_columns(), partition=rank)
-whole = H.oracle_table([tpch.FlatTable(sf, cols, r, world) for r in range(world)])
+if os.environ.get("CHECK_SKEW"):
+    # rank 0 holds 1/16 of the rows, the others share the rest: the merged table on rank 0 has far more groups than
+    # rank 0 scanned rows (what a root sees at 8+ ranks)
+    pieces = 16
+    owners = [0] + [1 + (i % max(world - 1, 1)) if world > 1 else 0 for i in range(pieces - 1)]
+    mine = None
+    for i in range(pieces):
+        if owners[i] == rank:
+            t = tpch.FlatTable(sf, cols, i, pieces)
+            eng.load("tpch", t.engine_columns(), partition=i)
+            mine = mine or t
+    whole = H.oracle_table([tpch.FlatTable(sf, cols, i, pieces) for i in range(pieces)])
+else:
+    mine = tpch.FlatTable(sf, cols, rank, world)
+    eng.load("tpch", mine.engine_columns(), partition=rank)
+    whole = H.oracle_table([tpch.FlatTable(sf, cols, r, world) for r in range(world)])
 ok = True
 # second pass: the same dense shapes with the merge inside the library (sdo_query_execute_sharded)
 passes = [("host-merge", False), ("native-merge", True)]
