@@ -524,10 +524,53 @@ def _having(h, row):
     return v > h["value"] if t == "greaterThan" else (v < h["value"] if t == "lessThan" else v == h["value"])
 
 
+def _search(tbl, q):
+    """SearchQuerySpec (DruidQuerySpec.scala:870-927): the values of the search dimensions that occur in the rows passing
+    interval and filter and match the search query, with their row counts; ordered by value then dimension; null value
+    not reported."""
+    mask = np.zeros(tbl.n, dtype=bool)
+    ivs = q.get("intervals")
+    if ivs is None:
+        mask[:] = True
+    else:
+        if isinstance(ivs, dict):
+            ivs = [s["itvl"] for s in ivs["segments"]] if ivs.get("type") == "segments" else ivs["intervals"]
+        for s in ivs:
+            a, b = parse_interval(s)
+            mask |= (tbl.time >= a) & (tbl.time < b)
+    if q.get("filter"):
+        mask &= filter_mask(tbl, q["filter"])
+    sq = q["query"]
+    if sq["type"] == "insensitive_contains":
+        terms, fold = [sq.get("value") or ""], True
+    elif sq["type"] == "contains":
+        terms, fold = [sq.get("value") or ""], not sq.get("caseSensitive", True)
+    elif sq["type"] == "fragment":
+        terms, fold = list(sq["values"]), not sq.get("caseSensitive", False)
+    else:
+        raise NotImplementedError(sq["type"])
+    low = lambda s: "".join(c.lower() if "A" <= c <= "Z" else c for c in s)  # noqa: E731  ASCII case folding
+    hits = []
+    dims = [d if isinstance(d, str) else d["dimension"] for d in (q.get("searchDimensions") or sorted(tbl.dims))]
+    for d in dims:
+        if d not in tbl.dims:
+            continue
+        vals, inv = tbl.dim_strings_of_unique(d)
+        counts = np.bincount(inv[mask], minlength=len(vals))
+        for v, c in zip(vals, counts.tolist()):
+            if c and v != "" and all((low(t) in low(v)) if fold else (t in v) for t in terms):
+                hits.append({"dimension": d, "value": v, "count": int(c)})
+    strlen = (q.get("sort") or {}).get("type") == "strlen" if isinstance(q.get("sort"), dict) else q.get("sort") == "strlen"
+    hits.sort(key=lambda h: ((len(h["value"].encode("utf-8")),) if strlen else ()) + (h["value"].encode("utf-8"), h["dimension"]))
+    return hits[:int(q.get("limit", 1000))]
+
+
 def execute(tbl, q, return_registers=False):
     """Run a groupBy / timeseries / topN query dict; returns a list of row dicts in result order.
     Dimension values are strings (integer dimensions as decimal strings); 'timestamp' holds the bucket start."""
     qt = q["queryType"]
+    if qt == "search":
+        return _search(tbl, q)
     mask = np.zeros(tbl.n, dtype=bool)
     ivs = q.get("intervals")
     if ivs is None:

@@ -1070,7 +1070,7 @@ Result* Engine::finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st
 // Plans are cached by the query's JSON text: dashboards repeat queries, and planning a day-granularity query
 // (thousands of spans, calendar maths, dictionary searches) can cost more than running it.  A cached plan is
 // reused only while the datasource object and its version are the ones it was made for.  Results are never cached.
-std::shared_ptr<const Plan> Engine::plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out) {
+std::shared_ptr<const Plan> Engine::plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out, QuerySpec* search_out) {
   std::string key(json, len);
   std::shared_ptr<const Plan> cached;
   {
@@ -1087,6 +1087,10 @@ std::shared_ptr<const Plan> Engine::plan_for(const char* json, size_t len, std::
     }
   }
   QuerySpec spec = parse_query_spec(json, len);
+  if (spec.type == QuerySpec::Search && search_out) {
+    *search_out = std::move(spec);
+    return nullptr;
+  }
   auto ds = store_.get(spec.data_source);
   std::shared_lock<std::shared_mutex> lk(ds->mu);
   auto plan = std::make_shared<Plan>(make_plan(spec, ds, opt_));
@@ -1100,10 +1104,142 @@ std::shared_ptr<const Plan> Engine::plan_for(const char* json, size_t len, std::
   return plan;
 }
 
+// Search (SearchQuerySpec, DruidQuerySpec.scala:870-927; emitted by the planner for a group-by on one dimension without
+// aggregations, QuerySpecTransforms.scala:224-278): per search dimension one group-by with a row count, the search terms
+// added to the filter as predicates on that dimension's dictionary.  Result columns as Druid's: dimension, value, count;
+// ordered by value (lexicographic or strlen) then dimension, cut at `limit`.
+Result* Engine::execute_search(const QuerySpec& spec, double t0) {
+  auto ds = store_.get(spec.data_source);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  check_cancel(spec.query_id);
+  std::vector<std::string> dims = spec.search_dimensions;
+  if (dims.empty())
+    for (auto& d : ds->dims) dims.push_back(d.name);
+  struct Hit { std::string dim, value; int64_t count; };
+  std::vector<Hit> hits;
+  double scan_ms = 0, dev_ms = 0;
+  int64_t rows_scanned = 0, launches = 0;
+  for (auto& dname : dims) {
+    if (ds->dim_index(dname) < 0) continue;  // Druid: an unknown dimension has no values to report
+    QuerySpec g;
+    g.type = QuerySpec::GroupBy;
+    g.data_source = spec.data_source;
+    DimensionSpec d;
+    d.dimension = d.output_name = dname;
+    g.dimensions.push_back(d);
+    AggregationSpec cnt;
+    cnt.kind = AggregationSpec::Count;
+    cnt.name = "count";
+    g.aggregations.push_back(cnt);
+    g.intervals = spec.intervals;
+    g.by_segments = spec.by_segments;
+    g.segments = spec.segments;
+    g.query_id = spec.query_id;
+    g.gpu_strategy = spec.gpu_strategy;
+    g.gpu_jit = spec.gpu_jit;
+    FilterNode all;
+    all.kind = FilterNode::And;
+    if (spec.has_filter) all.fields.push_back(spec.filter);
+    for (FilterNode t : spec.search_terms) {
+      t.dimension = dname;
+      all.fields.push_back(t);
+    }
+    if (!all.fields.empty()) { g.has_filter = true; g.filter = all; }
+    Plan plan = make_plan(g, ds, opt_);
+    std::unique_ptr<Result> r(execute_plan(plan, now_ms()));
+    const ResultColumn& vc = r->columns.at(0);
+    const ResultColumn& cc = r->columns.at(1);
+    for (int64_t i = 0; i < r->n_rows; i++) {
+      std::string v;
+      if (vc.type == SDO_RES_STRING) {
+        const uint32_t id = vc.raw ? ((const uint32_t*)vc.raw)[i] : vc.ids[i];
+        v = vc.dict->get(id);
+      } else {
+        v = std::to_string(vc.raw ? ((const int64_t*)vc.raw)[i] : vc.i64[i]);
+      }
+      if (v.empty()) continue;  // Druid's search does not report the null value
+      hits.push_back({dname, std::move(v), cc.raw ? ((const int64_t*)cc.raw)[i] : cc.i64[i]});
+    }
+    // carry the scan statistics of the sub-queries
+    const std::string& sj = r->stats;
+    auto num = [&](const char* key) {
+      size_t k = sj.find(std::string("\"") + key + "\":");
+      return k == std::string::npos ? 0.0 : atof(sj.c_str() + k + strlen(key) + 3);
+    };
+    scan_ms += num("scanKernelMs");
+    dev_ms += num("deviceMs");
+    rows_scanned += (int64_t)num("rowsScanned");
+    launches += (int64_t)num("launches");
+  }
+  const bool by_len = spec.search_sort_strlen;
+  std::sort(hits.begin(), hits.end(), [by_len](const Hit& a, const Hit& b) {
+    if (by_len && a.value.size() != b.value.size()) return a.value.size() < b.value.size();
+    int c = utf8_cmp(a.value.data(), a.value.size(), b.value.data(), b.value.size());
+    if (c) return c < 0;
+    return a.dim < b.dim;
+  });
+  if ((int64_t)hits.size() > spec.search_limit) hits.resize((size_t)spec.search_limit);
+  std::unique_ptr<Result> res(new Result());
+  res->n_rows = (int64_t)hits.size();
+  ResultColumn cd, cv, cn;
+  cd.name = "dimension";
+  cv.name = "value";
+  cn.name = "count";
+  cd.type = cv.type = SDO_RES_STRING;
+  cn.type = SDO_RES_INT64;
+  cd.dict = std::make_shared<Dictionary>();
+  cv.dict = std::make_shared<Dictionary>();
+  std::map<std::string, uint32_t> dim_ids;
+  for (auto& h : hits) {
+    auto it = dim_ids.find(h.dim);
+    if (it == dim_ids.end()) {
+      it = dim_ids.emplace(h.dim, (uint32_t)cd.dict->size()).first;
+      cd.dict->push(h.dim.data(), h.dim.size());
+    }
+    cd.ids.push_back(it->second);
+    cv.ids.push_back((uint32_t)cv.dict->size());
+    cv.dict->push(h.value.data(), h.value.size());
+    cn.i64.push_back(h.count);
+  }
+  res->columns.push_back(std::move(cd));
+  res->columns.push_back(std::move(cv));
+  res->columns.push_back(std::move(cn));
+  char buf[512];
+  snprintf(buf, sizeof buf,
+           "{\"queryType\":\"search\",\"strategy\":\"per-dimension group-by\",\"rowsScanned\":%lld,\"resultRows\":%lld,\"scanKernelMs\":%.6f,"
+           "\"deviceMs\":%.6f,\"totalMs\":%.6f,\"launches\":%lld,\"dimensions\":%d}",
+           (long long)rows_scanned, (long long)res->n_rows, scan_ms, dev_ms, now_ms() - t0, (long long)launches, (int)dims.size());
+  res->stats = buf;
+  return res.release();
+}
+
+Result* Engine::execute_plan(const Plan& plan, double t0) {
+  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+  QueryCtx* ctx = acquire_ctx();
+  ScanState st;
+  st.plan_ms = now_ms() - t0;
+  Result* r = nullptr;
+  try {
+    if (!plan.always_false) run_scan(ctx, plan, &st);
+    check_cancel(plan.spec.query_id);
+    r = finalize(ctx, plan, &st, t0);
+  } catch (...) {
+    cudaStreamSynchronize(ctx->stream);
+    free_state(ctx, &st);
+    release_ctx(ctx);
+    throw;
+  }
+  free_state(ctx, &st);
+  release_ctx(ctx);
+  return r;
+}
+
 Result* Engine::execute(const char* json, size_t len) {
   const double t0 = now_ms();
   std::shared_lock<std::shared_mutex> lk;
-  std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk);
+  QuerySpec search;
+  std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk, &search);
+  if (!plan_ptr) return execute_search(search, t0);
   const Plan& plan = *plan_ptr;
   check_cancel(plan.spec.query_id);
   if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");

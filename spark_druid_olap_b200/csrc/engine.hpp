@@ -152,7 +152,10 @@ class Engine {
   void ensure_pinned(void** p, size_t* cur, size_t need);
   void check_cancel(const std::string& qid);
   void run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st);
-  std::shared_ptr<const Plan> plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out);
+  // search_out (optional): a search query has no plan of its own -- its spec is handed back and nullptr returned
+  std::shared_ptr<const Plan> plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out, QuerySpec* search_out = nullptr);
+  Result* execute_search(const QuerySpec& spec, double t_start_ms);
+  Result* execute_plan(const Plan& plan, double t_start_ms);
   std::mutex plan_mu_;
   std::map<std::string, std::shared_ptr<const Plan>> plan_cache_;
   void compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st);

@@ -275,6 +275,14 @@ struct Compiler {
       }
       case FilterNode::Contains: {
         const std::string& needle = f.value;
+        if (f.ignore_case) {
+          // search "insensitive_contains": ASCII letters compare without case
+          auto lower = [](char c) { return (char)(c >= 'A' && c <= 'Z' ? c + 32 : c); };
+          return predicate_node(di, [&needle, lower](const char* p, size_t n) {
+            if (needle.empty()) return true;
+            return std::search(p, p + n, needle.begin(), needle.end(), [lower](char a, char b) { return lower(a) == lower(b); }) != p + n;
+          });
+        }
         return predicate_node(di, [&needle](const char* p, size_t n) {
           if (needle.empty()) return true;
           return std::search(p, p + n, needle.begin(), needle.end()) != p + n;
@@ -475,6 +483,8 @@ void build_extraction(const DimMeta& dm, const ExtractionFn& fn, PlanDim* pd) {
 }  // namespace
 
 Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const PlanOptions& opt) {
+  if (spec.type == QuerySpec::Search)
+    throw Unsupported("a search query has no single plan: sdo_query_execute runs it as one group-by per search dimension");
   Plan plan;
   plan.spec = spec;
   plan.ds = ds_ptr;

@@ -58,7 +58,7 @@ FilterNode parse_filter(const Json& j) {
     if (t == "search") {
       const Json* q = j.find("query");
       if (!q || (q->get_str("type") != "contains" && q->get_str("type") != "insensitive_contains")) throw Unsupported("search filter query type");
-      if (q->get_str("type") == "insensitive_contains" || !q->get_bool("caseSensitive", true)) throw Unsupported("case-insensitive search filter");
+      f.ignore_case = q->get_str("type") == "insensitive_contains" || !q->get_bool("caseSensitive", true);
       f.value = q->get_str("value");
     } else {
       f.value = req_str(j, "value", "contains filter");  // StringContainsSpec, DruidQuerySpec.scala:178-183
@@ -397,6 +397,7 @@ QuerySpec parse_query_spec(const Json& j) {
   if (qt == "groupBy") q.type = QuerySpec::GroupBy;
   else if (qt == "timeseries") q.type = QuerySpec::Timeseries;
   else if (qt == "topN") q.type = QuerySpec::TopN;
+  else if (qt == "search") q.type = QuerySpec::Search;
   else throw Unsupported("queryType '" + qt + "' is not supported by the GPU engine (groupBy, timeseries, topN only)");
   const Json* ds = j.find("dataSource");
   if (!ds) throw Invalid("query: missing 'dataSource'");
@@ -458,6 +459,37 @@ QuerySpec parse_query_spec(const Json& j) {
       }
     }
     if (const Json* h = j.find("having")) { q.has_having = true; q.having = parse_having(*h); }
+  } else if (q.type == QuerySpec::Search) {
+    if (q.granularity.kind != Granularity::All) throw Unsupported("search query with a granularity other than 'all'");
+    if (const Json* d = j.find("searchDimensions")) {
+      if (!d->is_arr()) throw Invalid("'searchDimensions' must be an array");
+      for (auto& x : d->arr) q.search_dimensions.push_back(x.is_obj() ? x.get_str("dimension") : x.str);
+    }
+    const Json* sq = j.find("query");
+    if (!sq || !sq->is_obj()) throw Invalid("search: missing 'query'");
+    // SearchQueryQuerySpec (:543-552): insensitive_contains (what the planner emits, with value ""), contains, fragment
+    const std::string st = sq->get_str("type");
+    auto term = [&](const std::string& v, bool ignore_case) {
+      FilterNode f;
+      f.kind = FilterNode::Contains;
+      f.value = v;
+      f.ignore_case = ignore_case;
+      q.search_terms.push_back(f);
+    };
+    if (st == "insensitive_contains") term(sq->get_str("value", ""), true);
+    else if (st == "contains") term(sq->get_str("value", ""), !sq->get_bool("caseSensitive", true));
+    else if (st == "fragment") {
+      const Json* vs = sq->find("values");
+      if (!vs || !vs->is_arr()) throw Invalid("search fragment query: 'values' missing");
+      for (auto& v : vs->arr) term(v.str, !sq->get_bool("caseSensitive", false));
+    } else throw Unsupported("search query type '" + st + "'");
+    q.search_limit = j.get_int("limit", 1000);
+    if (q.search_limit < 0) throw Invalid("search: negative 'limit'");
+    if (const Json* so = j.find("sort")) {
+      const std::string t = so->is_obj() ? so->get_str("type", "lexicographic") : so->str;
+      if (t == "strlen") q.search_sort_strlen = true;
+      else if (t != "lexicographic") throw Unsupported("search sort '" + t + "'");
+    }
   } else if (q.type == QuerySpec::TopN) {
     const Json* d = j.find("dimension");
     if (!d) throw Invalid("topN: missing 'dimension'");

@@ -22,6 +22,7 @@ struct FilterNode {
   bool has_lower = false, has_upper = false, lower_strict = false, upper_strict = false, alpha_numeric = false;
   std::string lower, upper;       // Bound
   std::vector<FilterNode> fields; // And / Or / Not(1)
+  bool ignore_case = false;       // Contains: ASCII case-insensitive (search query "insensitive_contains")
   std::shared_ptr<const minijs::Function> js;  // Javascript: function(value) -> truthy keeps the row
 };
 
@@ -89,7 +90,13 @@ struct TopNMetric {
 struct SegmentIntervalRef { Interval itvl; std::string version; int part = -1; };
 
 struct QuerySpec {
-  enum Type { GroupBy, Timeseries, TopN } type = GroupBy;
+  enum Type { GroupBy, Timeseries, TopN, Search } type = GroupBy;
+  // Search (SearchQuerySpec, DruidQuerySpec.scala:870-927): which values of `search_dimensions` occur, with row counts.
+  // The planner turns a group-by on one dimension without aggregations into this (QuerySpecTransforms.scala:224-278).
+  std::vector<std::string> search_dimensions;       // empty = every dimension
+  std::vector<FilterNode> search_terms;             // per term a Contains on a placeholder dimension; all must match
+  bool search_sort_strlen = false;                  // sort: lexicographic (default) or strlen
+  int64_t search_limit = 1000;
   std::string data_source;
   std::vector<DimensionSpec> dimensions;  // TopN: exactly one
   Granularity granularity;

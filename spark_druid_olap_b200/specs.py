@@ -335,6 +335,26 @@ class TimeSeriesQuerySpec(_Spec):
                          context)
 
 
+class InsensitiveContainsSearchQuerySpec(_Spec):
+    """DruidQuerySpec.scala:547-552"""
+    _fields = ("type", "value")
+
+    def __init__(self, value=""):
+        super().__init__("insensitive_contains", value)
+
+
+class SortSearchQuerySpec(_Spec):
+    _fields = ("type",)
+
+
+class SearchQuerySpec(_Spec):
+    """DruidQuerySpec.scala:870-927"""
+    _fields = ("queryType", "dataSource", "intervals", "granularity", "filter", "searchDimensions", "query", "limit", "sort", "context")
+
+    def __init__(self, dataSource, intervals, granularity, filter, searchDimensions, query, limit, sort=None, context=None):
+        super().__init__("search", dataSource, list(intervals), _gran(granularity), filter, list(searchDimensions), query, limit, sort, context)
+
+
 class TopNQuerySpec(_Spec):
     _fields = ("queryType", "dataSource", "intervals", "granularity", "filter", "aggregations", "postAggregations", "dimension",
                "threshold", "metric", "context")

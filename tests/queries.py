@@ -157,6 +157,24 @@ def filter_cases():
     ] + js_filter_cases()
 
 
+def search_cases():
+    """SearchQuerySpec shapes: what SearchQuerySpecTransform emits for `select distinct dim` / `group by dim order by dim
+    limit n` (QuerySpecTransforms.scala:224-278) plus Druid's other search query types."""
+    return [
+        ("distinct_nation", SearchQuerySpec(DS, ALL_TIME, "all", None, ["s_nation"], InsensitiveContainsSearchQuerySpec(), 2147483647)),
+        ("distinct_limit_sorted", SearchQuerySpec(DS, ALL_TIME, "all", SelectorFilterSpec("c_mktsegment", "BUILDING"), ["p_brand"],
+                                                  InsensitiveContainsSearchQuerySpec(), 7, SortSearchQuerySpec("lexicographic"))),
+        ("insensitive_two_dims", SearchQuerySpec(DS, ["1994-01-01T00:00:00.000Z/1995-01-01T00:00:00.000Z"], "all", None, ["s_nation", "c_nation", "l_shipmode"],
+                                                 InsensitiveContainsSearchQuerySpec("ai"), 1000)),
+        ("contains_case", SearchQuerySpec(DS, ALL_TIME, "all", None, ["p_type"], {"type": "contains", "value": "BRUSHED", "caseSensitive": True}, 1000,
+                                          SortSearchQuerySpec("strlen"))),
+        ("fragment", SearchQuerySpec(DS, ALL_TIME, "all", None, ["p_type"], {"type": "fragment", "values": ["promo", "TIN"]}, 1000)),
+        ("integer_dim", SearchQuerySpec(DS, ALL_TIME, "all", None, ["p_size"], InsensitiveContainsSearchQuerySpec("4"), 1000)),
+        ("no_match", SearchQuerySpec(DS, ALL_TIME, "all", None, ["s_nation"], InsensitiveContainsSearchQuerySpec("zzz"), 1000)),
+        ("unknown_dim", SearchQuerySpec(DS, ALL_TIME, "all", None, ["no_such_dim", "l_returnflag"], InsensitiveContainsSearchQuerySpec(), 1000)),
+    ]
+
+
 def js_filter_cases():
     """JavascriptFilterSpec functions in the expression subset the engine evaluates per dictionary entry."""
     return [

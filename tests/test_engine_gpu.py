@@ -228,6 +228,25 @@ def test_reference_benchmark_specs_run_verbatim(loaded):
     assert ran >= 6
 
 
+@pytest.mark.parametrize("name,spec", Q.search_cases(), ids=[n for n, _ in Q.search_cases()])
+def test_search_queries(loaded, name, spec):
+    """Search queries (the planner's form of `select distinct dim`): dimension, value, row count, ordered as Druid orders."""
+    res, want = run_both(loaded, spec, ordered=True, what=name)
+    assert res.names == ["dimension", "value", "count"]
+    if name == "distinct_nation":
+        assert res.n_rows == 25 and sum(r["count"] for r in want) == loaded[1].n
+
+
+def test_search_filter_case_insensitive(loaded):
+    # the `search` filter type with an insensitive_contains query
+    f = {"type": "search", "dimension": "p_type", "query": {"type": "insensitive_contains", "value": "brushed"}}
+    q = json.loads(Q.with_filter(None).to_json())
+    q["filter"] = f
+    eng, tbl = loaded
+    want = orc.execute(tbl, dict(q, filter={"type": "regex", "dimension": "p_type", "pattern": "BRUSHED"}))
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), want)
+
+
 def test_having_and_limit_order(loaded):
     run_both(loaded, Q.having_query(), ordered=True)
 

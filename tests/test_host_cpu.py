@@ -202,7 +202,13 @@ def test_error_statuses(planning):
     with pytest.raises(sdo.InvalidQuery):
         eng.explain({"queryType": "groupBy", "dataSource": "tpch", "granularity": "fortnight", "aggregations": []})
     with pytest.raises(sdo.UnsupportedQuery):
-        eng.explain({"queryType": "search", "dataSource": "tpch"})
+        eng.explain({"queryType": "select", "dataSource": "tpch"})
+    with pytest.raises(sdo.InvalidQuery):
+        eng.explain({"queryType": "search", "dataSource": "tpch"})  # no 'query'
+    with pytest.raises(sdo.UnsupportedQuery):  # a search runs as one group-by per dimension: there is no single plan to explain
+        eng.explain(Q.search_cases()[0][1])
+    with pytest.raises(sdo.UnsupportedQuery):
+        eng.explain(json.loads(Q.search_cases()[0][1].to_json()) | {"granularity": "day"})
     with pytest.raises(sdo.UnsupportedQuery):
         # what JSCodeGenerator emits for date arithmetic (FilterPlanningTest.scala:85-104): statements and Java interop
         eng.explain(Q.with_filter(Q.JavascriptFilterSpec("o_orderdate", "function (o_orderdate) {\n var v1 = new org.joda.time.DateTimeZone.forID(\"UTC\");"

@@ -213,3 +213,18 @@ def test_extraction_function_known_answers():
     assert ex({"type": "regex", "expr": "^(\\d+)", "replaceMissingValue": True, "replaceMissingValueWith": "n/a"}, "x") == "n/a"
     assert ex({"type": "substring", "index": 2, "length": 3}, "abcdef") == "cde" and ex({"type": "substring", "index": 4}, "abcdef") == "ef"
     assert ex({"type": "substring", "index": 9}, "abc") == "" and ex({"type": "upper"}, "aBc") == "ABC" and ex({"type": "strlen"}, "abcd") == "4"
+
+
+def test_hand_computed_search():
+    t = _tiny()  # color: red x3, blue x3, "" x1, Zebra x1; k: 10 x3, 11 x2, 12, 9, 100
+    base = {"queryType": "search", "dataSource": "t", "granularity": "all", "searchDimensions": ["color", "k"], "limit": 100}
+    rows = orc.execute(t, dict(base, query={"type": "insensitive_contains", "value": ""}))
+    assert rows == [{"dimension": "k", "value": "10", "count": 3}, {"dimension": "k", "value": "100", "count": 1}, {"dimension": "k", "value": "11", "count": 2},
+                    {"dimension": "k", "value": "12", "count": 1}, {"dimension": "k", "value": "9", "count": 1}, {"dimension": "color", "value": "Zebra", "count": 1},
+                    {"dimension": "color", "value": "blue", "count": 3}, {"dimension": "color", "value": "red", "count": 3}]  # the null value is not reported
+    rows = orc.execute(t, dict(base, query={"type": "insensitive_contains", "value": "E"}))
+    assert [(r["value"], r["count"]) for r in rows] == [("Zebra", 1), ("blue", 3), ("red", 3)]
+    rows = orc.execute(t, dict(base, query={"type": "contains", "value": "e", "caseSensitive": True}, sort={"type": "strlen"}, limit=2))
+    assert [(r["value"], r["count"]) for r in rows] == [("red", 3), ("blue", 3)]
+    rows = orc.execute(t, dict(base, query={"type": "fragment", "values": ["z", "RA"]}, filter={"type": "selector", "dimension": "k", "value": "100"}))
+    assert rows == [{"dimension": "color", "value": "Zebra", "count": 1}]
