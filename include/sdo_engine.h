@@ -208,6 +208,14 @@ void* sdo_partial_stream(sdo_partial* p);
 int sdo_partial_finish(sdo_partial* p, sdo_result** out);
 void sdo_partial_free(sdo_partial* p);
 
+/* ---- persistence ------------------------------------------------------------------------------------
+ * Write a datasource as it sits in HBM -- dictionaries, encoded id / metric columns, time run index -- to one file, and
+ * bring it back under `name` (which must not exist) without dictionary encoding or time sort.  Stands in for the index
+ * the reference's Druid keeps on deep storage between restarts (written once by the indexing service,
+ * SLD/client/DruidOverlordClient.scala:51-129).  The file is private to this library version (magic "SDOSEG01"). */
+int sdo_datasource_save(sdo_engine* e, const char* name, const char* path);
+int sdo_datasource_restore(sdo_engine* e, const char* name, const char* path);
+
 /* ---- sharded execution with the merge inside the library ---------------------------------------
  * One engine per GPU, one process per engine.  Replaces the Spark-side re-aggregation of the per-historical partial
  * results (SQD/DruidStrategy.scala:353-359, SQD/PostAggregate.scala:39-103) for dense key spaces whose table (and HLL

@@ -105,6 +105,8 @@ def lib():
         "sdo_groupby_sum_noalloc": (C.c_int, [C.c_int, vp, vp, i64, C.c_int, vp, vp, vp]),
         "sdo_dimension_dictionary": (C.c_int, [vp, cp, cp, C.POINTER(i64), C.POINTER(vp), C.POINTER(vp), C.POINTER(i64)]),
         "sdo_dimension_extend": (C.c_int, [vp, cp, cp, i64, vp, vp, i64]),
+        "sdo_datasource_save": (C.c_int, [vp, cp, cp]),
+        "sdo_datasource_restore": (C.c_int, [vp, cp, cp]),
         "sdo_comm_unique_id": (C.c_int, [vp, cp]),
         "sdo_engine_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int, cp]),
         "sdo_query_execute_sharded": (C.c_int, [vp, cp, sz, C.c_int, C.POINTER(vp)]),
@@ -124,7 +126,7 @@ EXPORTED_SYMBOLS = [
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
     "sdo_dimension_dictionary", "sdo_dimension_extend", "sdo_partial_export", "sdo_partial_merge_gathered",
-    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded",
+    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded", "sdo_datasource_save", "sdo_datasource_restore",
 ]
 
 NOALLOC_MAX_KEYS = 24
@@ -324,6 +326,14 @@ class Engine:
 
     def drop_datasource(self, name):
         _check(lib().sdo_datasource_drop(self._h, name.encode()))
+
+    def save_datasource(self, name, path):
+        """Encoded segments, dictionaries and time index of `name` into one file."""
+        _check(lib().sdo_datasource_save(self._h, name.encode(), os.fsencode(path)))
+
+    def restore_datasource(self, name, path):
+        """A file written by save_datasource back into HBM under `name` (no re-encoding, no time sort)."""
+        _check(lib().sdo_datasource_restore(self._h, name.encode(), os.fsencode(path)))
 
     def load(self, datasource, columns, partition=0):
         n_rows = None

@@ -236,6 +236,15 @@ void sdo_partial_free(sdo_partial* p) {
   delete p;
 }
 
+int sdo_datasource_save(sdo_engine* e, const char* name, const char* path) {
+  if (!e || !name || !path) return bad("sdo_datasource_save: NULL argument");
+  return guard([&] { e->e->store().save(name, path); });
+}
+int sdo_datasource_restore(sdo_engine* e, const char* name, const char* path) {
+  if (!e || !name || !path) return bad("sdo_datasource_restore: NULL argument");
+  return guard([&] { e->e->store().restore(name, path); });
+}
+
 int sdo_comm_unique_id(void* id_out, const char* nccl_library) {
   if (!id_out) return bad("sdo_comm_unique_id: NULL argument");
   return guard([&] {

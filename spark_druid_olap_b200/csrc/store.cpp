@@ -1,7 +1,10 @@
 #include "store.hpp"
 
 #include <algorithm>
+#include <cerrno>
+#include <cstdio>
 #include <cstring>
+#include <memory>
 #include <numeric>
 #include <unordered_map>
 
@@ -580,6 +583,204 @@ std::string Store::segments_json(const std::string& name) const {
   }
   o += "]";
   return o;
+}
+
+}  // namespace sdo
+
+// ---- persistence: encoded segments on disk --------------------------------------------------------------------------------
+// The reference re-reads its OLAP index from Druid's deep storage after a restart (the indexing service wrote it once,
+// SLD/client/DruidOverlordClient.scala:51-129); here the already encoded, time-sorted segments are written as they sit in
+// HBM and read back without going through dictionary encoding or the time sort again.
+namespace sdo {
+namespace {
+
+constexpr char SAVE_MAGIC[8] = {'S', 'D', 'O', 'S', 'E', 'G', '0', '1'};
+
+struct Writer {
+  FILE* f;
+  const std::string& path;
+  void raw(const void* p, size_t n) {
+    if (n && fwrite(p, 1, n, f) != n) throw std::runtime_error("write to '" + path + "' failed: " + strerror(errno));
+  }
+  template <class T> void pod(T v) { raw(&v, sizeof v); }
+  void str(const std::string& s) { pod<uint64_t>(s.size()); raw(s.data(), s.size()); }
+  template <class T> void vec(const std::vector<T>& v) { pod<uint64_t>(v.size()); raw(v.data(), v.size() * sizeof(T)); }
+};
+struct Reader {
+  FILE* f;
+  const std::string& path;
+  void raw(void* p, size_t n) {
+    if (n && fread(p, 1, n, f) != n) throw Invalid("'" + path + "' is truncated or not a saved datasource");
+  }
+  template <class T> T pod() { T v; raw(&v, sizeof v); return v; }
+  std::string str() {
+    uint64_t n = pod<uint64_t>();
+    if (n > (1ull << 32)) throw Invalid("'" + path + "' is corrupt (string length)");
+    std::string s(n, '\0');
+    raw(&s[0], n);
+    return s;
+  }
+  template <class T> std::vector<T> vec() {
+    uint64_t n = pod<uint64_t>();
+    if (n > (1ull << 36) / sizeof(T)) throw Invalid("'" + path + "' is corrupt (array length)");
+    std::vector<T> v(n);
+    raw(v.data(), n * sizeof(T));
+    return v;
+  }
+};
+struct FileCloser { void operator()(FILE* f) const { if (f) fclose(f); } };
+
+}  // namespace
+
+void Store::save(const std::string& name, const std::string& path) const {
+  auto ds = get(name);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  std::unique_ptr<FILE, FileCloser> fp(fopen(path.c_str(), "wb"));
+  if (!fp) throw Invalid("cannot open '" + path + "' for writing: " + strerror(errno));
+  Writer w{fp.get(), path};
+  w.raw(SAVE_MAGIC, 8);
+  w.str(ds->segment_granularity);
+  w.str(ds->query_granularity);
+  w.pod<uint64_t>(ds->dims.size());
+  for (auto& d : ds->dims) {
+    w.str(d.name);
+    w.pod<int32_t>(d.enc == DimEncoding::Dict ? 0 : 1);
+    w.pod<int32_t>(d.src_type);
+    w.pod<int32_t>(d.width);
+    w.pod<int64_t>(d.cardinality);
+    w.vec(d.dict->offsets);
+    w.str(d.dict->bytes);
+  }
+  w.pod<uint64_t>(ds->metrics.size());
+  for (auto& m : ds->metrics) {
+    w.str(m.name);
+    w.pod<int32_t>((m.is_float ? 1 : 0) | (m.constant ? 2 : 0) | (m.seen ? 4 : 0));
+    w.pod<int64_t>(m.const_value);
+  }
+  w.pod<uint64_t>(ds->segments.size());
+  if (device_ >= 0) SDO_CUDA(cudaSetDevice(device_));
+  std::vector<char> host;
+  auto column = [&](const void* dev, size_t bytes) {
+    w.pod<uint64_t>(dev ? bytes : 0);
+    if (!dev || !bytes) return;
+    host.resize(bytes);
+    SDO_CUDA(cudaMemcpy(host.data(), dev, bytes, cudaMemcpyDeviceToHost));
+    w.raw(host.data(), bytes);
+  };
+  for (auto& sp : ds->segments) {
+    const Segment& s = *sp;
+    w.pod<int64_t>(s.start_ms);
+    w.pod<int64_t>(s.end_ms);
+    w.pod<int32_t>(s.partition);
+    w.pod<int64_t>(s.n_rows);
+    w.vec(s.time_vals);
+    w.vec(s.time_rows);
+    for (size_t d = 0; d < ds->dims.size(); d++) {
+      w.pod<int32_t>(d < s.dim_width.size() ? s.dim_width[d] : 0);
+      column(d < s.dim_data.size() ? s.dim_data[d] : nullptr, (size_t)s.n_rows * (d < s.dim_width.size() ? s.dim_width[d] : 0));
+    }
+    for (size_t m = 0; m < ds->metrics.size(); m++) column(m < s.metric_data.size() ? s.metric_data[m] : nullptr, (size_t)s.n_rows * 8);
+  }
+  if (fflush(fp.get()) != 0) throw std::runtime_error("write to '" + path + "' failed: " + strerror(errno));
+}
+
+void Store::restore(const std::string& name, const std::string& path) {
+  if (device_ < 0) throw NoDevice("restoring a datasource needs a CUDA device: segments live in HBM");
+  std::unique_ptr<FILE, FileCloser> fp(fopen(path.c_str(), "rb"));
+  if (!fp) throw NotFound("cannot open '" + path + "': " + strerror(errno));
+  Reader r{fp.get(), path};
+  char magic[8];
+  r.raw(magic, 8);
+  if (memcmp(magic, SAVE_MAGIC, 8) != 0) throw Invalid("'" + path + "' is not a saved datasource (bad magic)");
+  auto ds = std::make_shared<DataSource>();
+  ds->name = name;
+  ds->segment_granularity = r.str();
+  ds->query_granularity = r.str();
+  const uint64_t n_dims = r.pod<uint64_t>();
+  if (n_dims > 4096) throw Invalid("'" + path + "' is corrupt (dimension count)");
+  for (uint64_t i = 0; i < n_dims; i++) {
+    DimMeta d;
+    d.name = r.str();
+    d.enc = r.pod<int32_t>() == 0 ? DimEncoding::Dict : DimEncoding::Direct;
+    d.src_type = r.pod<int32_t>();
+    d.width = r.pod<int32_t>();
+    d.cardinality = r.pod<int64_t>();
+    auto dict = std::make_shared<Dictionary>();
+    dict->offsets = r.vec<int64_t>();
+    dict->bytes = r.str();
+    if (dict->offsets.empty() || dict->offsets.front() != 0 || (uint64_t)dict->offsets.back() != dict->bytes.size() ||
+        (d.width != 1 && d.width != 2 && d.width != 4))
+      throw Invalid("'" + path + "' is corrupt (dictionary of '" + d.name + "')");
+    d.dict = dict;
+    ds->dims.push_back(std::move(d));
+  }
+  const uint64_t n_metrics = r.pod<uint64_t>();
+  if (n_metrics > 4096) throw Invalid("'" + path + "' is corrupt (metric count)");
+  for (uint64_t i = 0; i < n_metrics; i++) {
+    MetricMeta m;
+    m.name = r.str();
+    const int32_t flags = r.pod<int32_t>();
+    m.is_float = flags & 1;
+    m.constant = flags & 2;
+    m.seen = flags & 4;
+    m.const_value = r.pod<int64_t>();
+    ds->metrics.push_back(std::move(m));
+  }
+  const uint64_t n_segs = r.pod<uint64_t>();
+  if (n_segs > (1u << 24)) throw Invalid("'" + path + "' is corrupt (segment count)");
+  SDO_CUDA(cudaSetDevice(device_));
+  std::vector<char> host;
+  try {
+    for (uint64_t si = 0; si < n_segs; si++) {
+      std::unique_ptr<Segment> s(new Segment());
+      s->start_ms = r.pod<int64_t>();
+      s->end_ms = r.pod<int64_t>();
+      s->partition = r.pod<int32_t>();
+      s->n_rows = r.pod<int64_t>();
+      if (s->n_rows < 0 || s->n_rows > 0x7fffffffll) throw Invalid("'" + path + "' is corrupt (segment rows)");
+      s->time_vals = r.vec<int64_t>();
+      s->time_rows = r.vec<int64_t>();
+      if (s->time_rows.size() != s->time_vals.size() + 1 || (!s->time_rows.empty() && s->time_rows.back() != s->n_rows))
+        throw Invalid("'" + path + "' is corrupt (time index)");
+      s->dim_data.assign(n_dims, nullptr);
+      s->dim_hll.assign(n_dims, nullptr);
+      s->dim_width.assign(n_dims, 0);
+      s->metric_data.assign(n_metrics, nullptr);
+      ds->segments.push_back(std::move(s));
+      Segment& sg = *ds->segments.back();
+      auto column = [&](size_t expect) -> void* {
+        const uint64_t bytes = r.pod<uint64_t>();
+        if (!bytes) return nullptr;
+        if (bytes != expect) throw Invalid("'" + path + "' is corrupt (column size)");
+        host.resize(bytes);
+        r.raw(host.data(), bytes);
+        // same slack as a loaded column: vector loads may run past the last row
+        const size_t padded = round_up((size_t)bytes + 64, 256);
+        void* dev = nullptr;
+        SDO_CUDA(cudaMalloc(&dev, padded));
+        SDO_CUDA(cudaMemset((char*)dev + bytes, 0, padded - bytes));
+        SDO_CUDA(cudaMemcpy(dev, host.data(), bytes, cudaMemcpyHostToDevice));
+        sg.device_bytes += padded;
+        return dev;
+      };
+      for (uint64_t d = 0; d < n_dims; d++) {
+        sg.dim_width[d] = r.pod<int32_t>();
+        sg.dim_data[d] = column((size_t)sg.n_rows * sg.dim_width[d]);
+      }
+      for (uint64_t m = 0; m < n_metrics; m++) sg.metric_data[m] = column((size_t)sg.n_rows * 8);
+      ds->n_rows += sg.n_rows;
+    }
+  } catch (...) {
+    for (auto& sp : ds->segments) free_segment(*sp);
+    throw;
+  }
+  ds->version = 1;
+  std::lock_guard<std::mutex> lk(mu_);
+  if (sources_.count(name)) {
+    for (auto& sp : ds->segments) free_segment(*sp);
+    throw Invalid("datasource '" + name + "' already exists");
+  }
+  sources_[name] = ds;
 }
 
 }  // namespace sdo

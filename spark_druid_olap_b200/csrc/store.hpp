@@ -115,6 +115,9 @@ class Store {
   std::string segments_json(const std::string& name) const;
   void extend_dimension(const std::string& name, const std::string& dim, const Dictionary* values, int64_t min_cardinality);
   std::shared_ptr<Dictionary> dictionary(const std::string& name, const std::string& dim) const;
+  // encoded segments + dictionaries + time index to / from one file (restart without re-encoding)
+  void save(const std::string& name, const std::string& path) const;
+  void restore(const std::string& name, const std::string& path);
   int device() const { return device_; }
 
  private:

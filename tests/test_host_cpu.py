@@ -257,3 +257,14 @@ def test_loader_rejects_bad_input(native_libs):
     with pytest.raises(sdo.InvalidQuery):
         eng.load("d", [sdo.time_column("__time", t), sdo.metric("a", np.array([1.0, 2.0, 3.0]))])  # 'a' is a dimension
     eng.close()
+
+
+def test_persistence_error_paths(planning, tmp_path):
+    import spark_druid_olap_b200 as sdo
+    eng, _, _ = planning
+    with pytest.raises(sdo.DruidDataSourceException) as ei:
+        eng.save_datasource("missing", tmp_path / "x.sdoseg")
+    assert ei.value.status == sdo.SDO_NOT_FOUND
+    (tmp_path / "junk").write_bytes(b"SDOSEG01")
+    with pytest.raises(sdo.NoDevice):
+        eng.restore_datasource("r", tmp_path / "junk")  # segments live in HBM: no device, no restore
