@@ -524,6 +524,37 @@ def _having(h, row):
     return v > h["value"] if t == "greaterThan" else (v < h["value"] if t == "lessThan" else v == h["value"])
 
 
+def _select(tbl, q):
+    """SelectSpec (DruidQuerySpec.scala:980-1098) without the paging: every row that passes interval and filter, as
+    {timestamp, dimension values (strings), metric values}; order unspecified (the engine pages through them in segment
+    order, which this table does not know)."""
+    mask = np.zeros(tbl.n, dtype=bool)
+    ivs = q.get("intervals")
+    if ivs is None:
+        mask[:] = True
+    else:
+        if isinstance(ivs, dict):
+            ivs = [s["itvl"] for s in ivs["segments"]] if ivs.get("type") == "segments" else ivs["intervals"]
+        for s in ivs:
+            a, b = parse_interval(s)
+            mask |= (tbl.time >= a) & (tbl.time < b)
+    if q.get("filter"):
+        mask &= filter_mask(tbl, q["filter"])
+    rows = np.nonzero(mask)[0]
+    dims, mets = list(q.get("dimensions") or []), list(q.get("metrics") or [])
+    if not dims and not mets:
+        dims, mets = sorted(tbl.dims), sorted(tbl.metrics)
+    cols = {"timestamp": tbl.time[rows].tolist()}
+    for d in dims:
+        vals, inv = tbl.dim_strings_of_unique(d)
+        cols[d] = [vals[i] for i in inv[rows].tolist()]
+    for m in mets:
+        v = np.asarray(tbl.metrics[m])[rows]
+        cols[m] = v.tolist()
+    names = list(cols)
+    return [dict(zip(names, vals)) for vals in zip(*(cols[n] for n in names))]
+
+
 def _search(tbl, q):
     """SearchQuerySpec (DruidQuerySpec.scala:870-927): the values of the search dimensions that occur in the rows passing
     interval and filter and match the search query, with their row counts; ordered by value then dimension; null value
@@ -571,6 +602,8 @@ def execute(tbl, q, return_registers=False):
     qt = q["queryType"]
     if qt == "search":
         return _search(tbl, q)
+    if qt == "select":
+        return _select(tbl, q)
     mask = np.zeros(tbl.n, dtype=bool)
     ivs = q.get("intervals")
     if ivs is None:

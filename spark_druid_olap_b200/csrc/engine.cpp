@@ -185,7 +185,9 @@ static uint64_t pow2_ceil(uint64_t v) {
   return p;
 }
 
-void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
+// Upload the per-query blob (spans, coarse index, segment pointer table, bitsets, id remaps) and fill the parts of
+// ScanParams every kernel over the plan's rows needs: spans, columns, compiled filter, dimensions, aggregators.
+void Engine::prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
   SDO_CUDA(cudaSetDevice(device_));
   cudaStream_t s = ctx->stream;
@@ -281,8 +283,13 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   for (int i = 0; i < plan.n_slots; i++) { p.slot_op[i] = plan.slot_op[i]; p.slot_init[i] = plan.slot_init[i]; }
   p.counters = ctx->counters;
   SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
-
   if (plan.rows_scanned >= (1ll << 32)) throw Unsupported("a single launch scans at most 2^32 rows per GPU");
+}
+
+void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
+  prepare_params(ctx, plan, st);
+  cudaStream_t s = ctx->stream;
+  ScanParams& p = st->params;
   int strat = plan.strategy;
   st->strategy = strat;
   const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;
@@ -1087,7 +1094,7 @@ std::shared_ptr<const Plan> Engine::plan_for(const char* json, size_t len, std::
     }
   }
   QuerySpec spec = parse_query_spec(json, len);
-  if (spec.type == QuerySpec::Search && search_out) {
+  if ((spec.type == QuerySpec::Search || spec.type == QuerySpec::Select) && search_out) {
     *search_out = std::move(spec);
     return nullptr;
   }
@@ -1213,6 +1220,207 @@ Result* Engine::execute_search(const QuerySpec& spec, double t0) {
   return res.release();
 }
 
+// Select (SelectSpec, DruidQuerySpec.scala:980-1098): the rows that pass interval and filter, a page at a time, in
+// segment order then row order (= time order inside a segment), with the requested dimension and metric values.
+// Three small kernels: per-unit counts of passing rows; the host then knows which units hold the page
+// [start offset per segment, threshold rows in all]; those units emit (segment, row) in row order; one gather per column.
+// Result columns: timestamp, segmentId, offset, dimensions..., metrics...; stats carry the pagingIdentifiers for the
+// next page (pass them back with fromNext = true).
+Result* Engine::execute_select(const QuerySpec& spec, double t0) {
+  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+  auto ds = store_.get(spec.data_source);
+  std::shared_lock<std::shared_mutex> lk(ds->mu);
+  check_cancel(spec.query_id);
+  // the rows of a group-by without dimensions over the same intervals and filter
+  QuerySpec g;
+  g.type = QuerySpec::GroupBy;
+  g.data_source = spec.data_source;
+  g.intervals = spec.intervals;
+  g.by_segments = spec.by_segments;
+  g.segments = spec.segments;
+  g.has_filter = spec.has_filter;
+  g.filter = spec.filter;
+  g.query_id = spec.query_id;
+  Plan plan = make_plan(g, ds, opt_);
+  struct OutCol { std::string name; bool metric; int index; int slot; int width; };
+  std::vector<OutCol> out_cols;
+  auto add_dim = [&](const std::string& n) {
+    if (n == "__time" || n == "timestamp") return;  // the timestamp column is always there
+    int di = ds->dim_index(n);
+    if (di < 0) throw NotFound("unknown dimension '" + n + "' in datasource '" + ds->name + "'");
+    out_cols.push_back({n, false, di, (int)plan.columns.size(), ds->dims[di].width});
+    plan.columns.push_back({false, di, ds->dims[di].width});
+  };
+  auto add_metric = [&](const std::string& n) {
+    int mi = ds->metric_index(n);
+    if (mi < 0) throw NotFound("unknown metric '" + n + "' in datasource '" + ds->name + "'");
+    out_cols.push_back({n, true, mi, (int)plan.columns.size(), 8});
+    plan.columns.push_back({true, mi, 8});
+  };
+  if (spec.select_dims.empty() && spec.select_metrics.empty()) {
+    for (auto& d : ds->dims) add_dim(d.name);
+    for (auto& m : ds->metrics) add_metric(m.name);
+  } else {
+    for (auto& n : spec.select_dims) add_dim(n);
+    for (auto& n : spec.select_metrics) add_metric(n);
+  }
+  if (plan.columns.size() > 250) throw Unsupported("select of more than 250 columns");
+
+  std::map<std::string, int64_t> paging(spec.paging_ids.begin(), spec.paging_ids.end());
+  std::vector<uint32_t> h_seg, h_row;
+  std::vector<int64_t> h_off;
+  std::vector<std::vector<unsigned long long>> h_cols(out_cols.size());
+  int64_t launches = 0;
+  if (!plan.always_false && plan.n_units > 0) {
+    QueryCtx* ctx = acquire_ctx();
+    ScanState st;
+    uint32_t* d_counts = nullptr;
+    SelectUnit* d_units = nullptr;
+    uint32_t *d_seg = nullptr, *d_row = nullptr;
+    void* d_col = nullptr;
+    auto cleanup = [&] {
+      cudaStreamSynchronize(ctx->stream);
+      for (void* q : {(void*)d_counts, (void*)d_units, (void*)d_seg, (void*)d_row, d_col})
+        if (q) cudaFreeAsync(q, ctx->stream);
+      free_state(ctx, &st);
+      release_ctx(ctx);
+    };
+    try {
+      cudaStream_t s = ctx->stream;
+      prepare_params(ctx, plan, &st);
+      const ScanParams& p = st.params;
+      SDO_CUDA(cudaMallocAsync((void**)&d_counts, (size_t)plan.n_units * 4, s));
+      launch_select_count(p, d_counts, s);
+      std::vector<uint32_t> counts(plan.n_units);
+      SDO_CUDA(cudaMemcpyAsync(counts.data(), d_counts, counts.size() * 4, cudaMemcpyDeviceToHost, s));
+      SDO_CUDA(cudaStreamSynchronize(s));
+      launches += 1;
+      // which units hold the page: walk the spans in order, keeping each segment's count of matching rows so far
+      std::vector<SelectUnit> units;
+      std::map<uint32_t, int64_t> seg_pos;  // plan segment -> matching rows before the current unit
+      int64_t remaining = spec.paging_threshold;
+      uint32_t out_base = 0;
+      for (size_t si = 0; si < plan.spans.size() && remaining > 0; si++) {
+        const DevSpan& sp = plan.spans[si];
+        const uint32_t u_end = si + 1 < plan.spans.size() ? plan.spans[si + 1].unit_begin : plan.n_units;
+        const Segment& sg = *ds->segments[plan.seg_index[sp.seg]];
+        auto it = paging.find(segment_identifier(*ds, sg));
+        const int64_t start = it == paging.end() ? 0 : it->second + (spec.paging_from_next ? 1 : 0);
+        int64_t& pos = seg_pos[sp.seg];
+        for (uint32_t u = sp.unit_begin; u < u_end && remaining > 0; u++) {
+          const int64_t c = counts[u], lo = pos;
+          pos += c;
+          if (pos <= start || c == 0) continue;
+          const int64_t skip = std::max<int64_t>(start, lo) - lo;
+          const int64_t take = std::min<int64_t>(c - skip, remaining);
+          units.push_back({u, (uint32_t)skip, (uint32_t)take, out_base});
+          for (int64_t k = 0; k < take; k++) h_off.push_back(lo + skip + k);
+          out_base += (uint32_t)take;
+          remaining -= take;
+        }
+      }
+      const uint32_t n_out = out_base;
+      if (n_out) {
+        SDO_CUDA(cudaMallocAsync((void**)&d_units, units.size() * sizeof(SelectUnit), s));
+        SDO_CUDA(cudaMemcpyAsync(d_units, units.data(), units.size() * sizeof(SelectUnit), cudaMemcpyHostToDevice, s));
+        SDO_CUDA(cudaMallocAsync((void**)&d_seg, (size_t)n_out * 4, s));
+        SDO_CUDA(cudaMallocAsync((void**)&d_row, (size_t)n_out * 4, s));
+        launch_select_emit(p, d_units, (uint32_t)units.size(), d_seg, d_row, s);
+        h_seg.resize(n_out);
+        h_row.resize(n_out);
+        SDO_CUDA(cudaMemcpyAsync(h_seg.data(), d_seg, (size_t)n_out * 4, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaMemcpyAsync(h_row.data(), d_row, (size_t)n_out * 4, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaMallocAsync(&d_col, (size_t)n_out * 8, s));
+        for (size_t c = 0; c < out_cols.size(); c++) {
+          const OutCol& oc = out_cols[c];
+          launch_select_gather(p, oc.slot, oc.width, d_seg, d_row, n_out, d_col, s);
+          h_cols[c].resize(n_out);  // ids arrive as uint32: two per word
+          SDO_CUDA(cudaMemcpyAsync(h_cols[c].data(), d_col, (size_t)n_out * (oc.width == 8 ? 8 : 4), cudaMemcpyDeviceToHost, s));
+          SDO_CUDA(cudaStreamSynchronize(s));  // d_col is reused by the next column
+        }
+        SDO_CUDA(cudaStreamSynchronize(s));
+        launches += 1 + (int64_t)out_cols.size();
+      }
+    } catch (...) {
+      cleanup();
+      throw;
+    }
+    cleanup();
+  }
+  // ---- result columns ---------------------------------------------------------------------------------------------
+  const size_t n = h_seg.size();
+  std::unique_ptr<Result> res(new Result());
+  res->n_rows = (int64_t)n;
+  ResultColumn ts, sid, off;
+  ts.name = "timestamp";
+  ts.type = SDO_RES_TIMESTAMP;
+  sid.name = "segmentId";
+  sid.type = SDO_RES_STRING;
+  sid.dict = std::make_shared<Dictionary>();
+  off.name = "offset";
+  off.type = SDO_RES_INT64;
+  std::map<uint32_t, uint32_t> sid_ids;
+  for (size_t i = 0; i < n; i++) {
+    const Segment& sg = *ds->segments[plan.seg_index[h_seg[i]]];
+    // the row's (truncated) time: the run of the time index that holds it
+    const size_t run = (size_t)(std::upper_bound(sg.time_rows.begin(), sg.time_rows.end(), (int64_t)h_row[i]) - sg.time_rows.begin()) - 1;
+    ts.i64.push_back(sg.time_vals.at(run));
+    auto it = sid_ids.find(h_seg[i]);
+    if (it == sid_ids.end()) {
+      it = sid_ids.emplace(h_seg[i], (uint32_t)sid.dict->size()).first;
+      const std::string id = segment_identifier(*ds, sg);
+      sid.dict->push(id.data(), id.size());
+      paging[id] = h_off[i];
+    }
+    sid.ids.push_back(it->second);
+    off.i64.push_back(h_off[i]);
+    paging[sid.dict->get(it->second)] = std::max(paging[sid.dict->get(it->second)], h_off[i]);
+  }
+  res->columns.push_back(std::move(ts));
+  res->columns.push_back(std::move(sid));
+  res->columns.push_back(std::move(off));
+  for (size_t c = 0; c < out_cols.size(); c++) {
+    const OutCol& oc = out_cols[c];
+    ResultColumn col;
+    col.name = oc.name;
+    if (oc.metric) {
+      if (ds->metrics[oc.index].is_float) {
+        col.type = SDO_RES_FLOAT64;
+        col.f64.resize(n);
+        if (n) memcpy(col.f64.data(), h_cols[c].data(), n * 8);
+      } else {
+        col.type = SDO_RES_INT64;
+        col.i64.resize(n);
+        if (n) memcpy(col.i64.data(), h_cols[c].data(), n * 8);
+      }
+    } else {
+      const uint32_t* ids = (const uint32_t*)h_cols[c].data();
+      if (ds->dims[oc.index].enc == DimEncoding::Dict) {
+        col.type = SDO_RES_STRING;
+        col.dict = ds->dims[oc.index].dict;
+        col.ids.assign(ids, ids + n);
+      } else {
+        col.type = SDO_RES_DIM_INT64;
+        col.i64.resize(n);
+        for (size_t i = 0; i < n; i++) col.i64[i] = (int64_t)ids[i];
+      }
+    }
+    res->columns.push_back(std::move(col));
+  }
+  std::string pj = "{";
+  for (auto& kv : paging) {
+    if (pj.size() > 1) pj += ",";
+    json_escape(pj, kv.first);
+    pj += ":" + std::to_string((long long)kv.second);
+  }
+  pj += "}";
+  char buf[256];
+  snprintf(buf, sizeof buf, "{\"queryType\":\"select\",\"rowsScanned\":%lld,\"resultRows\":%lld,\"launches\":%lld,\"totalMs\":%.6f,\"pagingIdentifiers\":",
+           (long long)plan.rows_scanned, (long long)n, (long long)launches, now_ms() - t0);
+  res->stats = std::string(buf) + pj + "}";
+  return res.release();
+}
+
 Result* Engine::execute_plan(const Plan& plan, double t0) {
   if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
   QueryCtx* ctx = acquire_ctx();
@@ -1239,7 +1447,7 @@ Result* Engine::execute(const char* json, size_t len) {
   std::shared_lock<std::shared_mutex> lk;
   QuerySpec search;
   std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk, &search);
-  if (!plan_ptr) return execute_search(search, t0);
+  if (!plan_ptr) return search.type == QuerySpec::Select ? execute_select(search, t0) : execute_search(search, t0);
   const Plan& plan = *plan_ptr;
   check_cancel(plan.spec.query_id);
   if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");

@@ -151,7 +151,9 @@ class Engine {
   void release_ctx(QueryCtx* c);
   void ensure_pinned(void** p, size_t* cur, size_t need);
   void check_cancel(const std::string& qid);
+  void prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st);
   void run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st);
+  Result* execute_select(const QuerySpec& spec, double t_start_ms);
   // search_out (optional): a search query has no plan of its own -- its spec is handed back and nullptr returned
   std::shared_ptr<const Plan> plan_for(const char* json, size_t len, std::shared_lock<std::shared_mutex>* lock_out, QuerySpec* search_out = nullptr);
   Result* execute_search(const QuerySpec& spec, double t_start_ms);

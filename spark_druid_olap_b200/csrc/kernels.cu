@@ -567,3 +567,118 @@ void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut
   SDO_CUDA(cudaGetLastError());
 }
 }  // namespace sdo
+
+// ---------------------------------------------------------------------------------------------
+// Select queries: which rows pass, in row order, and their column values
+// ---------------------------------------------------------------------------------------------
+namespace sdo {
+namespace {
+
+// the query's filter on one row (same postfix program as the scan's, one bit per stack entry)
+__device__ __forceinline__ bool row_passes(const ScanParams& p, const void* const* cols, uint32_t r) {
+  uint32_t stack = 0;  // bit 0 = top
+  for (int k = 0; k < p.n_ops; k++) {
+    const uint32_t op = p.op_code[k];
+    if (op == FOP_LEAF) stack = (stack << 1) | leaf_test<1>(p, p.op_arg[k], cols, r);
+    else if (op == FOP_TRUE) stack = (stack << 1) | 1u;
+    else if (op == FOP_FALSE) stack <<= 1;
+    else if (op == FOP_NOT) stack ^= 1u;
+    else {
+      const uint32_t a = stack & 1u;
+      stack >>= 1;
+      stack = op == FOP_AND ? ((stack & ~1u) | (stack & a)) : (stack | a);
+    }
+  }
+  return p.n_ops == 0 || (stack & 1u);
+}
+
+// span of unit u (block-uniform): coarse window, then the threads probe it
+__device__ __forceinline__ uint32_t span_of_unit(const ScanParams& p, const uint32_t* coarse, uint32_t u, uint32_t* s_span) {
+  const uint32_t lo = coarse[u / 64], hi = coarse[u / 64 + 1];
+  for (uint32_t s = lo + threadIdx.x; s <= hi && s < p.n_spans; s += blockDim.x)
+    if (p.spans[s].unit_begin <= u && u < p.spans[s + 1].unit_begin) *s_span = s;
+  __syncthreads();
+  return *s_span;
+}
+
+}  // namespace
+
+// counts[u] = rows of unit u that pass the filter
+__global__ void __launch_bounds__(256) select_count_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse, uint32_t* __restrict__ counts) {
+  __shared__ uint32_t s_span, s_count;
+  for (uint32_t u = blockIdx.x; u < p.n_units; u += gridDim.x) {
+    if (threadIdx.x == 0) s_count = 0;
+    const DevSpan sp = p.spans[span_of_unit(p, coarse, u, &s_span)];
+    const void* const* cols = p.segptr + (size_t)sp.seg * p.n_cols;
+    const uint32_t first = (sp.row_begin & ~3u) + (u - sp.unit_begin) * UNIT_ROWS;
+    uint32_t mine = 0;
+    for (uint32_t r = first + threadIdx.x; r < first + UNIT_ROWS && r < sp.row_end; r += 256)
+      if (r >= sp.row_begin && row_passes(p, cols, r)) mine++;
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0 && mine) atomicAdd(&s_count, mine);
+    __syncthreads();
+    if (threadIdx.x == 0) counts[u] = s_count;
+    __syncthreads();
+  }
+}
+
+// One block per selected unit: the passing rows with rank (in row order) in [skip, skip + take) go to out[out_base ...].
+__global__ void __launch_bounds__(256) select_emit_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse, const SelectUnit* __restrict__ units,
+                                                          uint32_t* __restrict__ out_seg, uint32_t* __restrict__ out_row) {
+  __shared__ uint32_t s_span, s_warp[8];
+  const SelectUnit su = units[blockIdx.x];
+  const DevSpan sp = p.spans[span_of_unit(p, coarse, su.unit, &s_span)];
+  const void* const* cols = p.segptr + (size_t)sp.seg * p.n_cols;
+  const uint32_t first = (sp.row_begin & ~3u) + (su.unit - sp.unit_begin) * UNIT_ROWS;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  uint32_t seen = 0;  // passing rows of the earlier rounds
+  for (uint32_t r0 = first; r0 < first + UNIT_ROWS && r0 < sp.row_end; r0 += 256) {
+    const uint32_t r = r0 + threadIdx.x;
+    const bool ok = r >= sp.row_begin && r < sp.row_end && row_passes(p, cols, r);
+    const unsigned b = __ballot_sync(0xffffffffu, ok);
+    if (lane == 0) s_warp[warp] = __popc(b);
+    __syncthreads();
+    uint32_t before = 0, total = 0;
+    for (uint32_t w = 0; w < 8; w++) {
+      if (w < warp) before += s_warp[w];
+      total += s_warp[w];
+    }
+    const uint32_t rank = seen + before + __popc(b & ((1u << lane) - 1u));
+    if (ok && rank >= su.skip && rank < su.skip + su.take) {
+      out_seg[su.out_base + rank - su.skip] = sp.seg;
+      out_row[su.out_base + rank - su.skip] = r;
+    }
+    seen += total;
+    __syncthreads();
+  }
+}
+
+// out[i] = column `col` of row (seg[i], row[i]), widened: ids -> uint32, metrics -> 8 bytes
+__global__ void select_gather_kernel(const void* const* __restrict__ segptr, uint32_t n_cols, int col, int width, const uint32_t* __restrict__ seg,
+                                     const uint32_t* __restrict__ row, uint32_t n, void* __restrict__ out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const void* base = segptr[(size_t)seg[i] * n_cols + col];
+  const uint32_t r = row[i];
+  if (width == 8) ((unsigned long long*)out)[i] = ((const unsigned long long*)base)[r];
+  else ((uint32_t*)out)[i] = width == 1 ? ((const uint8_t*)base)[r] : (width == 2 ? ((const uint16_t*)base)[r] : ((const uint32_t*)base)[r]);
+}
+
+void launch_select_count(const ScanParams& p, uint32_t* counts, cudaStream_t st) {
+  if (!p.n_units) return;
+  const uint32_t* coarse = (const uint32_t*)(p.spans + p.n_spans + 1);
+  select_count_kernel<<<(unsigned)std::min<uint32_t>(p.n_units, 148 * 8), 256, 0, st>>>(p, coarse, counts);
+  SDO_CUDA(cudaGetLastError());
+}
+void launch_select_emit(const ScanParams& p, const SelectUnit* units, uint32_t n_units, uint32_t* out_seg, uint32_t* out_row, cudaStream_t st) {
+  if (!n_units) return;
+  const uint32_t* coarse = (const uint32_t*)(p.spans + p.n_spans + 1);
+  select_emit_kernel<<<n_units, 256, 0, st>>>(p, coarse, units, out_seg, out_row);
+  SDO_CUDA(cudaGetLastError());
+}
+void launch_select_gather(const ScanParams& p, int col, int width, const uint32_t* seg, const uint32_t* row, uint32_t n, void* out, cudaStream_t st) {
+  if (!n) return;
+  select_gather_kernel<<<(n + 255) / 256, 256, 0, st>>>(p.segptr, p.n_cols, col, width, seg, row, n, out);
+  SDO_CUDA(cudaGetLastError());
+}
+}  // namespace sdo

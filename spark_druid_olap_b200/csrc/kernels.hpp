@@ -239,6 +239,13 @@ void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size
                            const ScanParams& p, unsigned long long* table, cudaStream_t st);
 void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
 
+// select queries: per-unit counts of passing rows; then, for the units that hold the wanted page, the passing rows with
+// rank in [skip, skip + take) in row order; then a gather of each requested column
+struct SelectUnit { uint32_t unit, skip, take, out_base; };
+void launch_select_count(const ScanParams& p, uint32_t* counts, cudaStream_t st);
+void launch_select_emit(const ScanParams& p, const SelectUnit* units, uint32_t n_units, uint32_t* out_seg, uint32_t* out_row, cudaStream_t st);
+void launch_select_gather(const ScanParams& p, int col, int width, const uint32_t* seg, const uint32_t* row, uint32_t n, void* out, cudaStream_t st);
+
 #endif  // !__CUDACC_RTC__
 
 }  // namespace sdo

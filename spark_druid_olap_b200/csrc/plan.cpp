@@ -485,6 +485,7 @@ void build_extraction(const DimMeta& dm, const ExtractionFn& fn, PlanDim* pd) {
 Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const PlanOptions& opt) {
   if (spec.type == QuerySpec::Search)
     throw Unsupported("a search query has no single plan: sdo_query_execute runs it as one group-by per search dimension");
+  if (spec.type == QuerySpec::Select) throw Unsupported("a select query returns rows, not groups: sdo_query_execute pages through it; there is no aggregation plan");
   Plan plan;
   plan.spec = spec;
   plan.ds = ds_ptr;

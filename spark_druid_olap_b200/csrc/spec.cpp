@@ -398,7 +398,8 @@ QuerySpec parse_query_spec(const Json& j) {
   else if (qt == "timeseries") q.type = QuerySpec::Timeseries;
   else if (qt == "topN") q.type = QuerySpec::TopN;
   else if (qt == "search") q.type = QuerySpec::Search;
-  else throw Unsupported("queryType '" + qt + "' is not supported by the GPU engine (groupBy, timeseries, topN only)");
+  else if (qt == "select") q.type = QuerySpec::Select;
+  else throw Unsupported("queryType '" + qt + "' is not supported by the GPU engine (groupBy, timeseries, topN, search, select)");
   const Json* ds = j.find("dataSource");
   if (!ds) throw Invalid("query: missing 'dataSource'");
   q.data_source = ds->is_obj() ? ds->get_str("name") : j.get_str("dataSource");
@@ -459,6 +460,30 @@ QuerySpec parse_query_spec(const Json& j) {
       }
     }
     if (const Json* h = j.find("having")) { q.has_having = true; q.having = parse_having(*h); }
+  } else if (q.type == QuerySpec::Select) {
+    if (q.granularity.kind != Granularity::All) throw Unsupported("select query with a granularity other than 'all'");
+    if (j.get_bool("descending", false)) throw Unsupported("select query with descending = true");
+    for (const char* key : {"dimensions", "metrics"}) {
+      if (const Json* d = j.find(key)) {
+        if (!d->is_arr()) throw Invalid(std::string("'") + key + "' must be an array");
+        for (auto& x : d->arr) {
+          if (x.is_obj() && x.get_str("type", "default") != "default") throw Unsupported("select query with an extraction dimension");
+          (key[0] == 'd' ? q.select_dims : q.select_metrics).push_back(x.is_obj() ? x.get_str("dimension") : x.str);
+        }
+      }
+    }
+    const Json* ps = j.find("pagingSpec");
+    if (!ps || !ps->is_obj()) throw Invalid("select: missing 'pagingSpec'");
+    q.paging_threshold = ps->get_int("threshold", 0);
+    if (q.paging_threshold <= 0) throw Invalid("select: pagingSpec.threshold must be positive");
+    q.paging_from_next = ps->get_bool("fromNext", false);
+    if (const Json* ids = ps->find("pagingIdentifiers")) {
+      if (!ids->is_obj()) throw Invalid("select: pagingSpec.pagingIdentifiers must be an object");
+      for (auto& kv : ids->obj) {
+        if (!kv.second.is_num()) throw Invalid("select: paging offsets must be numbers");
+        q.paging_ids.emplace_back(kv.first, kv.second.is_int ? kv.second.inum : (int64_t)kv.second.num);
+      }
+    }
   } else if (q.type == QuerySpec::Search) {
     if (q.granularity.kind != Granularity::All) throw Unsupported("search query with a granularity other than 'all'");
     if (const Json* d = j.find("searchDimensions")) {

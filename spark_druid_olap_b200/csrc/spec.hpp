@@ -90,7 +90,14 @@ struct TopNMetric {
 struct SegmentIntervalRef { Interval itvl; std::string version; int part = -1; };
 
 struct QuerySpec {
-  enum Type { GroupBy, Timeseries, TopN, Search } type = GroupBy;
+  enum Type { GroupBy, Timeseries, TopN, Search, Select } type = GroupBy;
+  // Select (SelectSpecWithIntervals / ...WithSegmentIntervals, DruidQuerySpec.scala:1021-1098): the rows themselves, a
+  // page at a time, in segment order then row order.  paging_ids: segment identifier -> offset among the segment's
+  // matching rows where the previous page stopped (PagingSpec, :976-978).
+  std::vector<std::string> select_dims, select_metrics;   // empty = all
+  std::vector<std::pair<std::string, int64_t>> paging_ids;
+  int64_t paging_threshold = 0;
+  bool paging_from_next = false;
   // Search (SearchQuerySpec, DruidQuerySpec.scala:870-927): which values of `search_dimensions` occur, with row counts.
   // The planner turns a group-by on one dimension without aggregations into this (QuerySpecTransforms.scala:224-278).
   std::vector<std::string> search_dimensions;       // empty = every dimension

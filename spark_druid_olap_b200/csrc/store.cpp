@@ -564,6 +564,10 @@ std::string Store::metadata_json(const std::string& name) const {
   return o;
 }
 
+std::string segment_identifier(const DataSource& ds, const Segment& s) {
+  return ds.name + "_" + format_iso_instant(s.start_ms) + "/" + format_iso_instant(s.end_ms) + "_v1_" + std::to_string(s.partition);
+}
+
 std::string Store::segments_json(const std::string& name) const {
   auto ds = get(name);
   std::shared_lock<std::shared_mutex> lk(ds->mu);
@@ -575,7 +579,7 @@ std::string Store::segments_json(const std::string& name) const {
     first = false;
     std::string itv = format_iso_instant(s->start_ms) + "/" + format_iso_instant(s->end_ms);
     o += "{\"identifier\":";
-    json_escape(o, ds->name + "_" + itv + "_v1_" + std::to_string(s->partition));
+    json_escape(o, segment_identifier(*ds, *s));
     o += ",\"interval\":\"" + itv + "\",\"version\":\"v1\",\"size\":" + std::to_string((unsigned long long)s->device_bytes);
     o += ",\"numRows\":" + std::to_string((long long)s->n_rows);
     o += ",\"shardSpec\":{\"type\":\"linear\",\"partitionNum\":" + std::to_string(s->partition) + "}";

@@ -129,6 +129,8 @@ class Store {
   void merge_dictionary(DataSource& ds, int di, const Dictionary& bd, std::vector<uint32_t>* code_to_id);
 };
 
+// Druid-style segment identifier: <datasource>_<interval>_<version>_<partition> (DruidSegmentInfo.identifier)
+std::string segment_identifier(const DataSource& ds, const Segment& s);
 int64_t truncate_time(const std::string& gran, int64_t t);
 int64_t segment_start(const std::string& gran, int64_t t);
 int64_t segment_end(const std::string& gran, int64_t start);

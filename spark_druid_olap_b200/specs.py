@@ -335,6 +335,27 @@ class TimeSeriesQuerySpec(_Spec):
                          context)
 
 
+class PagingSpec(_Spec):
+    """DruidQuerySpec.scala:976-978"""
+    _fields = ("pagingIdentifiers", "threshold", "fromNext")
+
+    def __init__(self, pagingIdentifiers, threshold, fromNext=None):
+        super().__init__(dict(pagingIdentifiers), threshold, fromNext)
+
+
+class SelectSpecWithIntervals(_Spec):
+    """DruidQuerySpec.scala:1021-1067"""
+    _fields = ("queryType", "dataSource", "dimensions", "metrics", "filter", "pagingSpec", "intervals", "descending", "granularity", "context")
+
+    def __init__(self, dataSource, dimensions, metrics, filter, pagingSpec, intervals, descending=False, granularity="all", context=None):
+        super().__init__("select", dataSource, list(dimensions), list(metrics), filter, pagingSpec, list(intervals), descending, granularity, context)
+
+    def withPagingIdentifier(self, ps):
+        d = self.to_dict()
+        d["pagingSpec"] = dict(d["pagingSpec"], pagingIdentifiers=dict(ps), fromNext=True)
+        return d
+
+
 class InsensitiveContainsSearchQuerySpec(_Spec):
     """DruidQuerySpec.scala:547-552"""
     _fields = ("type", "value")

@@ -311,7 +311,7 @@ def test_unsupported_and_invalid(loaded):
     with pytest.raises(sdo.DruidDataSourceException):
         eng.execute(dict(json.loads(Q.q1_style().to_json()), dataSource="nope"))
     with pytest.raises(sdo.UnsupportedQuery):
-        eng.execute({"queryType": "select", "dataSource": "tpch"})
+        eng.execute({"queryType": "segmentMetadata", "dataSource": "tpch"})
 
 
 def test_cancel(loaded):

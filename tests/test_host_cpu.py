@@ -202,7 +202,11 @@ def test_error_statuses(planning):
     with pytest.raises(sdo.InvalidQuery):
         eng.explain({"queryType": "groupBy", "dataSource": "tpch", "granularity": "fortnight", "aggregations": []})
     with pytest.raises(sdo.UnsupportedQuery):
-        eng.explain({"queryType": "select", "dataSource": "tpch"})
+        eng.explain({"queryType": "segmentMetadata", "dataSource": "tpch"})
+    with pytest.raises(sdo.InvalidQuery):
+        eng.explain({"queryType": "select", "dataSource": "tpch"})  # no 'pagingSpec'
+    with pytest.raises(sdo.UnsupportedQuery):  # rows, not groups: nothing to explain
+        eng.explain(Q.SelectSpecWithIntervals("tpch", ["s_nation"], [], None, Q.PagingSpec({}, 10), Q.ALL_TIME))
     with pytest.raises(sdo.InvalidQuery):
         eng.explain({"queryType": "search", "dataSource": "tpch"})  # no 'query'
     with pytest.raises(sdo.UnsupportedQuery):  # a search runs as one group-by per dimension: there is no single plan to explain
