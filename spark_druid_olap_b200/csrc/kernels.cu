@@ -29,6 +29,7 @@ size_t scan_hll_smem_bytes(int hll_mode, bool wide, uint64_t n_keys, int n_hll) 
 }
 size_t scan_smem_bytes(int strategy, uint64_t n_keys, int n_slots, uint32_t replicas, uint32_t rep_stride) {
   if (strategy == STRAT_LANE) return (size_t)n_keys * n_slots * SCAN_THREADS * 8;
+  if (strategy == STRAT_SPAN) return (size_t)n_slots * SCAN_THREADS * 8;
   if (strategy == STRAT_BLOCK) return replicas > 1 ? (size_t)replicas * rep_stride * 8 : (size_t)n_keys * n_slots * 8;
   return 0;
 }
@@ -63,6 +64,7 @@ int scan_grid_size(int strategy, size_t smem_bytes, int sm_count) {
     case STRAT_LANE: nb = occupancy<STRAT_LANE>(smem_bytes); break;
     case STRAT_BLOCK: nb = occupancy<STRAT_BLOCK>(smem_bytes); break;
     case STRAT_GLOBAL: nb = occupancy<STRAT_GLOBAL>(smem_bytes); break;
+    case STRAT_SPAN: nb = occupancy<STRAT_SPAN>(smem_bytes); break;
     default: nb = occupancy<STRAT_HASH>(smem_bytes); break;
   }
   if (nb < 1) nb = 1;
@@ -76,6 +78,7 @@ void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem, cudaS
     case STRAT_LANE: opt_in_shared_memory<STRAT_LANE>(); scan_kernel<STRAT_LANE><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     case STRAT_BLOCK: opt_in_shared_memory<STRAT_BLOCK>(); scan_kernel<STRAT_BLOCK><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     case STRAT_GLOBAL: opt_in_shared_memory<STRAT_GLOBAL>(); scan_kernel<STRAT_GLOBAL><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    case STRAT_SPAN: opt_in_shared_memory<STRAT_SPAN>(); scan_kernel<STRAT_SPAN><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     default: opt_in_shared_memory<STRAT_HASH>(); scan_kernel<STRAT_HASH><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
   }
   SDO_CUDA(cudaGetLastError());

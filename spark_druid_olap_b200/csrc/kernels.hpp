@@ -129,6 +129,9 @@ enum Strategy : int32_t {
   STRAT_BLOCK = 1,  // block-shared shared-memory table with shared atomics
   STRAT_HASH = 2,   // open-addressing global hash table (atomicCAS)
   STRAT_GLOBAL = 3, // direct-indexed global table (dense key space too big for shared memory)
+  STRAT_SPAN = 4,   // no grouping dimension (timeseries): the key is constant over a span, so a thread keeps private
+                    // accumulators for its warp's current key only and the warp merges them into the direct-indexed
+                    // HBM table when it moves to another key -- no atomics, votes or shuffles per row
 };
 
 struct ScanParams {

@@ -15,6 +15,7 @@ const char* strategy_name(int s) {
     case STRAT_LANE: return "lane";
     case STRAT_BLOCK: return "block";
     case STRAT_GLOBAL: return "global";
+    case STRAT_SPAN: return "span";
     case STRAT_HASH: return "hash";
   }
   return "?";
@@ -841,6 +842,11 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   int strat;
   std::string why;
   if (plan.n_keys <= (1ull << 20) && cells <= opt.lane_max_cells) { strat = STRAT_LANE; why = "key space x slots = " + std::to_string(cells) + " cells fit lane-private shared memory"; }
+  else if (plan.dev_dims.empty() && plan.n_keys <= (1ull << 31)) {
+    // timeseries with more buckets than lane-private memory holds: the key never changes inside a span
+    strat = STRAT_SPAN;
+    why = "no grouping dimension: private accumulators for the current time bucket, merged into a direct table of " + std::to_string(plan.n_keys) + " rows";
+  }
   else if (plan.n_keys <= (1ull << 24) && cells * 8 <= opt.block_max_bytes) { strat = STRAT_BLOCK; why = "table of " + std::to_string(cells * 8) + " bytes fits shared memory"; }
   else if (plan.n_keys <= opt.global_max_keys) { strat = STRAT_GLOBAL; why = "dense key space of " + std::to_string(plan.n_keys) + " keys indexed directly in HBM"; }
   else if (plan.n_hll == 0 && plan.n_keys <= opt.global_big_max_keys && plan.n_keys <= 4 * (uint64_t)std::max<int64_t>(plan.rows_scanned, 1) &&
@@ -853,7 +859,8 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   else { strat = STRAT_HASH; why = "key space of " + std::to_string(plan.n_keys) + " keys is sparse: open-addressing hash table"; }
   if (!spec.gpu_strategy.empty()) {
     const std::string& g = spec.gpu_strategy;
-    int forced = g == "lane" ? STRAT_LANE : g == "block" ? STRAT_BLOCK : g == "global" ? STRAT_GLOBAL : g == "hash" ? STRAT_HASH : -1;
+    int forced = g == "lane" ? STRAT_LANE : g == "block" ? STRAT_BLOCK : g == "global" ? STRAT_GLOBAL : g == "hash" ? STRAT_HASH : g == "span" ? STRAT_SPAN : -1;
+    if (forced == STRAT_SPAN && !plan.dev_dims.empty()) throw Invalid("gpuStrategy span: the query has grouping dimensions");
     if (forced < 0) throw Invalid("context.gpuStrategy '" + g + "'");
     if (forced == STRAT_LANE && (cells > 104 || plan.n_keys > (1ull << 20))) throw Invalid("gpuStrategy lane: key space too large");
     if (forced == STRAT_BLOCK && (cells * 8 > 200 * 1024 || plan.n_keys > (1ull << 24))) throw Invalid("gpuStrategy block: key space too large");

@@ -268,6 +268,23 @@ struct Acc<STRAT_LANE> {
   __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v < c) *(long long*)q = v; }
   __device__ __forceinline__ void max_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v > c) *(long long*)q = v; }
 };
+template <>
+struct Acc<STRAT_SPAN> {
+  typedef uint32_t key_t;
+  unsigned long long* base;  // smem + tid
+  int ns;
+  unsigned int* hll_sm;  // shared-memory HLL sketches (HLL_IN_SMEM_*), as words
+  static constexpr int SLOT_STRIDE = SCAN_THREADS;  // elements between consecutive slots of one group
+  // one set of slots per thread, for the warp's current key (scan_body flushes it when the key changes)
+  __device__ __forceinline__ unsigned long long* at(key_t) const { return base; }
+  // a thread's own count stays far below 2^32: bump the low word only
+  __device__ __forceinline__ void count1(unsigned long long* q) const { *(unsigned int*)q += 1u; }
+  __device__ __forceinline__ void countn(unsigned long long* q, int c) const { *(unsigned int*)q += (unsigned int)c; }
+  __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { *q += (unsigned long long)v; }
+  __device__ __forceinline__ void add_f64(unsigned long long* q, double v) const { *(double*)q += v; }
+  __device__ __forceinline__ void min_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v < c) *(long long*)q = v; }
+  __device__ __forceinline__ void max_i64(unsigned long long* q, long long v) const { long long c = *(long long*)q; if (v > c) *(long long*)q = v; }
+};
 // shared-memory or global atomics; the pointer's address space is visible after inlining
 struct AtomicOps {
   __device__ __forceinline__ void add_i64(unsigned long long* q, long long v) const { atomicAdd(q, (unsigned long long)v); }
@@ -572,7 +589,7 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
   for (int i = 0; i < R; i++) row[i] = acc.at(key[i]);
   bool uni = false, is_leader = false;
   unsigned long long* rowL = row[0];
-  if (WARP && STRAT != STRAT_LANE) {
+  if (WARP && STRAT != STRAT_LANE && STRAT != STRAT_SPAN) {
     key_t lk = key[0];
 #pragma unroll
     for (int i = R - 1; i >= 0; i--)
@@ -739,6 +756,26 @@ __device__ __forceinline__ unsigned long long slot_merge(int op, unsigned long l
   return (unsigned long long)max((long long)v, (long long)w);
 }
 
+// STRAT_SPAN: fold the warp's 32 private copies of every slot, merge them into row `key` of the HBM table, start over
+__device__ __forceinline__ void span_flush(const ScanParams& p, unsigned long long* smem, int tid, int ns, uint64_t key) {
+  for (int s = 0; s < ns; s++) {
+    unsigned long long* cell = smem + (size_t)s * SCAN_THREADS + tid;
+    const unsigned long long init = p.slot_init[s];
+    const int op = p.slot_op[s];
+    unsigned long long v = *cell;
+    *cell = init;
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v = slot_merge(op, v, __shfl_xor_sync(0xffffffffu, v, off));
+    if ((tid & 31) == 0 && v != init) {
+      unsigned long long* q = p.table + key * (uint64_t)ns + s;
+      if (op == SLOT_SUM_I64) atomicAdd(q, v);
+      else if (op == SLOT_SUM_F64) atomicAdd((double*)q, __longlong_as_double((long long)v));
+      else if (op == SLOT_MIN_I64) atomicMin((long long*)q, (long long)v);
+      else atomicMax((long long*)q, (long long)v);
+    }
+  }
+}
+
 // ---- the kernel body ------------------------------------------------------------------------------------------------
 // `coarse` = coarse span index, stored right after the n_spans + 1 span records in the per-query device blob.
 template <int STRAT>
@@ -759,7 +796,7 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   const uint32_t hll_copy_words = Q_HLL_WIDE ? hll_words * 4u : hll_words;
   const uint32_t hll_sm_words = hll_copy_words * hll_copies;
   {
-    size_t table_words = STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS
+    size_t table_words = STRAT == STRAT_SPAN ? (size_t)ns * SCAN_THREADS : STRAT == STRAT_LANE ? (size_t)p.n_keys * ns * SCAN_THREADS
                          : (STRAT == STRAT_BLOCK ? (p.rep_mask ? (size_t)(p.rep_mask + 1u) * p.rep_stride : (size_t)p.n_keys * ns) : 0);
     acc.hll_sm = (unsigned int*)(smem + ((table_words + 1) & ~(size_t)1));  // 16-byte aligned (the host pads likewise)
     for (uint32_t w = tid; w < hll_sm_words; w += SCAN_THREADS) acc.hll_sm[w] = 0u;
@@ -767,7 +804,11 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   }
   const uint32_t flush_first = hll_copies > 1 ? lane : (uint32_t)tid, flush_step = hll_copies > 1 ? 32u : (uint32_t)SCAN_THREADS;
   uint64_t hll_key = ~0ull;  // HLL_IN_SMEM_SPAN: group whose sketch is cached (uniform over the warp / block)
-  if (STRAT == STRAT_LANE) {
+  uint64_t slot_key = ~0ull; // STRAT_SPAN: group the private accumulators belong to
+  if (STRAT == STRAT_SPAN) {
+    for (int x = 0; x < ns; x++) smem[(size_t)x * SCAN_THREADS + tid] = p.slot_init[x];
+    acc.base = smem + tid;
+  } else if (STRAT == STRAT_LANE) {
     const uint32_t n = (uint32_t)p.n_keys * ns;
     for (uint32_t x = 0; x < n; x++) smem[(size_t)x * SCAN_THREADS + tid] = p.slot_init[x % ns];
     acc.base = smem + tid;
@@ -833,6 +874,10 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
       }
       const uint32_t row0 = (sp.row_begin & ~3u) + (u - sp.unit_begin) * UNIT_ROWS + (t & ((1u << unit_ticket_shift) - 1u)) * ticket_rows;
       if (row0 >= sp.row_end) continue;  // the span ends before this quarter of its last unit
+      if (STRAT == STRAT_SPAN && sp.key_base != slot_key) {
+        if (slot_key != ~0ull) span_flush(p, smem, tid, ns, slot_key);
+        slot_key = sp.key_base;
+      }
       if (Q_HLL_PLACE == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
         // the warp's cached sketch belongs to another group: merge it into HBM, start an empty one
         __syncwarp();
@@ -869,6 +914,10 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
         sp = p.spans[s];
         next_begin = p.spans[s + 1].unit_begin;
       }
+      if (STRAT == STRAT_SPAN && sp.key_base != slot_key) {
+        if (slot_key != ~0ull) span_flush(p, smem, tid, ns, slot_key);
+        slot_key = sp.key_base;
+      }
       if (Q_HLL_PLACE == HLL_IN_SMEM_SPAN && sp.key_base != hll_key) {
         // the cached sketch belongs to another group: merge it into HBM, start an empty one
         __syncthreads();
@@ -892,7 +941,9 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
     }
   }
 
-  if (STRAT == STRAT_LANE) {
+  if (STRAT == STRAT_SPAN) {
+    if (slot_key != ~0ull) span_flush(p, smem, tid, ns, slot_key);
+  } else if (STRAT == STRAT_LANE) {
     // fixed-order reduction of the 256 lane-private copies: 8 strided values per lane, then a
     // shuffle tree; one warp per (key, slot)
     __syncthreads();

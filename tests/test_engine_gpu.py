@@ -148,6 +148,31 @@ def test_ticket_sizes(loaded, shape, rows):
     H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, q), what=f"{shape} {rows} jit")
 
 
+@pytest.mark.parametrize("strategy", [None, "span", "block", "global", "hash"])
+@pytest.mark.parametrize("shape", ["ts_day_hll", "ts_month_sum_filter", "ts_zoo"])
+def test_timeseries_strategies(loaded, shape, strategy):
+    """Queries without a grouping dimension default to the span strategy (private accumulators for the warp's current
+    time bucket); every other strategy must agree, filters (sparse row walks) and min / max slots included."""
+    eng, tbl = loaded
+    if shape == "ts_day_hll":
+        q = json.loads(Q.timeseries("P1D", True, strategy).to_json())
+    elif shape == "ts_month_sum_filter":
+        q = json.loads(Q.timeseries("P1M", True, strategy).to_json())
+        q["filter"] = json.loads(Q.And(Q.SelectorFilterSpec("l_returnflag", "R"), Q.ExtractionFilterSpec("l_shipmode", ["AIR", "MAIL"])).to_json())
+    else:
+        q = json.loads(Q.agg_zoo(strategy).to_json())
+        q["queryType"] = "timeseries"
+        q.pop("dimensions")
+        q["granularity"] = {"type": "period", "period": "P1W"}
+    res = eng.execute(q)
+    want, regs = orc.execute(tbl, q, return_registers=True)
+    H.assert_rows_equal(H.engine_rows(res), want, what=f"{shape} {strategy}")
+    assert res.stats["strategy"] == (strategy or "span")
+    order = np.argsort(res["timestamp"], kind="stable")
+    for name, r in regs.items():
+        assert np.array_equal(res.hll[name][order], r), name
+
+
 def test_timeseries_simple_granularity_strings(loaded):
     eng, tbl = loaded
     for g in ("day", "month", "year"):

@@ -21,6 +21,10 @@ SHAPES = {
     "tsday": (lambda: Q.timeseries("P1D", True, strategy), ["o_custkey", "l_extendedprice", "count"]),
     "tsmonth": (lambda: Q.timeseries("P1M", True, strategy), ["o_custkey", "l_extendedprice", "count"]),
     "okey": (lambda: Q.by_orderkey(strategy), ["o_orderkey", "l_extendedprice", "count"]),
+    "tssum": (lambda: Q.TimeSeriesQuerySpec(Q.DS, Q.ALL_TIME, Q.PeriodGranularitySpec("P1D"), None, [Q.agg("count", "n", "count"), Q.agg("doubleSum", "rev", "l_extendedprice")],
+                                            None, Q.ctx(strategy)), ["l_extendedprice", "count"]),
+    "tshll": (lambda: Q.TimeSeriesQuerySpec(Q.DS, Q.ALL_TIME, Q.PeriodGranularitySpec("P1D"), None, [Q.agg("count", "n", "count"), Q.CardinalityAggregationSpec("custs", ["o_custkey"])],
+                                            None, Q.ctx(strategy)), ["o_custkey", "count"]),
     "q7": (lambda: Q.q7(strategy), ["s_nation", "c_nation", "l_extendedprice"]),
     "year": (lambda: Q.with_extraction(Q.extraction_dims()[0][1], "s_nation", strategy), ["o_orderdate", "s_nation", "l_extendedprice", "o_custkey", "count"]),
     "yearsum": (lambda: Q.GroupByQuerySpec(Q.DS, [Q.extraction_dims()[0][1], Q.DefaultDimensionSpec("s_nation")], None, None, "all", None,
