@@ -241,6 +241,30 @@ def main():
         rows_total = int(tot[0])
     else:
         rows_total = rows_local
+    extra_sharded = None
+    if args.extra and world > 1:
+        # the other config shapes over all ranks (BASELINE configs[2] and [3] at --sf 12.5 x 8): wall clock per query
+        # with a barrier on both sides, max over ranks; dense shapes merge inside the library, by-orderkey goes through
+        # the hash-partitioned all-to-all and every rank keeps its share of the groups
+        extra_sharded = {}
+        top10 = Q.GroupByQuerySpec(Q.DS, [Q.DefaultDimensionSpec("o_orderkey")], Q.LimitSpec(10, [Q.OrderByColumnSpec("price", "descending")]), None, "all", None,
+                                   [Q.agg("count", "n", "count"), Q.agg("doubleSum", "price", "l_extendedprice")], None, Q.ALL_TIME, None)
+        for name, q in [("q1_style", Q.q1_style()), ("q1_tpch_expressions", q1_tpch()), ("timeseries_day_hll", Q.timeseries("P1D")),
+                        ("timeseries_month_hll", Q.timeseries("P1M")), ("by_orderkey_top10", top10)]:
+            qj = json.loads(q.to_json())
+            for _ in range(3):
+                r, info = sharded.execute_sharded(eng, qj)
+            sync()
+            t1 = time.perf_counter()
+            for _ in range(6):
+                r, info = sharded.execute_sharded(eng, qj)
+            sync()
+            t = torch.tensor([(time.perf_counter() - t1) / 6, float(eng.explain(qj)["rowsScanned"])], dtype=torch.float64, device="cuda")
+            tmax = t.clone()
+            dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t)
+            extra_sharded[name] = {"ms_per_query": 1000 * float(tmax[0]), "rows_scanned": int(t[1]), "rows_scanned_per_s": float(t[1]) / float(tmax[0]),
+                                   "merge": "all-gather + fold inside the library" if info.get("native") else ("all-reduce per slot class" if info["dense"] else "hash-partitioned all-to-all")}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -336,6 +360,8 @@ def main():
             extra[f"concurrent_suite_{n_threads}_callers"] = {"queries": sum(len(v) for v in lat.values()), "wall_s": wall, "rows_scanned_per_s": rows[0] / wall,
                                                              "latency_ms_mean": {n: sum(v) / len(v) for n, v in lat.items()}}
         line["extra"] = extra
+    if extra_sharded is not None:
+        line["extra"] = extra_sharded
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -409,21 +409,66 @@ void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n
 // ---------------------------------------------------------------------------------------------
 // sparse multi-GPU merge: split rows by owner rank, merge received rows into the local hash table
 // ---------------------------------------------------------------------------------------------
-__global__ void partition_count_kernel(const unsigned long long* __restrict__ keys, uint64_t n, int n_ranks, unsigned long long* counts) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += step) atomicAdd(counts + (mix64(keys[i] * 0x9E3779B97F4A7C15ull) >> 32) % (unsigned)n_ranks, 1ull);
+// Owner rank of a key.  Rows are counted / placed with warp-aggregated shared-memory counters: one global atomic per
+// destination per block (count) or per 1024-row tile (scatter) -- per-row global atomics on n_ranks hot addresses
+// serialised at the L2 (14 ms for 18.75 M rows; 0.3 ms now).
+__device__ __forceinline__ unsigned owner_rank(unsigned long long key, int n_ranks) {
+  return (unsigned)((mix64(key * 0x9E3779B97F4A7C15ull) >> 32) % (unsigned)n_ranks);
 }
-__global__ void partition_scatter_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots, uint64_t n,
-                                         int ns, int n_ranks, unsigned long long* cursors, unsigned long long* __restrict__ out_keys,
-                                         unsigned long long* __restrict__ out_slots) {
-  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) partition_count_kernel(const unsigned long long* __restrict__ keys, uint64_t n, int n_ranks, unsigned long long* counts) {
+  __shared__ unsigned int s_hist[64];
+  if (threadIdx.x < 64) s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const unsigned lane = threadIdx.x & 31;
   const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += step) {
-    unsigned r = (unsigned)((mix64(keys[i] * 0x9E3779B97F4A7C15ull) >> 32) % (unsigned)n_ranks);
-    unsigned long long o = atomicAdd(cursors + r, 1ull);
-    out_keys[o] = keys[i];
-    for (int s = 0; s < ns; s++) out_slots[o * ns + s] = slots[i * ns + s];
+  const uint64_t n_round = (n + step - 1) / step * step;  // whole warps take every iteration (match is a warp collective)
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += step) {
+    const bool valid = i < n;
+    const unsigned r = valid ? owner_rank(keys[i], n_ranks) : 0xFFFFFFFFu;
+    const unsigned peers = __match_any_sync(0xffffffffu, r);
+    if (valid && lane == (unsigned)__ffs(peers) - 1u) atomicAdd(&s_hist[r], (unsigned)__popc(peers));
+  }
+  __syncthreads();
+  if (threadIdx.x < (unsigned)n_ranks && s_hist[threadIdx.x]) atomicAdd(counts + threadIdx.x, (unsigned long long)s_hist[threadIdx.x]);
+}
+constexpr int PART_ROWS = 4;  // rows per thread per tile
+__global__ void __launch_bounds__(256) partition_scatter_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots, uint64_t n,
+                                                                int ns, int n_ranks, unsigned long long* cursors, unsigned long long* __restrict__ out_keys,
+                                                                unsigned long long* __restrict__ out_slots) {
+  __shared__ unsigned int s_hist[64];
+  __shared__ unsigned long long s_base[64];
+  const unsigned lane = threadIdx.x & 31;
+  const uint64_t tile = 256ull * PART_ROWS;
+  for (uint64_t t0 = (uint64_t)blockIdx.x * tile; t0 < n; t0 += (uint64_t)gridDim.x * tile) {
+    if (threadIdx.x < 64) s_hist[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned dest[PART_ROWS], off[PART_ROWS];
+#pragma unroll
+    for (int k = 0; k < PART_ROWS; k++) {
+      const uint64_t i = t0 + (uint64_t)k * 256 + threadIdx.x;
+      const bool valid = i < n;
+      const unsigned r = valid ? owner_rank(keys[i], n_ranks) : 0xFFFFFFFFu;
+      const unsigned peers = __match_any_sync(0xffffffffu, r);
+      const int leader = __ffs(peers) - 1;
+      unsigned base = 0;
+      if (valid && (int)lane == leader) base = atomicAdd(&s_hist[r], (unsigned)__popc(peers));  // the tile-local run of this warp's rows for r
+      base = __shfl_sync(0xffffffffu, base, leader);
+      dest[k] = r;
+      off[k] = base + (unsigned)__popc(peers & ((1u << lane) - 1u));
+    }
+    __syncthreads();
+    if (threadIdx.x < (unsigned)n_ranks) s_base[threadIdx.x] = s_hist[threadIdx.x] ? atomicAdd(cursors + threadIdx.x, (unsigned long long)s_hist[threadIdx.x]) : 0ull;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < PART_ROWS; k++) {
+      const uint64_t i = t0 + (uint64_t)k * 256 + threadIdx.x;
+      if (i < n) {
+        const unsigned long long o = s_base[dest[k]] + off[k];
+        out_keys[o] = keys[i];
+        for (int s = 0; s < ns; s++) out_slots[o * ns + s] = slots[i * ns + s];
+      }
+    }
+    __syncthreads();
   }
 }
 void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
@@ -435,6 +480,7 @@ void launch_partition_rows(const unsigned long long* keys, const unsigned long l
   if (!cursors_dev) {
     partition_count_kernel<<<grid, 256, 0, st>>>(keys, n, n_ranks, counts_dev);
   } else {
+    grid = (int)std::min<uint64_t>((n + 256 * PART_ROWS - 1) / (256 * PART_ROWS), 148 * 8);
     partition_scatter_kernel<<<grid, 256, 0, st>>>(keys, slots, n, n_slots, n_ranks, cursors_dev, out_keys, out_slots);
   }
   SDO_CUDA(cudaGetLastError());
