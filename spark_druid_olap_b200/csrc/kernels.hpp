@@ -138,7 +138,7 @@ struct ScanParams {
   const DevSpan* spans;  // n_spans + 1 entries (sentinel carries unit_begin = n_units)
   uint32_t n_spans;
   uint32_t n_units;
-  uint32_t units_per_chunk;
+  uint32_t units_per_chunk;     // block-ticket variant only (SDO_WARP_TICKETS 0)
   uint32_t n_cols;
   const void* const* segptr;  // [segment][n_cols] column base pointers
   int32_t n_leaves, n_ops;
@@ -156,7 +156,7 @@ struct ScanParams {
   uint64_t n_keys;  // dense key-space size (LANE / BLOCK / GLOBAL)
   int32_t slot_op[MAX_SLOTS];
   uint64_t slot_init[MAX_SLOTS];
-  unsigned long long* table;    // LANE: partials [grid][n_keys*n_slots]; BLOCK/GLOBAL: [n_keys*n_slots]; HASH: [cap*n_slots]
+  unsigned long long* table;    // LANE: partials [grid][n_keys*n_slots]; BLOCK/GLOBAL/SPAN: [n_keys*n_slots]; HASH: [cap*hstride]
   uint8_t* hll;                 // [n_keys or cap][n_hll][512]
   // HASH: one bucket = hstride words: [key | slot 0 .. slot n_slots-1 | padding]; key and aggregates of a group share a
   // 32-byte sector (hstride is a power of two), so claiming the bucket and updating it touch one sector

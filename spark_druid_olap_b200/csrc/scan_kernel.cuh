@@ -15,9 +15,10 @@
 // come from ScanParams, so one compiled shape serves every query of that shape.
 //
 // Layout of the work:
-//   * persistent grid; blocks pull chunks of units from an atomic ticket; 1 unit = 4096 rows =
-//     256 threads x 4 vectors x 4 consecutive rows, the vectors 1024 rows apart so that every load
-//     instruction of a warp is fully coalesced; a unit never crosses a span, a span never a segment;
+//   * persistent grid; every warp draws its own tickets (512 .. 4096 rows, 16 interleaved counters) and walks them in
+//     passes of 512 rows = 32 lanes x 4 vectors x 4 consecutive rows, the vectors 128 rows apart so that every load
+//     instruction of a warp is fully coalesced; no block-wide barrier in the main loop.  Rows are counted in units of
+//     4096; a unit never crosses a span, a span never a segment;
 //   * a thread's 4 consecutive rows make every column load a natural vector: 1-byte ids -> 32-bit
 //     load, 2-byte -> 64-bit, 4-byte -> 128-bit, 8-byte metric -> two 128-bit loads = one 32-byte DRAM
 //     sector, skipped entirely when none of the 4 rows survives the filter;
@@ -27,8 +28,9 @@
 //     scalar loads (the aggregate path runs max-popcount times per warp instead of 16 times with most
 //     lanes idle); otherwise vector by vector, all 32 lanes together, and a warp whose surviving rows
 //     share one key folds them with shuffles into one atomic per aggregate;
-//   * aggregation: LANE lane-private shared-memory accumulators (no atomics, fixed reduction order),
-//     BLOCK block-shared shared-memory table, GLOBAL direct-indexed HBM table, HASH open addressing.
+//   * aggregation: LANE lane-private shared-memory accumulators (no atomics, fixed reduction order), SPAN the same for
+//     the warp's current time bucket only (queries without grouping dimension), BLOCK block-shared replicated
+//     shared-memory table, GLOBAL direct-indexed HBM table, HASH open addressing (key and slots in one bucket).
 #pragma once
 
 #include "kernels.hpp"
