@@ -82,6 +82,7 @@ Engine::~Engine() {
       if (c->pinned_in) cudaFreeHost(c->pinned_in);
       if (c->pinned_out) cudaFreeHost(c->pinned_out);
       if (c->counters) cudaFree(c->counters);
+      if (c->scratch) cudaFree(c->scratch);
       delete c;
     }
   }
@@ -100,9 +101,18 @@ QueryCtx* Engine::acquire_ctx() {
   SDO_CUDA(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   for (auto& e : c->ev) SDO_CUDA(cudaEventCreate(&e));
   SDO_CUDA(cudaMalloc((void**)&c->counters, COUNTER_BYTES));
+  SDO_CUDA(cudaMemset(c->counters, 0, COUNTER_BYTES));
+  c->scratch_bytes = 2u << 20;
+  SDO_CUDA(cudaMalloc((void**)&c->scratch, c->scratch_bytes));
   ensure_pinned(&c->pinned_in, &c->pinned_in_bytes, 1 << 20);
   ensure_pinned(&c->pinned_out, &c->pinned_out_bytes, 4 << 20);
   return c;
+}
+void* Engine::take_scratch(QueryCtx* c, size_t bytes) {
+  const size_t at = round_up(c->scratch_used, 256);
+  if (at + bytes > c->scratch_bytes) return nullptr;
+  c->scratch_used = at + bytes;
+  return c->scratch + at;
 }
 void Engine::release_ctx(QueryCtx* c) {
   std::lock_guard<std::mutex> lk(ctx_mu_);
@@ -217,9 +227,25 @@ void Engine::prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st) {
       off_remap[i] = off;
       off = round_up(off + scan_dims[i]->remap.size() * 4, 16);
     }
+  // small dense tables ride along: their initial image (slot identities, zeroed registers) is part of the blob, so the
+  // scan needs neither an allocation nor a fill kernel before it
+  const uint64_t cells_pre = plan.n_keys * (uint64_t)plan.n_slots;
+  const size_t tb_pre = round_up(std::max<uint64_t>(cells_pre, 1) * 8, 256);
+  const size_t hb_pre = plan.n_hll ? (size_t)plan.n_keys * plan.n_hll * HLL_M : 0;
+  size_t off_table = 0;
+  const bool preinit = plan.strategy != STRAT_HASH && plan.n_keys <= 4096 && tb_pre + hb_pre <= 16 * 1024;
+  if (preinit) {
+    off_table = round_up(off, 256);
+    off = off_table + tb_pre + hb_pre;
+  }
   const size_t blob_bytes = off;
   ensure_pinned(&ctx->pinned_in, &ctx->pinned_in_bytes, blob_bytes);
   char* h = (char*)ctx->pinned_in;
+  if (preinit) {
+    unsigned long long* img = (unsigned long long*)(h + off_table);
+    for (uint64_t x = 0; x < cells_pre; x++) img[x] = plan.slot_init[x % plan.n_slots];
+    memset(h + off_table + cells_pre * 8, 0, tb_pre + hb_pre - cells_pre * 8);
+  }
   memcpy(h + off_spans, plan.spans.data(), n_spans * sizeof(DevSpan));
   DevSpan sentinel{};
   sentinel.unit_begin = plan.n_units;
@@ -244,8 +270,13 @@ void Engine::prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st) {
     if (!scan_dims[i]->remap.empty()) memcpy(h + off_remap[i], scan_dims[i]->remap.data(), scan_dims[i]->remap.size() * 4);
 
   SDO_CUDA(cudaEventRecord(ctx->ev[0], s));
-  SDO_CUDA(cudaMallocAsync(&st->blob, blob_bytes, s));
+  st->blob = take_scratch(ctx, blob_bytes);
+  if (!st->blob) SDO_CUDA(cudaMallocAsync(&st->blob, blob_bytes, s));
   SDO_CUDA(cudaMemcpyAsync(st->blob, h, blob_bytes, cudaMemcpyHostToDevice, s));
+  if (preinit) {
+    st->table_preinit = true;
+    st->table = (unsigned long long*)((char*)st->blob + off_table);
+  }
   st->h2d_bytes += blob_bytes;
 
   ScanParams& p = st->params;
@@ -281,8 +312,7 @@ void Engine::prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   p.n_hll = plan.n_hll;
   p.n_keys = plan.n_keys;
   for (int i = 0; i < plan.n_slots; i++) { p.slot_op[i] = plan.slot_op[i]; p.slot_init[i] = plan.slot_init[i]; }
-  p.counters = ctx->counters;
-  SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
+  p.counters = ctx->counters;  // zeroed when the context was created and by free_state after every query
   if (plan.rows_scanned >= (1ll << 32)) throw Unsupported("a single launch scans at most 2^32 rows per GPU");
 }
 
@@ -338,18 +368,20 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
     const size_t tb = round_up(std::max<uint64_t>(cells, 1) * 8, 256);
     const size_t hb = plan.n_hll ? (size_t)plan.n_keys * plan.n_hll * HLL_M : 0;
     if (hb > opt_.hll_max_bytes) throw Unsupported("cardinality aggregation needs " + std::to_string(hb) + " bytes of registers");
-    SDO_CUDA(cudaMallocAsync((void**)&st->table, tb + hb, s));
+    if (!st->table_preinit) SDO_CUDA(cudaMallocAsync((void**)&st->table, tb + hb, s));
     st->dense_blob_bytes = tb + hb;
     st->dense_table_bytes = tb;
     if (hb) {
       st->hll = (uint8_t*)st->table + tb;
       st->hll_in_table = true;
-      SDO_CUDA(cudaMemsetAsync(st->hll, 0, hb, s));
+      if (!st->table_preinit) SDO_CUDA(cudaMemsetAsync(st->hll, 0, hb, s));
       p.hll = st->hll;
     }
     if (strat != STRAT_LANE) {
-      launch_fill_slots(st->table, plan.n_keys, plan.n_slots, nullptr, p, s);
-      st->launches += 1;
+      if (!st->table_preinit) {
+        launch_fill_slots(st->table, plan.n_keys, plan.n_slots, nullptr, p, s);
+        st->launches += 1;
+      }
       p.table = st->table;
     }
   }
@@ -411,7 +443,8 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   const uint32_t n_chunks = (uint32_t)((((uint64_t)plan.n_units << (12 - p.ticket_shift)) + 7) / 8);
   grid = (int)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid, n_chunks));
   if (strat == STRAT_LANE) {
-    SDO_CUDA(cudaMallocAsync((void**)&st->partials, (size_t)grid * std::max<uint64_t>(cells, 1) * 8, s));
+    st->partials = (unsigned long long*)take_scratch(ctx, (size_t)grid * std::max<uint64_t>(cells, 1) * 8);
+    if (!st->partials) SDO_CUDA(cudaMallocAsync((void**)&st->partials, (size_t)grid * std::max<uint64_t>(cells, 1) * 8, s));
     p.table = st->partials;
   }
   SDO_CUDA(cudaEventRecord(ctx->ev[1], s));
@@ -465,7 +498,11 @@ void Engine::free_state(QueryCtx* ctx, ScanState* st) {
   cudaStream_t s = ctx->stream;
   void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll_in_table ? nullptr : (void*)st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll, st->hll_stats};
   for (void* p : ptrs)
-    if (p) cudaFreeAsync(p, s);
+    if (p && !((char*)p >= ctx->scratch && (char*)p < ctx->scratch + ctx->scratch_bytes)) cudaFreeAsync(p, s);
+  ctx->scratch_used = 0;
+  // the next query of this context finds its ticket counters zeroed (off its critical path)
+  cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s);
+  st->table_preinit = false;
   st->blob = nullptr; st->table = nullptr; st->hkeys = nullptr; st->hll = nullptr; st->partials = nullptr;
   st->rows_keys = nullptr; st->rows_slots = nullptr; st->rows_hll = nullptr; st->hll_stats = nullptr;
 }

@@ -67,7 +67,11 @@ struct QueryCtx {
   size_t pinned_in_bytes = 0;
   void* pinned_out = nullptr;
   size_t pinned_out_bytes = 0;
-  unsigned int* counters = nullptr;  // device: [0] chunk ticket [1] overflow; +8 bytes: u64 compaction counter
+  unsigned int* counters = nullptr;  // device: [0] chunk ticket [1] overflow; +8 bytes: u64 compaction counter; zero between queries
+  // Device scratch of the context for a query's small buffers (plan blob, small dense table, lane partials): every
+  // stream-ordered allocation saved before the scan launch is a few microseconds of a 100-microsecond query.
+  char* scratch = nullptr;
+  size_t scratch_bytes = 0, scratch_used = 0;
 };
 
 // device state of a finished scan (before finalisation / merging)
@@ -93,6 +97,7 @@ struct ScanState {
   unsigned long long* rows_keys = nullptr;
   unsigned long long* rows_slots = nullptr;
   uint8_t* rows_hll = nullptr;
+  bool table_preinit = false;     // small dense table: lives in the context scratch, initial image uploaded with the plan blob
   bool merged = false;            // the table may hold other ranks' groups too: local row counts no longer bound it
   double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
@@ -152,6 +157,7 @@ class Engine {
   void ensure_pinned(void** p, size_t* cur, size_t need);
   void check_cancel(const std::string& qid);
   void prepare_params(QueryCtx* ctx, const Plan& plan, ScanState* st);
+  void* take_scratch(QueryCtx* ctx, size_t bytes);  // nullptr when it does not fit
   void run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st);
   Result* execute_select(const QuerySpec& spec, double t_start_ms);
   // search_out (optional): a search query has no plan of its own -- its spec is handed back and nullptr returned
