@@ -1562,7 +1562,9 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root) {
     run_scan(ctx, *plan, &st);
     st.merged = true;
     if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
-    SDO_CUDA(cudaMallocAsync(&gathered, blob * comm_world_, s));
+    gathered = take_scratch(ctx, blob * comm_world_);
+    const bool gathered_in_scratch = gathered != nullptr;
+    if (!gathered) SDO_CUDA(cudaMallocAsync(&gathered, blob * comm_world_, s));
     {
       std::lock_guard<std::mutex> g(comm_mu_);
       nccl_all_gather_bytes(comm_, st.table, gathered, blob, s);
@@ -1571,17 +1573,17 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root) {
       launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)plan->n_slots,
                             plan->n_slots, st.params, st.table, s);
       st.launches += 1;
-      SDO_CUDA(cudaFreeAsync(gathered, s));
+      if (!gathered_in_scratch) SDO_CUDA(cudaFreeAsync(gathered, s));
       gathered = nullptr;
       r = finalize(ctx, *plan, &st, t0);
     } else {
-      SDO_CUDA(cudaFreeAsync(gathered, s));
+      if (!gathered_in_scratch) SDO_CUDA(cudaFreeAsync(gathered, s));
       gathered = nullptr;
       SDO_CUDA(cudaStreamSynchronize(s));
     }
   } catch (...) {
     cudaStreamSynchronize(ctx->stream);
-    if (gathered) cudaFreeAsync(gathered, ctx->stream);
+    if (gathered && !((char*)gathered >= ctx->scratch && (char*)gathered < ctx->scratch + ctx->scratch_bytes)) cudaFreeAsync(gathered, ctx->stream);
     free_state(ctx, &st);
     release_ctx(ctx);
     throw;
