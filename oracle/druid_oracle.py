@@ -158,6 +158,32 @@ def _tz_ms(tz):
     return (1 if m.group(1) == "+" else -1) * (int(m.group(2)) * 3600000 + int(m.group(3)) * 60000)
 
 
+def _zone(tz):
+    """A fixed offset in ms, or a zoneinfo.ZoneInfo for a region id (the system's zone database, read by Python)."""
+    try:
+        return _tz_ms(tz)
+    except NotImplementedError:
+        import zoneinfo
+        return zoneinfo.ZoneInfo(tz)
+
+
+def _zoff(z, ms):
+    """Offset of zone z (ms east of UTC) at the instant ms."""
+    if isinstance(z, int):
+        return z
+    d = _dt.datetime(1970, 1, 1, tzinfo=_dt.timezone.utc) + _dt.timedelta(milliseconds=int(ms))
+    return int(d.astimezone(z).utcoffset().total_seconds() * 1000)
+
+
+def _local_to_utc(z, local_ms):
+    """Wall-clock ms in zone z -> UTC ms; ambiguous times mean their first occurrence, skipped ones the offset before
+    the change (PEP 495 fold = 0, as java.time / Joda's lenient conversion)."""
+    if isinstance(z, int):
+        return local_ms - z
+    naive = _EPOCH + _dt.timedelta(milliseconds=int(local_ms))
+    return local_ms - int(naive.replace(tzinfo=z).utcoffset().total_seconds() * 1000)
+
+
 def _dt_of(ms, tz_ms=0):
     return _EPOCH + _dt.timedelta(milliseconds=int(ms) + tz_ms)
 
@@ -258,21 +284,30 @@ def bucket_fn(gran):
         return lambda x: x - (x - org) % dur
     if t == "period":
         months, fixed = _period(gran["period"])
-        tz = _tz_ms(gran.get("timeZone"))
+        tz = _zone(gran.get("timeZone"))
         if months:
             return _month_bucket(months, tz)
-        org = parse_instant(gran["origin"]) if gran.get("origin") else ((-3 * 86400000 if fixed % (7 * 86400000) == 0 else 0) - tz)
-        return lambda x: x - (x - org) % fixed
+        if gran.get("origin"):
+            org = parse_instant(gran["origin"])
+            return lambda x: x - (x - org) % fixed
+        if fixed < 86400000:
+            return lambda x: x - (x + _zoff(tz, x)) % fixed
+        lorg = -3 * 86400000 if fixed % (7 * 86400000) == 0 else 0
+
+        def local_bucket(x):
+            loc = x + _zoff(tz, x)
+            return _local_to_utc(tz, loc - (loc - lorg) % fixed)
+        return local_bucket
     raise ValueError(gran)
 
 
 def _month_bucket(months, tz):
     def f(t):
-        d = _dt_of(t, tz)
+        d = _dt_of(t, _zoff(tz, t))
         idx = d.year * 12 + d.month - 1
         idx -= idx % months
         s = _dt.datetime(idx // 12, idx % 12 + 1, 1)
-        return int((s - _EPOCH).total_seconds()) * 1000 - tz
+        return _local_to_utc(tz, int((s - _EPOCH).total_seconds()) * 1000)
     return f
 
 
@@ -421,7 +456,7 @@ def extract_value(fn, v):
     """Druid dimension extraction functions (DruidQuerySpec.scala:45-106) on one value; '' is null."""
     t = fn["type"]
     if t == "timeFormat":
-        return "" if v == "" else joda_format(fn.get("format", "yyyy-MM-dd'T'HH:mm:ss.SSS'Z'"), parse_instant(v), _tz_ms(fn.get("timeZone")))
+        return "" if v == "" else joda_format(fn.get("format", "yyyy-MM-dd'T'HH:mm:ss.SSS'Z'"), parse_instant(v), _zoff(_zone(fn.get("timeZone")), parse_instant(v)))
     if t == "time":
         if v == "":
             return ""
@@ -641,8 +676,8 @@ def execute(tbl, q, return_registers=False):
         elif d.get("type", "default") == "extraction":
             fn = d["extractionFn"]
             assert fn["type"] == "timeFormat"
-            tz = _tz_ms(fn.get("timeZone"))
-            strs = [joda_format(fn["format"], int(t), tz) for t in ut]
+            tz = _zone(fn.get("timeZone"))
+            strs = [joda_format(fn["format"], int(t), _zoff(tz, int(t))) for t in ut]
             us = sorted(set(strs), key=lambda s: s.encode("utf-8"))
             rank = {s: i for i, s in enumerate(us)}
             key_cols.append(np.array([rank[s] for s in strs], dtype=np.int64)[tinv])

@@ -396,10 +396,10 @@ bool parse_by_pattern(const std::string& pat, const char* v, size_t nv, int64_t*
 // the value a dimension's extraction function yields for one dictionary value ("" = null)
 struct Extractor {
   const ExtractionFn& fn;
-  int64_t tz = 0;
+  Zone zone;
   std::regex re;
   explicit Extractor(const ExtractionFn& f) : fn(f) {
-    if (fn.kind == ExtractionFn::TimeFormat) tz = tz_offset_ms(fn.time_zone);
+    if (fn.kind == ExtractionFn::TimeFormat) zone = load_zone(fn.time_zone);
     if (fn.kind == ExtractionFn::Regex) {
       try { re = std::regex(fn.expr, std::regex::ECMAScript | std::regex::optimize); } catch (const std::regex_error&) { throw Invalid("bad regex '" + fn.expr + "'"); }
     }
@@ -411,7 +411,7 @@ struct Extractor {
         if (!n) return std::string();
         int64_t ms;
         try { ms = parse_iso_instant(std::string(p, n)); } catch (const Invalid&) { throw Invalid("timeFormat extraction: dimension value '" + std::string(p, n) + "' is not an ISO-8601 instant"); }
-        return joda_format(fn.format, ms, tz);
+        return joda_format(fn.format, ms, zone.offset_at(ms));
       }
       case ExtractionFn::TimeParse: {
         int64_t ms;
@@ -496,7 +496,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   // ---- dimensions --------------------------------------------------------------------------
   // AggregateTransform.scala:48-96: grouping expressions become DefaultDimensionSpec, or
   // ExtractionDimensionSpec(__time, timeFormat) for date-part expressions on the time column.
-  std::vector<std::pair<std::string, int64_t>> time_fmts;  // (format, tz offset)
+  std::vector<std::pair<std::string, Zone>> time_fmts;  // (format, zone)
   for (auto& d : spec.dimensions) {
     PlanDim pd;
     pd.output_name = d.output_name;
@@ -514,7 +514,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
     if (d.fn.kind == ExtractionFn::TimeFormat) {
       pd.is_time = true;
       pd.time_fmt = (int)time_fmts.size();
-      time_fmts.emplace_back(d.fn.format, tz_offset_ms(d.fn.time_zone));
+      time_fmts.emplace_back(d.fn.format, load_zone(d.fn.time_zone));
     } else {
       if (d.dimension == "__time") throw Unsupported("grouping on raw __time; use a granularity or a timeFormat extraction");
       pd.ds_dim = ds.dim_index(d.dimension);
@@ -699,8 +699,6 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
   // ---- segments, spans, time keys ---------------------------------------------------------------
   // QueryIntervals.scala:40-130 (half-open ms intervals), DruidMetadataCache.scala:94,131-143 (overlap).
   std::vector<Interval> ivs = spec.intervals.empty() ? std::vector<Interval>{{INT64_MIN / 2, INT64_MAX / 2}} : normalise(spec.intervals);
-  const int64_t bucket_tz = spec.granularity.tz_ms;
-  (void)bucket_tz;
   struct RawSpan { int seg; int64_t rb, re; TimeKey tk; };
   std::vector<RawSpan> raw;
   std::map<TimeKey, uint64_t> tk_ids;
@@ -731,7 +729,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
         if (i < i1) {
           int64_t t = sg.time_vals[i];
           if (plan.has_bucket) tk.bucket = bucket_start(spec.granularity, t);
-          for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second));
+          for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second.offset_at(t)));
         }
         if (i == i0) { cur = tk; continue; }
         if (i == i1 || !(tk == cur)) {
@@ -763,7 +761,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
       if (!in) continue;
       TimeKey tk;
       if (plan.has_bucket) tk.bucket = bucket_start(spec.granularity, t);
-      for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second));
+      for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second.offset_at(t)));
       tk_ids[tk] = 0;
     }
   }

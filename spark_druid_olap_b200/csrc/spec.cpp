@@ -329,7 +329,7 @@ Granularity parse_granularity(const Json* j) {
   if (t == "period") {
     g.kind = Granularity::Period;  // PeriodGranularitySpec, DruidQuerySpec.scala:144-150
     parse_period(req_str(*j, "period", "period granularity"), &g.months, &g.period_ms);
-    g.tz_ms = tz_offset_ms(j->get_str("timeZone", "UTC"));
+    g.zone = load_zone(j->get_str("timeZone", "UTC"));
     if (j->has("origin")) { g.origin_ms = parse_iso_instant(j->get_str("origin")); g.has_origin = true; }
     return g;
   }

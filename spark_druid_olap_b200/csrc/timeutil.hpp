@@ -6,11 +6,16 @@
 // Time zones: UTC and fixed offsets only (the reference's tests pin UTC,
 // AbstractTest.scala:83-88); a named zone is rejected as unsupported.
 #pragma once
+#include <algorithm>
+#include <cctype>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <stdexcept>
 #include <string>
+#include <vector>
 
 namespace sdo {
 
@@ -81,7 +86,98 @@ inline int64_t tz_offset_ms(const std::string& tz_in) {
       return sign * (h * 3600000ll + m * 60000ll);
     }
   }
-  throw Unsupported("time zone '" + tz_in + "' is not supported (UTC and fixed offsets only)");
+  throw Unsupported("time zone '" + tz_in + "' is not a fixed offset");
+}
+
+// ---- time zones -----------------------------------------------------------------------------------------------------
+// A zone is a fixed offset ("UTC", "+05:30") or a named region ("America/Los_Angeles": what the planner sends when
+// spark.sparklinedata.tz.id / the JVM default is one, SQD/DruidPlanner.scala:73-76).  Named zones come from the system's
+// TZif files (/usr/share/zoneinfo, or $TZDIR): the 64-bit transition table of the version-2+ block; instants past the last
+// listed transition keep its offset (the installed files list transitions to 2037).
+struct ZoneRules {
+  std::vector<int64_t> at_ms;      // transition instants (UTC ms), ascending
+  std::vector<int64_t> offset_ms;  // offset_ms[i] applies from at_ms[i-1] (or forever before) up to at_ms[i]; size = at_ms.size() + 1
+};
+struct Zone {
+  int64_t fixed_ms = 0;
+  std::shared_ptr<const ZoneRules> rules;  // null = fixed offset
+  int64_t offset_at(int64_t utc_ms) const {
+    if (!rules) return fixed_ms;
+    const size_t k = (size_t)(std::upper_bound(rules->at_ms.begin(), rules->at_ms.end(), utc_ms) - rules->at_ms.begin());
+    return rules->offset_ms[k];
+  }
+  // Local wall-clock ms -> UTC ms.  A time that occurs twice (clocks set back) means its first occurrence, one that does
+  // not exist (clocks set forward) is read with the offset in force before the change -- what java.time / Joda's lenient
+  // conversion and Python's fold = 0 do.
+  int64_t local_to_utc(int64_t local_ms) const {
+    if (!rules) return local_ms - fixed_ms;
+    const int64_t before = offset_at(local_ms - 36 * 3600000ll), after = offset_at(local_ms + 36 * 3600000ll);
+    const int64_t u1 = local_ms - before, u2 = local_ms - after;
+    const bool ok1 = offset_at(u1) == before, ok2 = offset_at(u2) == after;
+    if (ok1 && ok2) return std::min(u1, u2);
+    if (ok1) return u1;
+    if (ok2) return u2;
+    return u1;
+  }
+};
+
+inline std::shared_ptr<const ZoneRules> load_tzif(const std::string& id) {
+  for (char c : id)
+    if (!(isalnum((unsigned char)c) || c == '_' || c == '-' || c == '+' || c == '/')) throw Invalid("bad time zone id '" + id + "'");
+  if (id.find("..") != std::string::npos || id.empty() || id[0] == '/') throw Invalid("bad time zone id '" + id + "'");
+  const char* dir = getenv("TZDIR");
+  const std::string path = std::string(dir && *dir ? dir : "/usr/share/zoneinfo") + "/" + id;
+  FILE* f = fopen(path.c_str(), "rb");
+  if (!f) throw Unsupported("time zone '" + id + "' is not known (no " + path + ")");
+  std::vector<unsigned char> b;
+  unsigned char buf[4096];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof buf, f)) > 0) b.insert(b.end(), buf, buf + n);
+  fclose(f);
+  auto be32 = [&](size_t o) { return (int64_t)(int32_t)((uint32_t)b[o] << 24 | (uint32_t)b[o + 1] << 16 | (uint32_t)b[o + 2] << 8 | (uint32_t)b[o + 3]); };
+  auto be64 = [&](size_t o) {
+    uint64_t v = 0;
+    for (int k = 0; k < 8; k++) v = v << 8 | b[o + k];
+    return (int64_t)v;
+  };
+  auto bad = [&]() -> Invalid { return Invalid("time zone file '" + path + "' is not a version 2+ TZif file"); };
+  if (b.size() < 44 || memcmp(b.data(), "TZif", 4) != 0 || b[4] < '2') throw bad();
+  // skip the version-1 block: header (44) + its data sized with 4-byte transition times
+  size_t o = 0;
+  const int64_t isut1 = be32(20), isstd1 = be32(24), leap1 = be32(28), time1 = be32(32), type1 = be32(36), char1 = be32(40);
+  o = 44 + (size_t)(time1 * 4 + time1 + type1 * 6 + char1 + leap1 * 8 + isstd1 + isut1);
+  if (b.size() < o + 44 || memcmp(b.data() + o, "TZif", 4) != 0) throw bad();
+  const int64_t timecnt = be32(o + 32), typecnt = be32(o + 36);
+  o += 44;
+  if (typecnt < 1 || b.size() < o + (size_t)(timecnt * 9 + typecnt * 6)) throw bad();
+  auto rules = std::make_shared<ZoneRules>();
+  std::vector<int64_t> type_off((size_t)typecnt);
+  const size_t o_idx = o + (size_t)timecnt * 8, o_types = o_idx + (size_t)timecnt;
+  for (int64_t t = 0; t < typecnt; t++) type_off[(size_t)t] = be32(o_types + (size_t)t * 6) * 1000;
+  // before the first transition: the first standard-time type (RFC 8536 3.2), i.e. the first type without the DST flag
+  size_t first = 0;
+  for (int64_t t = 0; t < typecnt; t++)
+    if (b[o_types + (size_t)t * 6 + 4] == 0) { first = (size_t)t; break; }
+  rules->offset_ms.push_back(type_off[first]);
+  for (int64_t k = 0; k < timecnt; k++) {
+    const unsigned idx = b[o_idx + (size_t)k];
+    if ((int64_t)idx >= typecnt) throw bad();
+    rules->at_ms.push_back(be64(o + (size_t)k * 8) * 1000);
+    rules->offset_ms.push_back(type_off[idx]);
+  }
+  return rules;
+}
+
+// any zone id: a fixed offset, else a region of the system's zone database
+inline Zone load_zone(const std::string& id) {
+  Zone z;
+  try {
+    z.fixed_ms = tz_offset_ms(id);
+    return z;
+  } catch (const Unsupported&) {
+  }
+  z.rules = load_tzif(id);
+  return z;
 }
 
 // ISO-8601 instant -> epoch ms.  Accepts yyyy-MM-dd['T'HH:mm[:ss[.SSS]]][Z|±HH:mm|±HHmm];
@@ -155,7 +251,7 @@ struct Granularity {
   int64_t origin_ms = 0;    // Duration / Period origin
   int months = 0;           // Period: calendar part (years*12 + months)
   int64_t period_ms = 0;    // Period: fixed part (weeks/days/hours/minutes/seconds)
-  int64_t tz_ms = 0;
+  Zone zone;                // Period: buckets are aligned in this zone's local time
   bool has_origin = false;
 };
 
@@ -220,22 +316,26 @@ inline int64_t bucket_start(const Granularity& g, int64_t t) {
     case Granularity::None: return t;
     case Granularity::Duration: return t - floormod(t - g.origin_ms, g.duration_ms);
     case Granularity::Period: {
+      const int64_t off = g.zone.offset_at(t);
       if (g.months) {
-        Civil c = civil_from_ms(t, g.tz_ms);
+        Civil c = civil_from_ms(t, off);
         int64_t midx = c.year * 12 + (c.month - 1);
         int64_t o = 0;
         if (g.has_origin) {
-          Civil oc = civil_from_ms(g.origin_ms, g.tz_ms);
+          Civil oc = civil_from_ms(g.origin_ms, g.zone.offset_at(g.origin_ms));
           o = oc.year * 12 + (oc.month - 1);
           // an origin off a month boundary is not supported (Druid allows it; no caller uses it)
           if (oc.day != 1 || oc.hour || oc.minute || oc.second || oc.millis) throw Unsupported("period origin must be a month start");
         }
         int64_t b = midx - floormod(midx - o, g.months);
-        return days_from_civil(floordiv(b, 12), (int)floormod(b, 12) + 1, 1) * MS_DAY - g.tz_ms;
+        return g.zone.local_to_utc(days_from_civil(floordiv(b, 12), (int)floormod(b, 12) + 1, 1) * MS_DAY);
       }
       // Fixed periods: aligned in local time.  Weeks start on Monday (ISO, as Joda).
-      int64_t origin = g.has_origin ? g.origin_ms : (g.period_ms % (7 * MS_DAY) == 0 ? -3 * MS_DAY - g.tz_ms : -g.tz_ms);
-      return t - floormod(t - origin, g.period_ms);
+      if (g.has_origin) return t - floormod(t - g.origin_ms, g.period_ms);
+      if (g.period_ms < MS_DAY) return t - floormod(t + off, g.period_ms);  // sub-day buckets: offsets are multiples of them in practice
+      const int64_t local = t + off;
+      const int64_t local_origin = g.period_ms % (7 * MS_DAY) == 0 ? -3 * MS_DAY : 0;
+      return g.zone.local_to_utc(local - floormod(local - local_origin, g.period_ms));
     }
   }
   return t;

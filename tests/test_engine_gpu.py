@@ -173,6 +173,24 @@ def test_timeseries_strategies(loaded, shape, strategy):
         assert np.array_equal(res.hll[name][order], r), name
 
 
+@pytest.mark.parametrize("zone", ["America/Los_Angeles", "Europe/Berlin", "Asia/Kolkata", "-08:00"])
+def test_named_time_zones(loaded, zone):
+    """Period granularities and timeFormat extraction in zones with daylight saving (spark.sparklinedata.tz.id is the JVM
+    default zone in a deployment): bucket starts, day boundaries and formatted values against the oracle's zoneinfo."""
+    eng, tbl = loaded
+    for period in ("P1D", "P1M", "P1W", "PT6H"):
+        q = json.loads(Q.timeseries(period, True, None, ["1995-02-01T00:00:00.000Z/1996-12-01T00:00:00.000Z"]).to_json())
+        q["granularity"]["timeZone"] = zone
+        res = eng.execute(q)
+        H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, q), what=f"{period} {zone}")
+    q = json.loads(Q.q7().to_json())
+    q["dimensions"][2]["extractionFn"]["timeZone"] = zone
+    q["dimensions"][2]["extractionFn"]["format"] = "yyyy-MM-dd EEE"
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, q), what=f"timeFormat {zone}")
+    q = json.loads(Q.with_extraction(Q.ExtractionDimensionSpec("o_orderdate", "d", Q.TimeFormatExtractionFunctionSpec("yyyy-MM-dd HH", zone))).to_json())
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), orc.execute(tbl, q), what=f"dimension timeFormat {zone}")
+
+
 def test_timeseries_simple_granularity_strings(loaded):
     eng, tbl = loaded
     for g in ("day", "month", "year"):

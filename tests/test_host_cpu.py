@@ -231,10 +231,18 @@ def test_error_statuses(planning):
             None, Q.ALL_TIME, None))
     with pytest.raises(sdo.UnsupportedQuery):  # dimensions cannot appear in arithmetic
         eng.explain(Q.GroupByQuerySpec(Q.DS, [], None, None, "all", None, [{"type": "doubleSum", "name": "x", "expression": "l_tax * p_size"}], None, Q.ALL_TIME, None))
-    with pytest.raises(sdo.UnsupportedQuery):
-        q = json.loads(Q.q7().to_json())
-        q["dimensions"][2]["extractionFn"]["timeZone"] = "America/Los_Angeles"
-        eng.explain(q)
+    q = json.loads(Q.q7().to_json())
+    q["dimensions"][2]["extractionFn"]["timeZone"] = "America/Los_Angeles"  # region ids come from the system zone database
+    assert eng.explain(q)["timeKeys"] in (7, 8)
+    for bad_zone, exc in (("Mars/Olympus_Mons", sdo.UnsupportedQuery), ("../../etc/passwd", sdo.InvalidQuery)):
+        q["dimensions"][2]["extractionFn"]["timeZone"] = bad_zone
+        with pytest.raises(exc):
+            eng.explain(q)
+    # day buckets in a zone with daylight saving: 23- and 25-hour days still make one bucket per local day
+    ts = json.loads(Q.timeseries("P1D", True, None, ["1996-03-01T00:00:00.000Z/1996-05-01T00:00:00.000Z"]).to_json())
+    utc_keys = eng.explain(ts)["timeKeys"]
+    ts["granularity"]["timeZone"] = "America/Los_Angeles"
+    assert eng.explain(ts)["timeKeys"] in (utc_keys, utc_keys + 1)
     with pytest.raises(sdo.DruidDataSourceException) as ei:
         eng.explain(dict(json.loads(Q.q1_style().to_json()), dataSource="missing"))
     assert ei.value.status == sdo.SDO_NOT_FOUND

@@ -228,3 +228,19 @@ def test_hand_computed_search():
     assert [(r["value"], r["count"]) for r in rows] == [("red", 3), ("blue", 3)]
     rows = orc.execute(t, dict(base, query={"type": "fragment", "values": ["z", "RA"]}, filter={"type": "selector", "dimension": "k", "value": "100"}))
     assert rows == [{"dimension": "color", "value": "Zebra", "count": 1}]
+
+
+def test_named_time_zones_in_the_oracle():
+    """Region ids go through Python's zoneinfo: daylight-saving changes move month / day bucket starts and formats."""
+    la = {"type": "period", "period": "P1D", "timeZone": "America/Los_Angeles"}
+    f = orc.bucket_fn(la)
+    # 1996-04-07 02:00 PST -> 03:00 PDT: the day before starts at 08:00Z, the day after at 07:00Z
+    assert f(orc.parse_instant("1996-04-06T20:00:00Z")) == orc.parse_instant("1996-04-06T08:00:00Z")
+    assert f(orc.parse_instant("1996-04-08T06:59:59Z")) == orc.parse_instant("1996-04-07T08:00:00Z")   # still the 7th, local 23:59
+    assert f(orc.parse_instant("1996-04-08T07:00:00Z")) == orc.parse_instant("1996-04-08T07:00:00Z")
+    m = orc.bucket_fn({"type": "period", "period": "P1M", "timeZone": "Europe/Berlin"})
+    assert m(orc.parse_instant("1997-07-15T12:00:00Z")) == orc.parse_instant("1997-06-30T22:00:00Z")   # CEST = +02:00
+    assert m(orc.parse_instant("1997-01-15T12:00:00Z")) == orc.parse_instant("1996-12-31T23:00:00Z")   # CET = +01:00
+    z = orc._zone("America/Los_Angeles")
+    assert orc.joda_format("yyyy-MM-dd HH", orc.parse_instant("1995-07-01T06:30:00Z"), orc._zoff(z, orc.parse_instant("1995-07-01T06:30:00Z"))) == "1995-06-30 23"
+    assert orc._zoff(orc._zone("Asia/Kolkata"), 0) == 19800000 and orc._zone("+05:30") == 19800000
