@@ -134,6 +134,8 @@ def _execute(ct, q, threads, return_registers):
     L = _load()
     keep = []  # numpy buffers that must outlive the call
     qt = q["queryType"]
+    if qt not in ("groupBy", "timeseries", "topN"):
+        raise _Unsupported()  # search / select: the numpy oracle only
     # intervals
     ivs = q.get("intervals")
     if isinstance(ivs, dict):
