@@ -104,9 +104,9 @@ namespace sdo {
 #endif
 
 constexpr int VECS = UNIT_ROWS / (SCAN_THREADS * ROWS_PER_THREAD);  // vectors per thread per unit
-// Work distribution.  Warp tickets (default): every warp draws its own tickets of 1024 rows (a quarter unit) and walks
-// them in passes of 512 rows -- 32 lanes x 4 vectors x 4 rows, the vectors 128 rows apart -- so the main loop has no
-// block-wide barrier and warps drift apart freely.  Block tickets (SDO_WARP_TICKETS 0): the block draws chunks of two
+// Work distribution.  Warp tickets (default): every warp draws its own tickets (512 .. 4096 rows, see ticket_shift) and
+// walks them in passes of 512 rows -- 32 lanes x 4 vectors x 4 rows, the vectors 128 rows apart -- so the main loop has
+// no block-wide barrier and warps drift apart freely.  Block tickets (SDO_WARP_TICKETS 0): the block draws chunks of two
 // units and all 256 threads walk a unit together, vectors 1024 rows apart.
 #ifndef SDO_WARP_TICKETS
 #define SDO_WARP_TICKETS 1
