@@ -25,7 +25,7 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 METRIC = "tpch_flat_rows_scanned_per_s"
 UNIT = "rows/s"
 Q5T_COLUMNS = ["s_region", "o_orderdate", "s_nation", "l_extendedprice"]
-Q5T_TRAFFIC_BYTES = 278798592  # ncu --set full capture of sdo_scan_jit on SF10 Q5T (profiles/r01_ncu_q5t_jit_v2_summary.txt): 275.67 MB read + 3.13 MB written
+Q5T_TRAFFIC_BYTES = 279396352  # ncu --set full capture of sdo_scan_jit on SF10 Q5T (profiles/r01_ncu_q5t_jit_v3_summary.txt): 275.64 MB read + 3.75 MB written
 EXTRA_COLUMNS = ["c_mktsegment", "o_orderkey", "o_shippriority", "l_returnflag", "l_linestatus", "l_quantity", "l_discount", "l_tax", "o_custkey"]
 
 
