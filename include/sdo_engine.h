@@ -33,8 +33,9 @@ typedef struct sdo_partial sdo_partial;
 
 /* Status codes.  Any non-zero status maps to DruidDataSourceException on the Scala side
  * (/root/reference/src/main/scala/org/sparklinedata/druid/DruidDataSourceException.scala),
- * except SDO_UNSUPPORTED, which tells the caller to leave the plan un-rewritten (javascript,
- * spatial, search, select specs: SURVEY.md 8b "Errors"), and SDO_CANCELLED, which the caller
+ * except SDO_UNSUPPORTED, which tells the caller to leave the plan un-rewritten (spatial filters,
+ * descending select, javascript outside the expression subset: SURVEY.md 8b "Errors"), and
+ * SDO_CANCELLED, which the caller
  * swallows as DruidRDD does (DruidRDD.scala:181-186). */
 typedef enum {
   SDO_OK = 0,
@@ -114,7 +115,16 @@ int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_o
 /* ---- query --------------------------------------------------------------------------------
  * sdo_query_execute replaces QuerySpec.executeQuery (DruidQuerySpec.scala:598-599): the JSON is
  * exactly what DruidClient.executeQueryAsStream renders (client/DruidClient.scala:328-331) with
- * Utils.jsonFormat (Utils.scala:38-105).  queryType in {groupBy, timeseries, topN}. */
+ * Utils.jsonFormat (Utils.scala:38-105).  queryType in {groupBy, timeseries, topN, search, select}.
+ *   search (SearchQuerySpec, DruidQuerySpec.scala:870-927; what the planner emits for a group-by on one
+ *     dimension without aggregations): result columns dimension, value, count.
+ *   select (SelectSpec, :980-1098): one page of rows per call; result columns timestamp, segmentId,
+ *     offset, then the requested dimensions and metrics; the pagingIdentifiers for the next page are in
+ *     sdo_result_stats_json (pass them back in pagingSpec with fromNext = true).
+ *   javascript filters / extraction functions / aggregations are accepted when the function is a single
+ *     `return <expression>` (comparisons, string methods, arithmetic); nothing of it runs per row.
+ *   context keys read: queryId, skipEmptyBuckets, gpuTimeBoundary, and the test knobs gpuStrategy,
+ *     gpuJit, gpuHllPlace, gpuTicketRows; unknown keys are ignored. */
 int sdo_query_execute(sdo_engine* e, const char* query_json, size_t len, sdo_result** out);
 /* Plan only (no device work): returns a JSON description of the spans, compiled filter,
  * key layout, strategy and algorithmic bytes.  No reference counterpart beyond
