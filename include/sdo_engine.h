@@ -124,14 +124,24 @@ int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_o
  *   javascript filters / extraction functions / aggregations are accepted when the function is a single
  *     `return <expression>` (comparisons, string methods, arithmetic); nothing of it runs per row.
  *   context keys read: queryId, skipEmptyBuckets, gpuTimeBoundary, and the test knobs gpuStrategy,
- *     gpuJit, gpuHllPlace, gpuTicketRows; unknown keys are ignored. */
+ *     gpuJit, gpuHllPlace, gpuTicketRows; unknown keys are ignored.
+ *     skipEmptyBuckets defaults to TRUE here (Druid: false): the parity target is Spark running the
+ *     un-rewritten plan, which has no rows for empty buckets.  An explicit false is honoured for
+ *     timeseries queries (one row per granularity bucket between the datasource's first and last
+ *     timestamp inside the query intervals, empty ones with the aggregators' identities; at most
+ *     65536 buckets); groupBy never zero-fills, as in Druid. */
 int sdo_query_execute(sdo_engine* e, const char* query_json, size_t len, sdo_result** out);
 /* Plan only (no device work): returns a JSON description of the spans, compiled filter,
  * key layout, strategy and algorithmic bytes.  No reference counterpart beyond
  * EXPLAIN DRUID REWRITE (sparklinedata/commands/DruidMetadataCommands.scala:49). */
 int sdo_query_explain(sdo_engine* e, const char* query_json, size_t len, const char** json_out);
 /* Cancel a running query by context.queryId from another thread.  Replaces
- * CancellableHolder / TaskCancelHandler (client/DruidClient.scala:82-103, DruidRDD.scala:428-491). */
+ * CancellableHolder / TaskCancelHandler (client/DruidClient.scala:82-103, DruidRDD.scala:428-491).
+ * The query fails with SDO_CANCELLED at its next poll: before its scan is queued, or after the scan
+ * has been queued and before results are read back (a launched scan kernel is not interrupted).
+ * A cancel for an id that is not running is remembered for 5 seconds (the canceller may race ahead
+ * of the execute call) and then forgotten, and a mark dies with the query it names, so a finished
+ * query's id can be reused by a retry (DruidRDD.scala:80 reuses <queryId>-<partition>). */
 int sdo_query_cancel(sdo_engine* e, const char* query_id);
 
 /* ---- result -------------------------------------------------------------------------------
@@ -263,6 +273,8 @@ int sdo_query_execute_sharded(sdo_engine* e, const char* query_json, size_t len,
  *
  * Limits: 1 <= n_keys <= SDO_NOALLOC_MAX_KEYS and 0 <= n_rows <= SDO_NOALLOC_MAX_ROWS; anything
  * beyond is refused with SDO_INVALID and a message in sdo_last_error().
+ * `device` is made current for the duration of the call only; the calling thread's current device
+ * is the same after the call as before it.
  * First call on a device: resolves the scratch array's device address (once per device, under a
  * lock); make that first call before starting any stream capture.
  * Sharing: every call on a device uses the same array, which still holds the last call's partials.

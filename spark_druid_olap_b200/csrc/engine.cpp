@@ -40,6 +40,15 @@ double hll_estimate(const uint8_t* regs) {
   }
   return hll_estimate_from((z0 + z1) + (z2 + z3), zeros);
 }
+// true when Spark would have subtracted an empirical bias from this sketch's estimate (raw E <= 5m and linear counting
+// not chosen): the only inputs for which the value column differs from Spark's
+bool hll_needs_bias_tables(double zinv, double V) {
+  const double m = HLL_M;
+  const double E = ((0.7213 / (1.0 + 1.079 / m)) * m * m) / zinv;
+  if (E > 5.0 * m) return false;
+  if (V > 0 && m * std::log(m / V) <= 400.0) return false;
+  return true;
+}
 double hll_estimate_from(double zinv, double V) {
   const double m = HLL_M;
   const double alpha_m2 = (0.7213 / (1.0 + 1.079 / m)) * m * m;
@@ -127,18 +136,42 @@ void Engine::ensure_pinned(void** p, size_t* cur, size_t need) {
   *cur = n;
 }
 
+// Cancellation (replaces CancellableHolder / TaskCancelHandler, DruidClient.scala:82-103, DruidRDD.scala:453-481).
+// A query registers its id while it runs; cancel() marks a running id, and the mark dies with the query.  A cancel
+// that arrives for an id that is not running (the canceller can race ahead of the execute call) is kept for
+// CANCEL_KEEP_MS only, so cancelling a finished or unknown query cannot abort a later retry that reuses the id
+// (Spark task retries and speculative attempts reuse <queryId>-<partition>, DruidRDD.scala:80).  The flag is polled
+// before the scan is queued and after it has been queued (before results are read back).
+static constexpr double CANCEL_KEEP_MS = 5000.0;
 void Engine::cancel(const std::string& qid) {
   std::lock_guard<std::mutex> lk(cancel_mu_);
-  cancelled_.insert(qid);
-  if (cancelled_.size() > 4096) cancelled_.erase(cancelled_.begin());
+  const double now = now_ms();
+  for (auto it = cancelled_.begin(); it != cancelled_.end();)
+    it = (now - it->second > CANCEL_KEEP_MS && !running_.count(it->first)) ? cancelled_.erase(it) : std::next(it);
+  cancelled_[qid] = now;
 }
 void Engine::check_cancel(const std::string& qid) {
   if (qid.empty()) return;
   std::lock_guard<std::mutex> lk(cancel_mu_);
   auto it = cancelled_.find(qid);
-  if (it != cancelled_.end()) {
-    cancelled_.erase(it);
-    throw Cancelled("query '" + qid + "' was cancelled");
+  if (it == cancelled_.end()) return;
+  const bool fresh = now_ms() - it->second <= CANCEL_KEEP_MS || running_since_.count(qid) && it->second >= running_since_[qid];
+  cancelled_.erase(it);
+  if (fresh) throw Cancelled("query '" + qid + "' was cancelled");
+}
+Engine::RunningQuery::RunningQuery(Engine* e, const std::string& qid) : e_(e), qid_(qid) {
+  if (qid_.empty()) return;
+  std::lock_guard<std::mutex> lk(e_->cancel_mu_);
+  if (e_->running_[qid_]++ == 0) e_->running_since_[qid_] = now_ms();
+}
+Engine::RunningQuery::~RunningQuery() {
+  if (qid_.empty()) return;
+  std::lock_guard<std::mutex> lk(e_->cancel_mu_);
+  auto it = e_->running_.find(qid_);
+  if (it != e_->running_.end() && --it->second == 0) {
+    e_->running_.erase(it);
+    e_->running_since_.erase(qid_);
+    e_->cancelled_.erase(qid_);  // a cancel that came too late dies with the query
   }
 }
 
@@ -607,6 +640,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
 
   if (!plan.always_false) {
     const bool dense = st->strategy != STRAT_HASH && !st->rows_valid;
+    if (plan.zero_fill && !(dense && st->table_rows <= 65536)) throw Unsupported("skipEmptyBuckets = false with more than 65536 buckets");
     if (dense && st->table_rows <= 65536 && (uint64_t)st->table_rows * std::max(1, plan.n_hll) * HLL_M <= (64u << 20)) {
       // small dense table: bring it back whole and drop empty groups on the host
       const size_t tb = (size_t)st->table_rows * ns * 8;
@@ -634,7 +668,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
         rows.hll_stats.assign(hs, hs + n_sets * 2);
       }
       for (uint64_t k = 0; k < st->table_rows; k++) {
-        if (t[k * ns] == 0) continue;
+        if (t[k * ns] == 0 && !plan.zero_fill) continue;
         rows.keys.push_back(k);
         rows.slots.insert(rows.slots.end(), t + k * ns, t + (k + 1) * ns);
         if (hb) rows.hll_set.push_back(k * plan.n_hll);
@@ -740,6 +774,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   Assembler as{plan, rows, {}, {}, {}};
   as.agg_i.resize(plan.aggs.size());
   as.agg_f.resize(plan.aggs.size());
+  uint64_t hll_uncorrected = 0;  // estimates Spark would have bias-corrected (tables not available: hll_estimate above)
   for (size_t a = 0; a < plan.aggs.size(); a++) {
     const PlanAgg& pa = plan.aggs[a];
     if (pa.out_float) as.agg_f[a].resize(n);
@@ -748,6 +783,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
       if (pa.hll_index >= 0) {
         const uint64_t set = rows.hll_set[r] + pa.hll_index;
         as.agg_f[a][r] = hll_estimate_from(rows.hll_stats[set * 2], rows.hll_stats[set * 2 + 1]);
+        hll_uncorrected += hll_needs_bias_tables(rows.hll_stats[set * 2], rows.hll_stats[set * 2 + 1]);
         continue;
       }
       uint64_t raw = rows.slots[r * ns + pa.slot];
@@ -959,16 +995,20 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   }
 
   // ---- stats (DruidQueryExecutionView analogue, DruidRDD.scala:194-216) ------------------------------
-  char buf[1024];
+  // cardinality columns: Spark's HLL++ subtracts an empirical bias for raw estimates up to 5m when linear counting does
+  // not apply; those tables are not available here, so such values are the raw estimate and the caller is told how many
+  std::string hll_note;
+  if (plan.n_hll) hll_note = ",\"hllBiasCorrected\":false,\"hllUncorrectedValues\":" + std::to_string((unsigned long long)hll_uncorrected);
+  char buf[1200];
   snprintf(buf, sizeof buf,
            "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
            "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
            "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":%s,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu,\"jit\":%s,\"jitCompileMs\":%.3f,"
-           "\"planMs\":%.4f,\"assembleMs\":%.4f}",
+           "\"planMs\":%.4f,\"assembleMs\":%.4f%s}",
            plan.always_false ? "none" : strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row,
            (long long)plan.algorithmic_bytes, (unsigned long long)n, (unsigned long long)m, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms,
            st->launches, st->h2d_bytes, st->d2h_bytes, device_topk ? "true" : "false", plan.spans.size(), plan.seg_index.size(),
-           (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms, st->plan_ms, now_ms() - t_assemble);
+           (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms, st->plan_ms, now_ms() - t_assemble, hll_note.c_str());
   res->stats = buf;
   return res.release();
 }
@@ -1458,8 +1498,24 @@ Result* Engine::execute_select(const QuerySpec& spec, double t0) {
   return res.release();
 }
 
-Result* Engine::execute_plan(const Plan& plan, double t0) {
+// A plan whose filter or intervals match nothing still has to produce its (empty) tables when something reads them:
+// the other ranks of a sharded query, or a timeseries that reports empty buckets.  Same plan, zero units to scan.
+static Plan scan_nothing_variant(const Plan& plan) {
+  Plan v = plan;
+  v.spans.clear();
+  v.n_units = 0;
+  v.coarse.assign(2, 0);
+  v.rows_scanned = 0;
+  v.always_false = false;
+  return v;
+}
+
+Result* Engine::execute_plan(const Plan& plan_in, double t0) {
   if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
+  Plan empty_variant;
+  const Plan* use = &plan_in;
+  if (plan_in.always_false && plan_in.zero_fill) { empty_variant = scan_nothing_variant(plan_in); use = &empty_variant; }
+  const Plan& plan = *use;
   QueryCtx* ctx = acquire_ctx();
   ScanState st;
   st.plan_ms = now_ms() - t0;
@@ -1484,27 +1540,11 @@ Result* Engine::execute(const char* json, size_t len) {
   std::shared_lock<std::shared_mutex> lk;
   QuerySpec search;
   std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk, &search);
+  const QuerySpec& spec = plan_ptr ? plan_ptr->spec : search;
+  RunningQuery running(this, spec.query_id);
   if (!plan_ptr) return search.type == QuerySpec::Select ? execute_select(search, t0) : execute_search(search, t0);
-  const Plan& plan = *plan_ptr;
-  check_cancel(plan.spec.query_id);
-  if (device_ < 0) throw NoDevice("this engine was created without a CUDA device (planning only); there is no CPU execution path");
-  QueryCtx* ctx = acquire_ctx();
-  ScanState st;
-  st.plan_ms = now_ms() - t0;
-  Result* r = nullptr;
-  try {
-    if (!plan.always_false) run_scan(ctx, plan, &st);
-    check_cancel(plan.spec.query_id);
-    r = finalize(ctx, plan, &st, t0);
-  } catch (...) {
-    cudaStreamSynchronize(ctx->stream);
-    free_state(ctx, &st);
-    release_ctx(ctx);
-    throw;
-  }
-  free_state(ctx, &st);
-  release_ctx(ctx);
-  return r;
+  check_cancel(spec.query_id);
+  return execute_plan(*plan_ptr, t0);
 }
 
 std::string Engine::explain(const char* json, size_t len) {
@@ -1535,16 +1575,12 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root) {
   const double t0 = now_ms();
   std::shared_lock<std::shared_mutex> lk;
   std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk);
+  RunningQuery running(this, plan_ptr->spec.query_id);
   // every rank must produce the same table layout even when its own shard has no matching rows: scan zero units
   Plan empty_variant;
   const Plan* plan = plan_ptr.get();
   if (plan->always_false) {
-    empty_variant = *plan;
-    empty_variant.spans.clear();
-    empty_variant.n_units = 0;
-    empty_variant.coarse.assign(2, 0);
-    empty_variant.rows_scanned = 0;
-    empty_variant.always_false = false;
+    empty_variant = scan_nothing_variant(*plan);
     plan = &empty_variant;
   }
   // the same decision on every rank, from the plan alone: dense table + registers within the gather limit
@@ -1606,13 +1642,7 @@ Partial* Engine::partial(const char* json, size_t len) {
     p->ctx = acquire_ctx();
     // every rank must produce the same table layout even when its own shard has no matching rows:
     // scan zero units, so the tables are initialised and nothing is added
-    if (p->plan.always_false) {
-      p->plan.spans.clear();
-      p->plan.n_units = 0;
-      p->plan.coarse.assign(2, 0);
-      p->plan.rows_scanned = 0;
-      p->plan.always_false = false;
-    }
+    if (p->plan.always_false) p->plan = scan_nothing_variant(p->plan);
     run_scan(p->ctx, p->plan, &p->st);
     if (p->st.strategy == STRAT_HASH) compact_rows(p->ctx, p->plan, &p->st);
     p->st.merged = true;  // from here on the caller may fold other ranks' state into the table

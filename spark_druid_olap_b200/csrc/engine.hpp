@@ -144,7 +144,15 @@ class Engine {
   std::mutex ctx_mu_;
   std::vector<QueryCtx*> free_ctx_;
   std::mutex cancel_mu_;
-  std::set<std::string> cancelled_;
+  std::map<std::string, double> cancelled_;      // query id -> time of the cancel request (ms)
+  std::map<std::string, int> running_;           // query id -> queries running under it
+  std::map<std::string, double> running_since_;  // query id -> start of the oldest of them
+  struct RunningQuery {  // scope guard: registers a query id for the duration of its execution
+    RunningQuery(Engine* e, const std::string& qid);
+    ~RunningQuery();
+    Engine* e_;
+    std::string qid_;
+  };
   std::mutex lut_mu_;
   PinnedPool pinned_pool_;
   void* comm_ = nullptr;  // ncclComm_t of this engine's rank (sdo_engine_comm_init)
@@ -175,5 +183,6 @@ class Engine {
 
 double hll_estimate(const uint8_t* regs);
 double hll_estimate_from(double zinv, double zeros);
+bool hll_needs_bias_tables(double zinv, double zeros);
 
 }  // namespace sdo

@@ -16,6 +16,18 @@ namespace sdo {
 
 __host__ __device__ __forceinline__ long long f64_ord(long long bits) { return bits ^ ((bits >> 63) & 0x7FFFFFFFFFFFFFFFll); }
 
+// SM count of the calling thread's current device (grid sizes of the helper kernels are multiples of it)
+static int sm_count() {
+  static std::mutex mu;
+  static int cached[64] = {};
+  int dev = 0;
+  SDO_CUDA(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lk(mu);
+  if (dev < 0 || dev >= 64) return 148;
+  if (!cached[dev]) SDO_CUDA(cudaDeviceGetAttribute(&cached[dev], cudaDevAttrMultiProcessorCount, dev));
+  return cached[dev];
+}
+
 template <int STRAT>
 __global__ void __launch_bounds__(SCAN_THREADS, 4) scan_kernel(const __grid_constant__ ScanParams p, const uint32_t* __restrict__ coarse) {
   scan_body<STRAT>(p, coarse);
@@ -95,7 +107,7 @@ __global__ void fill_slots_kernel(unsigned long long* table, uint64_t n, int ns,
 void launch_fill_slots(unsigned long long* table, uint64_t n_rows, int n_slots, const uint64_t*, const ScanParams& p, cudaStream_t st) {
   uint64_t n = n_rows * (uint64_t)n_slots;
   if (!n) return;
-  int grid = (int)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 16);
   fill_slots_kernel<<<grid, 256, 0, st>>>(table, n, n_slots, p);
   SDO_CUDA(cudaGetLastError());
 }
@@ -110,7 +122,7 @@ __global__ void fill_hash_kernel(unsigned long long* table, uint64_t cap, uint32
 }
 void launch_fill_hash(unsigned long long* table, uint64_t cap, uint32_t stride, int n_slots, const ScanParams& p, cudaStream_t st) {
   if (!cap) return;
-  int grid = (int)std::min<uint64_t>((cap * stride + 255) / 256, 148 * 16);
+  int grid = (int)std::min<uint64_t>((cap * stride + 255) / 256, (uint64_t)sm_count() * 16);
   fill_hash_kernel<<<grid, 256, 0, st>>>(table, cap, stride, n_slots, p);
   SDO_CUDA(cudaGetLastError());
 }
@@ -121,7 +133,7 @@ __global__ void fill_u64_kernel(unsigned long long* dst, uint64_t n, unsigned lo
 }
 void launch_fill_u64(unsigned long long* dst, uint64_t n, unsigned long long v, cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<uint64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 16);
   fill_u64_kernel<<<grid, 256, 0, st>>>(dst, n, v);
   SDO_CUDA(cudaGetLastError());
 }
@@ -362,7 +374,7 @@ __global__ void encode_dim_kernel(const void* __restrict__ src, bool src64, cons
 void launch_encode_dim(const void* src, bool src64, const int32_t* perm, int64_t r0, int64_t n, const uint32_t* lut, void* dst, int w,
                        cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 16);
   encode_dim_kernel<<<grid, 256, 0, st>>>(src, src64, perm, r0, n, lut, dst, w);
   SDO_CUDA(cudaGetLastError());
 }
@@ -379,7 +391,7 @@ __global__ void reencode_kernel(const void* __restrict__ src, int sw, void* __re
 }
 void launch_reencode(const void* src, int sw, void* dst, int dw, int64_t n, const uint32_t* lut, cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 16);
   reencode_kernel<<<grid, 256, 0, st>>>(src, sw, dst, dw, n, lut);
   SDO_CUDA(cudaGetLastError());
 }
@@ -391,7 +403,7 @@ __global__ void gather64_kernel(const unsigned long long* __restrict__ src, cons
 }
 void launch_gather64(const void* src, const int32_t* perm, int64_t r0, int64_t n, void* dst, cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 16);
   gather64_kernel<<<grid, 256, 0, st>>>((const unsigned long long*)src, perm, r0, n, (unsigned long long*)dst);
   SDO_CUDA(cudaGetLastError());
 }
@@ -476,11 +488,11 @@ void launch_partition_rows(const unsigned long long* keys, const unsigned long l
                            unsigned long long* cursors_dev, cudaStream_t st) {
   // counts_dev must be zeroed by the caller; cursors_dev receives the exclusive prefix (host computes it between the two launches)
   if (!n) return;
-  int grid = (int)std::min<uint64_t>((n + 255) / 256, 148 * 8);
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 8);
   if (!cursors_dev) {
     partition_count_kernel<<<grid, 256, 0, st>>>(keys, n, n_ranks, counts_dev);
   } else {
-    grid = (int)std::min<uint64_t>((n + 256 * PART_ROWS - 1) / (256 * PART_ROWS), 148 * 8);
+    grid = (int)std::min<uint64_t>((n + 256 * PART_ROWS - 1) / (256 * PART_ROWS), (uint64_t)sm_count() * 8);
     partition_scatter_kernel<<<grid, 256, 0, st>>>(keys, slots, n, n_slots, n_ranks, cursors_dev, out_keys, out_slots);
   }
   SDO_CUDA(cudaGetLastError());
@@ -506,7 +518,7 @@ __global__ void merge_rows_kernel(const unsigned long long* __restrict__ keys, c
 }
 void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<uint64_t>((n + 255) / 256, 148 * 8);
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 8);
   merge_rows_kernel<<<grid, 256, 0, st>>>(keys, slots, n, p);
   SDO_CUDA(cudaGetLastError());
 }
@@ -554,7 +566,7 @@ __global__ void materialize_kernel(const unsigned long long* __restrict__ keys, 
 }
 void launch_materialize(const unsigned long long* keys, const unsigned long long* slots, const MatParams& mp, cudaStream_t st) {
   if (!mp.n) return;
-  int grid = (int)std::min<uint64_t>((mp.n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<uint64_t>((mp.n + 255) / 256, (uint64_t)sm_count() * 16);
   materialize_kernel<<<grid, 256, 0, st>>>(keys, slots, mp);
   SDO_CUDA(cudaGetLastError());
 }
@@ -590,7 +602,7 @@ void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size
                            const ScanParams& p, unsigned long long* table, cudaStream_t st) {
   const uint64_t words = blob_bytes / 8;
   if (!words) return;
-  int grid = (int)std::min<uint64_t>((words + 255) / 256, 148 * 8);
+  int grid = (int)std::min<uint64_t>((words + 255) / 256, (uint64_t)sm_count() * 8);
   merge_gathered_kernel<<<grid, 256, 0, st>>>(gathered, n_ranks, words, table_bytes / 8, cells, n_slots, p, table);
   SDO_CUDA(cudaGetLastError());
 }
@@ -611,7 +623,7 @@ __global__ void hll_column_kernel(const void* __restrict__ ids, int width, int m
 }
 void launch_hll_column(const void* ids, int width, int mode, const uint16_t* lut, int64_t n, uint16_t* out, cudaStream_t st) {
   if (!n) return;
-  int grid = (int)std::min<int64_t>((n + 255) / 256, 148 * 16);
+  int grid = (int)std::min<int64_t>((n + 255) / 256, (int64_t)sm_count() * 16);
   hll_column_kernel<<<grid, 256, 0, st>>>(ids, width, mode, lut, n, out);
   SDO_CUDA(cudaGetLastError());
 }
@@ -716,7 +728,7 @@ __global__ void select_gather_kernel(const void* const* __restrict__ segptr, uin
 void launch_select_count(const ScanParams& p, uint32_t* counts, cudaStream_t st) {
   if (!p.n_units) return;
   const uint32_t* coarse = (const uint32_t*)(p.spans + p.n_spans + 1);
-  select_count_kernel<<<(unsigned)std::min<uint32_t>(p.n_units, 148 * 8), 256, 0, st>>>(p, coarse, counts);
+  select_count_kernel<<<(unsigned)std::min<uint32_t>(p.n_units, (uint32_t)sm_count() * 8), 256, 0, st>>>(p, coarse, counts);
   SDO_CUDA(cudaGetLastError());
 }
 void launch_select_emit(const ScanParams& p, const SelectUnit* units, uint32_t n_units, uint32_t* out_seg, uint32_t* out_row, cudaStream_t st) {

@@ -20,6 +20,7 @@ namespace sdo {
 
 constexpr int MAX_LEAVES = 12;
 constexpr int MAX_OPS = 32;
+constexpr int FILTER_STACK = 8;     // masks the device evaluator's register stack holds (eval_filter16: 8 x 16 bits in two registers)
 constexpr int MAX_DIMS = 8;
 constexpr int MAX_AGGS = 16;
 constexpr int MAX_SLOTS = MAX_AGGS + 1;

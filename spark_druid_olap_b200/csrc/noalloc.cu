@@ -15,11 +15,14 @@
 //  * at most SDO_NOALLOC_MAX_KEYS keys and SDO_NOALLOC_MAX_ROWS rows; more is refused with SDO_INVALID;
 //  * the first call on each device looks up the array's device address; make that first call
 //    before any stream capture begins;
+//  * the call makes `device` current only for its own duration: the calling thread's current device is put back
+//    before it returns, whatever the outcome (a plugin must not change its host's device behind its back);
 //  * all calls on a device share the one array, which still holds the previous call's partials:
 //    the kernel rewrites every word it later reads and the ticket is zeroed on entry, but two calls
 //    that overlap in time on the same GPU (different streams or threads) race on it -- serialise them.
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cstdint>
 #include <mutex>
 #include <string>
@@ -141,8 +144,19 @@ extern "C" int sdo_groupby_sum_noalloc(int device, const uint8_t* keys_dev, cons
   if (device < 0 || device >= NA_MAX_DEVICES) return fail(SDO_INVALID, "sdo_groupby_sum_noalloc: bad device ordinal");
   if (!counts_out_dev || !sums_out_dev || (n_rows > 0 && (!keys_dev || !values_dev))) return fail(SDO_INVALID, "sdo_groupby_sum_noalloc: NULL pointer");
   if (((uintptr_t)keys_dev & 3) || ((uintptr_t)values_dev & 15)) return fail(SDO_INVALID, "sdo_groupby_sum_noalloc: keys must be 4-byte and values 16-byte aligned");
-  cudaError_t e = cudaSetDevice(device);
-  if (e != cudaSuccess) return fail(SDO_NO_DEVICE, std::string("sdo_groupby_sum_noalloc: cudaSetDevice: ") + cudaGetErrorString(e));
+  // the caller's current device is restored on every way out of this function
+  struct DeviceRestore {
+    int prev = -1;
+    ~DeviceRestore() { if (prev >= 0) cudaSetDevice(prev); }
+  } restore;
+  int prev = -1;
+  cudaError_t e = cudaGetDevice(&prev);
+  if (e != cudaSuccess) return fail(SDO_NO_DEVICE, std::string("sdo_groupby_sum_noalloc: cudaGetDevice: ") + cudaGetErrorString(e));
+  if (prev != device) {
+    e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(SDO_NO_DEVICE, std::string("sdo_groupby_sum_noalloc: cudaSetDevice: ") + cudaGetErrorString(e));
+    restore.prev = prev;
+  }
   const size_t smem = (size_t)n_keys * NA_SLOTS * NA_THREADS * 8;
   {
     // once per device, with that device current: resolve the array's device address

@@ -309,6 +309,17 @@ struct Compiler {
     throw Unsupported("filter kind");
   }
 
+  // stack entries the postfix form of `n` needs when and/or children are emitted deepest first (and/or commute, so the
+  // order is free): the device evaluator (scan_kernel.cuh eval_filter16) holds 8 masks, and with at most MAX_LEAVES
+  // leaves the deepest-first order never needs more than 4
+  static int stack_need(const CNode& n) {
+    if (n.kind == CNode::Const || n.kind == CNode::Leaf) return 1;
+    if (n.kind == CNode::Not) return stack_need(n.kids[0]);
+    std::vector<int> need;
+    for (auto& k : n.kids) need.push_back(stack_need(k));
+    std::sort(need.begin(), need.end(), std::greater<int>());
+    return need.size() > 1 ? std::max(need[0], need[1] + 1) : need[0];
+  }
   void emit(const CNode& n, int* depth, int* max_depth) {
     switch (n.kind) {
       case CNode::Const:
@@ -326,9 +337,12 @@ struct Compiler {
         plan.op_code.push_back(FOP_NOT);
         plan.op_arg.push_back(0);
         break;
-      case CNode::And: case CNode::Or:
-        for (size_t i = 0; i < n.kids.size(); i++) {
-          emit(n.kids[i], depth, max_depth);
+      case CNode::And: case CNode::Or: {
+        std::vector<const CNode*> kids;
+        for (auto& k : n.kids) kids.push_back(&k);
+        std::stable_sort(kids.begin(), kids.end(), [](const CNode* a, const CNode* b) { return stack_need(*a) > stack_need(*b); });
+        for (size_t i = 0; i < kids.size(); i++) {
+          emit(*kids[i], depth, max_depth);
           if (i) {
             plan.op_code.push_back(n.kind == CNode::And ? FOP_AND : FOP_OR);
             plan.op_arg.push_back(0);
@@ -336,6 +350,7 @@ struct Compiler {
           }
         }
         break;
+      }
     }
     *max_depth = std::max(*max_depth, *depth);
   }
@@ -539,7 +554,7 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
     } else {
       int depth = 0, max_depth = 0;
       cc.emit(root, &depth, &max_depth);
-      if (max_depth > 16) throw Unsupported("filter expression nests too deep for the device evaluator");
+      if (max_depth > FILTER_STACK) throw Unsupported("filter expression nests too deep for the device evaluator");
       if ((int)plan.op_code.size() > MAX_OPS) throw Unsupported("filter has too many operators (" + std::to_string(plan.op_code.size()) + ")");
     }
   }
@@ -764,6 +779,34 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
       for (auto& tf : time_fmts) tk.formatted.push_back(joda_format(tf.first, t, tf.second.offset_at(t)));
       tk_ids[tk] = 0;
     }
+  }
+  if (spec.type == QuerySpec::Timeseries && plan.has_bucket && !spec.skip_empty_buckets && plan.n_time_fmt == 0) {
+    // context.skipEmptyBuckets = false (Druid's own default for timeseries): every bucket of the granularity between the
+    // datasource's first and last timestamp inside the query intervals gets a row, empty ones with the aggregators'
+    // identities.  The buckets become time keys here; finalize then keeps groups without rows.
+    if (spec.granularity.kind == Granularity::None) throw Unsupported("skipEmptyBuckets = false with granularity none");
+    int64_t lo = INT64_MAX, hi = INT64_MIN;
+    for (auto& sgp : ds.segments)
+      if (!sgp->time_vals.empty()) { lo = std::min(lo, sgp->time_vals.front()); hi = std::max(hi, sgp->time_vals.back()); }
+    const Granularity& g = spec.granularity;
+    for (auto& iv : ivs) {
+      if (lo > hi) break;
+      const int64_t a = std::max(iv.start, lo), b = std::min(iv.end, hi + 1);
+      for (int64_t t = a; t < b;) {
+        TimeKey tk;
+        tk.bucket = bucket_start(g, t);
+        tk_ids[tk] = 0;
+        if (tk_ids.size() > (1u << 22)) throw Unsupported("skipEmptyBuckets = false: more than 4 M buckets in the query intervals");
+        int64_t next;
+        if (g.kind == Granularity::Duration) next = tk.bucket + g.duration_ms;
+        else if (g.months) next = bucket_start(g, tk.bucket + (int64_t)g.months * 31 * MS_DAY + MS_DAY);
+        else if (g.period_ms < MS_DAY) next = bucket_start(g, tk.bucket + g.period_ms);
+        else next = bucket_start(g, tk.bucket + g.period_ms + 2 * 3600 * 1000);  // local-time aligned: step over a daylight-saving shift
+        if (next <= tk.bucket) throw std::runtime_error("internal: granularity buckets do not advance");
+        t = next;
+      }
+    }
+    plan.zero_fill = true;
   }
   if (plan.has_time_key) {
     uint64_t id = 0;

@@ -74,6 +74,7 @@ struct Plan {
   std::vector<DevExpr> exprs;       // argument programs of AGG_*_EXPR aggregations (DevAgg::col indexes this)
   std::vector<int> hll_ds_dim;      // per dev agg with AGG_HLL and HLL_LUT: datasource dim whose LUT is needed (-1 otherwise)
   std::vector<TimeKey> time_keys;   // index = time key id
+  bool zero_fill = false;           // timeseries with context.skipEmptyBuckets = false: groups without rows are reported too
   bool has_time_key = false;
   bool has_bucket = false;          // granularity != all
   int n_time_fmt = 0;

@@ -116,6 +116,42 @@ def test_timeseries_granularity_hll(loaded, period):
     assert np.array_equal(res.hll["custs"][order], regs["custs"])
 
 
+def test_hll_estimate_regimes_and_uncorrected_window(loaded):
+    """The value of a cardinality column follows Spark's HyperLogLogPlusPlusHelper.query for p = 9 in the two regimes that
+    need no empirical table -- linear counting (m ln(m / V) <= 400) and the raw estimate above 5m = 2560 -- and is the RAW
+    estimate in between, where Spark subtracts a table-driven bias that is not available offline.  The stats say so:
+    hllBiasCorrected false, hllUncorrectedValues = how many reported values lie in that window (computed here from the
+    exported registers with the test's own statement of Spark's rule)."""
+    import math
+    eng, tbl = loaded
+    m = 512.0
+    alpha_m2 = (0.7213 / (1.0 + 1.079 / m)) * m * m
+    seen = {"linear": 0, "window": 0, "raw": 0}
+    for gran, field in (("P1D", "o_custkey"), ("P1M", "o_custkey"), ("P1Y", "o_orderkey"), ("P1M", "o_orderkey")):
+        q = json.loads(Q.timeseries(gran, False).to_json())
+        q["aggregations"][1]["fieldNames"] = [field]
+        res = eng.execute(q)
+        window = 0
+        for i in range(res.n_rows):
+            regs = res.hll["custs"][i].astype(np.int64)
+            zinv = float(np.sum(1.0 / (1 << regs).astype(np.float64)))
+            V = int((regs == 0).sum())
+            E = alpha_m2 / zinv
+            H = m * math.log(m / V) if V else None
+            if H is not None and H <= 400.0:
+                want, regime = H, "linear"
+            elif E > 5 * m:
+                want, regime = E, "raw"
+            else:
+                want, regime = E, "window"  # Spark: E - estimateBias(E); here E, flagged
+                window += 1
+            seen[regime] += 1
+            assert float(res["custs"][i]) == float(math.floor(want + 0.5)), (gran, field, i, regime)
+        assert res.stats["hllBiasCorrected"] is False
+        assert res.stats["hllUncorrectedValues"] == window, (gran, field)
+    assert all(v > 0 for v in seen.values()), seen  # every regime was exercised
+
+
 @pytest.mark.parametrize("place", ["global", "shared"])
 @pytest.mark.parametrize("shape", ["ts_month", "ts_day", "year_nation", "agg_zoo", "basic_agg"])
 def test_hll_register_placement(loaded, shape, place):
@@ -198,6 +234,35 @@ def test_timeseries_simple_granularity_strings(loaded):
         q["granularity"] = g
         res = eng.execute(q)
         H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, q), what=g)
+
+
+@pytest.mark.parametrize("period,strategy", [("P1D", None), ("P1D", "global"), ("P1M", None), ("P1W", "lane")])
+def test_timeseries_reports_empty_buckets_on_request(loaded, period, strategy):
+    """context.skipEmptyBuckets = false (Druid's default for a timeseries query): every bucket between the datasource's
+    first and last timestamp inside the query interval gets a row, empty ones with the aggregators' identities.  The
+    non-empty rows are the oracle's (Spark has no rows for empty buckets, which is what the engine returns by default)."""
+    eng, tbl = loaded
+    q = json.loads(Q.timeseries(period, True, strategy, ["1993-02-10T00:00:00.000Z/1993-09-20T00:00:00.000Z"]).to_json())
+    # a filter selective enough to leave some days (and, for the rarest value, weeks) without a row
+    q["filter"] = json.loads(Q.And(Q.SelectorFilterSpec("s_nation", "PERU"), Q.SelectorFilterSpec("c_nation", "KENYA"), Q.SelectorFilterSpec("l_shipmode", "AIR")).to_json())
+    want = orc.execute(tbl, q)
+    q["context"] = dict(q.get("context") or {"queryId": "zf"}, skipEmptyBuckets=False)
+    res = eng.execute(q)
+    rows = H.engine_rows(res)
+    full = [r for r in rows if r["rows"] > 0]
+    H.assert_rows_equal(full, want, what=f"non-empty buckets {period}")
+    empty = [r for r in rows if r["rows"] == 0]
+    assert all(r["price"] == 0.0 and r["custs"] == 0.0 for r in empty)
+    # the buckets: consecutive starts of the granularity from the interval's first bucket to its last
+    a, b = orc.parse_interval(q["intervals"][0])
+    bfn = orc.bucket_fn(q["granularity"])
+    expect = sorted({bfn(t) for t in range(a, b, 3600 * 1000)})
+    assert sorted(r["timestamp"] for r in rows) == expect
+    if period == "P1D":
+        assert len(empty) > 0
+    # the default (and an explicit true) keeps Spark's shape: no rows for empty buckets
+    q["context"]["skipEmptyBuckets"] = True
+    H.assert_rows_equal(H.engine_rows(eng.execute(q)), want, what="skipEmptyBuckets true")
 
 
 @pytest.mark.parametrize("strategy", [None, "hash"])

@@ -77,6 +77,28 @@ def test_twelve_filter_leaves_and_one_more(loaded):
         loaded[0].execute(dict(json.loads(Q.with_filter(g).to_json()), dataSource=loaded[2]))
 
 
+@pytest.mark.parametrize("jit", [False, True])
+def test_alternating_and_or_nesting_twelve_levels(loaded, jit):
+    """and(a, or(b, and(c, or(d, ...)))) over 12 leaves: emitted left to right this needs a 12-entry evaluation stack, and
+    the device evaluator holds 8 masks (an overflow used to drop the oldest mask silently).  The planner emits the
+    deepest child first, so the nesting below needs 2 entries; both kernels must give the oracle's rows."""
+    leaves = [Q.ExtractionFilterSpec("s_nation", ["PERU", "CHINA", "KENYA", "JAPAN", "INDIA"]), Q.ExtractionFilterSpec("c_nation", ["FRANCE", "INDIA", "IRAQ"]),
+              Q.ExtractionFilterSpec("l_shipmode", ["AIR", "SHIP", "RAIL", "MAIL"]), Q.ExtractionFilterSpec("p_brand", ["Brand#11", "Brand#23", "Brand#55"]),
+              Q.Not(Q.RegexFilterSpec("p_type", "BRASS$")), Q.StringContainsSpec("p_type", "PROMO"),
+              Q.BoundFilterSpec("o_orderdate", "1993-06-01", False, "1997-02-01", True, False), Q.ExtractionFilterSpec("c_mktsegment", ["BUILDING", "MACHINERY"]),
+              Q.Not(Q.ExtractionFilterSpec("p_size", ["3", "17", "44"])), Q.ExtractionFilterSpec("l_linenumber", ["1", "5"]),
+              Q.Not(Q.SelectorFilterSpec("l_returnflag", "N")), Q.ExtractionFilterSpec("c_region", ["ASIA", "EUROPE"])]
+    f = leaves[-1]
+    for depth, leaf in enumerate(reversed(leaves[:-1])):
+        f = (Q.And if depth % 2 else Q.Or)(leaf, f)
+    q = json.loads(Q.with_filter(f).to_json())
+    q["context"] = dict(q.get("context") or {}, gpuJit=jit)
+    res = _run(loaded, q, f"12 alternating levels jit={jit}")
+    assert 0 < res.n_rows
+    ex = loaded[0].explain(dict(q, dataSource=loaded[2]))
+    assert len(ex["filter"]["leaves"]) == 12
+
+
 @pytest.mark.parametrize("sf,world,rank", [(0.05, 8, 7), (0.003, 1, 0), (0.0007, 1, 0), (0.0001, 1, 0)])
 def test_ragged_tiny_tables(gpu_engine, sf, world, rank):
     """Few rows per month segment: every span ends inside its first unit, most tickets fall past the end of their span."""

@@ -2,11 +2,15 @@
 inside another runtime's fixed device reservation, a host that forbids cudaMalloc after start-up).
 
 It is called here through the C ABI on caller-owned device buffers and checked against the regular
-entry point (sdo_query_execute) on the same rows: counts bit-exact, double sums within the 1e-9
+entry point (sdo_query_execute) on the same rows and, independently of the engine, against numpy on
+the raw generated rows (np.bincount, math.fsum): counts bit-exact, double sums within the 1e-9
 relative tolerance the other parity tests use.  Two calls run back to back on different metrics, so
-partials left in the shared scratch array by the first call would show up in the second.
+partials left in the shared scratch array by the first call would show up in the second; around the
+second call the free device memory (cudaMemGetInfo) must not move, which is the promise the entry
+point exists for.
 Collected last on purpose (file name), so an -x run has finished every other test before this one."""
 import json
+import math
 
 import numpy as np
 import pytest
@@ -44,18 +48,28 @@ def test_noalloc_matches_query_execute_twice_in_a_row(gpu_engine):
         keys = torch.from_numpy(tab.data["l_returnflag"].astype(np.uint8)).to(dev)
         counts = torch.full((nk,), -1, dtype=torch.int64, device=dev)
         sums = torch.full((nk,), float("nan"), dtype=torch.float64, device=dev)
-        for metric in ("l_extendedprice", "l_quantity"):  # two calls in a row on the shared scratch
+        raw_keys = tab.data["l_returnflag"]
+        for call, metric in enumerate(("l_extendedprice", "l_quantity")):  # two calls in a row on the shared scratch
             vals = torch.from_numpy(tab.data[metric]).to(dev)
             torch.cuda.synchronize()
+            free_before = torch.cuda.mem_get_info(dev)[0]  # cudaMemGetInfo
             sdo.groupby_sum_noalloc(eng.device, keys.data_ptr(), vals.data_ptr(), n, nk, counts.data_ptr(), sums.data_ptr(), None)
             torch.cuda.synchronize()
+            if call == 1:  # the first call may load the kernel's module; from then on the call takes no device memory at all
+                assert torch.cuda.mem_get_info(dev)[0] == free_before
+            assert torch.cuda.current_device() == eng.device
             want = _engine_sums(eng, metric)
             got_c, got_s = counts.cpu().numpy(), sums.cpu().numpy()
             assert sum(got_c) == n
+            np_counts = np.bincount(raw_keys, minlength=nk)
             for code, name in enumerate(names):
                 wc, ws = want.get(name, (0, 0.0))
                 assert int(got_c[code]) == wc, (metric, name)
                 assert abs(float(got_s[code]) - ws) <= H.F64_RTOL * max(abs(ws), 1e-300), (metric, name, got_s[code], ws)
+                # and against the raw rows, without the engine in between
+                exact = math.fsum(tab.data[metric][raw_keys == code].tolist())
+                assert int(got_c[code]) == int(np_counts[code]), (metric, name)
+                assert abs(float(got_s[code]) - exact) <= H.F64_RTOL * max(abs(exact), 1e-300), (metric, name, got_s[code], exact)
         # a row count that is not a multiple of 4 and ids outside n_keys (ignored)
         m = 1001
         sdo.groupby_sum_noalloc(eng.device, keys.data_ptr(), vals.data_ptr(), m, 2, counts.data_ptr(), sums.data_ptr(), None)
