@@ -124,7 +124,7 @@ int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_o
  *   javascript filters / extraction functions / aggregations are accepted when the function is a single
  *     `return <expression>` (comparisons, string methods, arithmetic); nothing of it runs per row.
  *   context keys read: queryId, skipEmptyBuckets, gpuTimeBoundary, and the test knobs gpuStrategy,
- *     gpuJit, gpuHllPlace, gpuTicketRows; unknown keys are ignored.
+ *     gpuJit, gpuHllPlace, gpuTicketRows, gpuShardMerge; unknown keys are ignored.
  *     skipEmptyBuckets defaults to TRUE here (Druid: false): the parity target is Spark running the
  *     un-rewritten plan, which has no rows for empty buckets.  An explicit false is honoured for
  *     timeseries queries (one row per granularity bucket between the datasource's first and last
@@ -238,21 +238,44 @@ int sdo_datasource_restore(sdo_engine* e, const char* name, const char* path);
 
 /* ---- sharded execution with the merge inside the library ---------------------------------------
  * One engine per GPU, one process per engine.  Replaces the Spark-side re-aggregation of the per-historical partial
- * results (SQD/DruidStrategy.scala:353-359, SQD/PostAggregate.scala:39-103) for dense key spaces whose table (and HLL
- * registers) fit 4 MB: scan, one NCCL all-gather of the raw partial tables and the fold on `root` are queued on one
- * stream by one call, without a round trip through the host language between them.
+ * results (SQD/DruidStrategy.scala:353-359, SQD/PostAggregate.scala:39-103; partitions from SLD/DruidRDD.scala:244-269):
+ * scan, the merge of the partial aggregates over NCCL and the finish are queued on one stream by one call, without a
+ * round trip through the host language between them.  The merge is chosen from the query's key space (the same on every
+ * rank once dictionaries are aligned), SURVEY 8e:
+ *   gather : dense table + HLL registers up to 256 KB -- one ncclAllGather of the raw partial blobs, folded in rank
+ *            order on `root` (bit-reproducible);
+ *   reduce : larger dense tables (up to 64 MB) -- the table is transposed to [slot][key] and every slot reduced to `root`
+ *            with its own operator (ncclReduce int64 / float64 sum, int64 min / max), HLL registers as uint8 max, one
+ *            NCCL group;
+ *   sparse : hash tables and key spaces beyond that -- every rank turns its groups into (key, slots) rows, splits them
+ *            by owner = mix(key) mod world, exchanges them with grouped ncclSend / ncclRecv and merges what it
+ *            receives, so it owns a disjoint share of the groups.  A query that asks for the top K <= 1024 groups by
+ *            one aggregate (TopN with a numeric metric, limitSpec over one aggregate column, no having) takes the top K
+ *            of every share, all-gathers the K * world candidates and finishes on `root`.  Any other sparse query
+ *            returns, on EVERY rank, that rank's share of the groups (*out non-NULL everywhere; the caller unions them,
+ *            as Spark unions partitions); ordering / limit / having then apply per share.  Cardinality aggregations
+ *            have no sparse merge (SDO_UNSUPPORTED before anything is queued).
  *
  * sdo_comm_unique_id: on one rank; hand the 128 bytes to every rank (any channel).  `nccl_library` = path of
  *   libnccl.so.2 to load if the process has none loaded yet (NULL: default search path).
  * sdo_engine_comm_init: on every rank, collectively; the engine's device must be the calling thread's current one.
  * sdo_query_execute_sharded: on every rank, collectively, with the same query (ids and time keys must mean the same on
  *   every rank: same dictionaries, context.gpuTimeBoundary set -- what sharded.align_datasource arranges).  On `root`
- *   *out is the merged result; elsewhere *out is NULL.  Shapes outside the dense / 4 MB case return SDO_UNSUPPORTED before
- *   anything is queued (use sdo_query_partial and the host-side merge). */
+ *   *out is the merged result; elsewhere *out is NULL (except the sparse shares described above).  The caller issues
+ *   sharded queries of one engine one at a time and in the same order on every rank.
+ * sdo_query_execute_sharded_at: the same for callers that run several sharded queries at once on one engine
+ *   (DruidPlanner.scala:83-90 allows 100 connections): `turn` is the query's position in the communicator's collective
+ *   order -- the same number on every rank, consecutive from sdo_engine_comm_next_turn (0 after comm_init).  Scans of
+ *   different turns overlap; their collectives are issued in turn order, so two ranks can never pair mismatched
+ *   collectives.  A turn whose query fails before its first collective is given up; a turn that never arrives makes the
+ *   later ones fail after 120 s.
+ * context.gpuShardMerge = gather | reduce | sparse forces the merge (tests). */
 #define SDO_COMM_ID_BYTES 128
 int sdo_comm_unique_id(void* id_out, const char* nccl_library);
 int sdo_engine_comm_init(sdo_engine* e, const void* id, int rank, int world, const char* nccl_library);
 int sdo_query_execute_sharded(sdo_engine* e, const char* query_json, size_t len, int root, sdo_result** out);
+int sdo_query_execute_sharded_at(sdo_engine* e, const char* query_json, size_t len, int root, int64_t turn, sdo_result** out);
+int sdo_engine_comm_next_turn(sdo_engine* e, int64_t* turn_out);
 
 /* ---- allocation-free group-by ----------------------------------------------------------------
  * No counterpart in the reference (it has no native code and no notion of device memory).

@@ -130,7 +130,78 @@ def execute(ct, q, threads=None, return_registers=False):
         return None
 
 
-def _execute(ct, q, threads, return_registers):
+def execute_partial(ct, q, threads=None):
+    """The grouped rows of `q` over this table BEFORE post-aggregations / having / ordering / limit, for merging with the
+    partials of other tables (bench.py's parity gate runs one shard of the generator at a time).
+    Returns (rows carrying "__key", registers, key_names) or None when the shape is not covered."""
+    try:
+        return _execute(ct, q, threads or default_threads(), True, partial=True)
+    except _Unsupported:
+        return None
+
+
+def merge_partials(q, partials, return_registers=False):
+    """Merge execute_partial() outputs of disjoint row sets and finish the query: count / sum -> sum (doubles with
+    math.fsum over the partial sums), min -> min, max -> max, cardinality -> register-wise max then the estimator
+    (the merge algebra of sources/druid/PostAggregate.scala:39-60)."""
+    import math
+    kinds = {}
+    for a in q.get("aggregations", []):
+        name = a.get("name")
+        if a["type"] == "filtered":
+            name = a.get("name") or a["aggregator"]["name"]
+            a = a["aggregator"]
+        t = a["type"]
+        if t == "javascript":
+            params, body = orc.js_subset.parse_function(a["fnAggregate"])
+            fold, _ = orc.js_subset.split_fold(params, body)
+            kinds[name] = {"sum": "fsum", "min": "min", "max": "max"}[fold]
+        elif t in ("cardinality", "hyperUnique"):
+            kinds[name] = "hll"
+        elif t in ("count", "longSum"):
+            kinds[name] = "isum"
+        elif t == "doubleSum":
+            kinds[name] = "fsum"
+        else:
+            kinds[name] = "min" if t.lower().endswith("min") else "max"
+    acc, regs, key_names = {}, {}, None
+    for rows, registers, kn in partials:
+        key_names = kn
+        for i, r in enumerate(rows):
+            k = r["__key"]
+            t = acc.get(k)
+            if t is None:
+                t = acc[k] = {n: ([v] if kinds.get(n) == "fsum" else v) for n, v in r.items()}
+                for n in registers:
+                    regs[(n, k)] = registers[n][i].copy()
+                continue
+            for n, kind in kinds.items():
+                if kind == "isum":
+                    t[n] += r[n]
+                elif kind == "fsum":
+                    t[n].append(r[n])
+                elif kind == "min":
+                    t[n] = min(t[n], r[n])
+                elif kind == "max":
+                    t[n] = max(t[n], r[n])
+            for n in registers:
+                np.maximum(regs[(n, k)], registers[n][i], out=regs[(n, k)])
+    keys = sorted(acc)
+    out = []
+    for k in keys:
+        t = acc[k]
+        for n, kind in kinds.items():
+            if kind == "fsum":
+                t[n] = math.fsum(t[n])
+            elif kind == "hll":
+                t[n] = orc.hll_estimate(regs[(n, k)])
+        out.append(t)
+    reg_names = [n for n, kind in kinds.items() if kind == "hll"]
+    registers = {n: np.array([regs[(n, k)] for k in keys], dtype=np.uint8).reshape(-1, 512) for n in reg_names}
+    return orc.finalize(q, out, registers, key_names or [], return_registers)
+
+
+def _execute(ct, q, threads, return_registers, partial=False):
     L = _load()
     keep = []  # numpy buffers that must outlive the call
     qt = q["queryType"]
@@ -347,4 +418,6 @@ def _execute(ct, q, threads, return_registers):
         out.append(row)
     registers = {k: np.array(v, dtype=np.uint8).reshape(-1, 512) for k, v in registers.items()}
     key_names = (["timestamp"] if buckets is not None else []) + [d[0] for d in decoders]
+    if partial:
+        return out, registers, key_names
     return orc.finalize(q, out, registers, key_names, return_registers)

@@ -110,6 +110,8 @@ def lib():
         "sdo_comm_unique_id": (C.c_int, [vp, cp]),
         "sdo_engine_comm_init": (C.c_int, [vp, vp, C.c_int, C.c_int, cp]),
         "sdo_query_execute_sharded": (C.c_int, [vp, cp, sz, C.c_int, C.POINTER(vp)]),
+        "sdo_query_execute_sharded_at": (C.c_int, [vp, cp, sz, C.c_int, i64, C.POINTER(vp)]),
+        "sdo_engine_comm_next_turn": (C.c_int, [vp, C.POINTER(i64)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -126,7 +128,7 @@ EXPORTED_SYMBOLS = [
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
     "sdo_dimension_dictionary", "sdo_dimension_extend", "sdo_partial_export", "sdo_partial_merge_gathered",
-    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded", "sdo_datasource_save", "sdo_datasource_restore",
+    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded", "sdo_query_execute_sharded_at", "sdo_engine_comm_next_turn", "sdo_datasource_save", "sdo_datasource_restore",
 ]
 
 NOALLOC_MAX_KEYS = 24
@@ -391,6 +393,12 @@ class Engine:
         out = C.c_char_p()
         _check(lib().sdo_query_explain(self._h, q, len(q), C.byref(out)))
         return json.loads(out.value.decode())
+
+    def sharded_next_turn(self):
+        """The next free turn of this engine's communicator (sdo_engine_comm_next_turn)."""
+        t = C.c_int64()
+        _check(lib().sdo_engine_comm_next_turn(self._h, C.byref(t)))
+        return int(t.value)
 
     def cancel(self, query_id):
         _check(lib().sdo_query_cancel(self._h, query_id.encode()))

@@ -268,4 +268,19 @@ int sdo_query_execute_sharded(sdo_engine* e, const char* query_json, size_t len,
   });
 }
 
+int sdo_query_execute_sharded_at(sdo_engine* e, const char* query_json, size_t len, int root, int64_t turn, sdo_result** out) {
+  if (!e || !query_json || !out) return bad("sdo_query_execute_sharded_at: NULL argument");
+  if (turn < 0) return bad("sdo_query_execute_sharded_at: turn must be >= 0");
+  *out = nullptr;
+  return guard([&] {
+    Result* r = e->e->execute_sharded(query_json, len, root, turn);
+    if (r) *out = new sdo_result{r};
+  });
+}
+
+int sdo_engine_comm_next_turn(sdo_engine* e, int64_t* turn_out) {
+  if (!e || !turn_out) return bad("sdo_engine_comm_next_turn: NULL argument");
+  return guard([&] { *turn_out = e->e->next_turn(); });
+}
+
 }  // extern "C"

@@ -17,6 +17,11 @@ struct Api {
   int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
   int (*CommDestroy)(void*) = nullptr;
   int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+  int (*Reduce)(const void*, void*, size_t, int, int, int, void*, cudaStream_t) = nullptr;
+  int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
   const char* (*GetErrorString)(int) = nullptr;
 };
 Api g_api;
@@ -51,7 +56,12 @@ void nccl_load(const char* path) {
   *(void**)&a.CommDestroy = dlsym(h, "ncclCommDestroy");
   *(void**)&a.AllGather = dlsym(h, "ncclAllGather");
   *(void**)&a.GetErrorString = dlsym(h, "ncclGetErrorString");
-  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather) throw std::runtime_error("libnccl.so.2 lacks the expected entry points");
+  *(void**)&a.Reduce = dlsym(h, "ncclReduce");
+  *(void**)&a.Send = dlsym(h, "ncclSend");
+  *(void**)&a.Recv = dlsym(h, "ncclRecv");
+  *(void**)&a.GroupStart = dlsym(h, "ncclGroupStart");
+  *(void**)&a.GroupEnd = dlsym(h, "ncclGroupEnd");
+  if (!a.GetUniqueId || !a.CommInitRank || !a.CommDestroy || !a.AllGather || !a.Reduce || !a.Send || !a.Recv || !a.GroupStart || !a.GroupEnd) throw std::runtime_error("libnccl.so.2 lacks the expected entry points");
   g_api = a;
 }
 
@@ -77,5 +87,19 @@ void nccl_comm_destroy(void* comm) {
 void nccl_all_gather_bytes(void* comm, const void* send, void* recv, size_t bytes, cudaStream_t stream) {
   check(api().AllGather(send, recv, bytes, /*ncclInt8*/ 0, comm, stream), "ncclAllGather");
 }
+
+
+// ncclDataType_t / ncclRedOp_t values (nccl.h): uint8 = 1, int64 = 4, float64 = 8; sum = 0, max = 2, min = 3
+void nccl_reduce(void* comm, const void* send, void* recv, size_t count, NcclType type, NcclOp op, int root, cudaStream_t stream) {
+  check(api().Reduce(send, recv, count, (int)type, (int)op, root, comm, stream), "ncclReduce");
+}
+void nccl_send_bytes(void* comm, const void* send, size_t bytes, int peer, cudaStream_t stream) {
+  check(api().Send(send, bytes, /*ncclInt8*/ 0, peer, comm, stream), "ncclSend");
+}
+void nccl_recv_bytes(void* comm, void* recv, size_t bytes, int peer, cudaStream_t stream) {
+  check(api().Recv(recv, bytes, /*ncclInt8*/ 0, peer, comm, stream), "ncclRecv");
+}
+void nccl_group_start() { check(api().GroupStart(), "ncclGroupStart"); }
+void nccl_group_end() { check(api().GroupEnd(), "ncclGroupEnd"); }
 
 }  // namespace sdo

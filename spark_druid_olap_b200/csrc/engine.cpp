@@ -680,21 +680,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
       // device top-k when only a few rows of a large result are wanted
       int topk_slot = -1, topk_f64 = 0, topk_desc = 1;
       int64_t k_want = 0;
-      if (!plan.spec.has_having && n > 65536) {
-        const QuerySpec& q = plan.spec;
-        std::string col;
-        bool desc = true;
-        if (q.type == QuerySpec::TopN && q.metric.kind == TopNMetric::Numeric) { col = q.metric.metric; desc = !q.metric.inverted; k_want = q.threshold; }
-        else if (q.type == QuerySpec::GroupBy && q.limit.present && q.limit.columns.size() == 1) { col = q.limit.columns[0].dimension; desc = !q.limit.columns[0].ascending; k_want = q.limit.limit; }
-        if (!col.empty() && k_want > 0 && k_want <= 1024) {
-          for (auto& a : plan.aggs)
-            if (a.name == col && a.hll_index < 0 && !a.const_times_count && !(a.kind == AggregationSpec::Count && a.slot == 0 && false)) {
-              topk_slot = a.slot;
-              topk_f64 = (a.kind == AggregationSpec::DoubleSum) ? 1 : 0;  // min/max doubles are already order-preserving ints
-              topk_desc = desc ? 1 : 0;
-            }
-        }
-      }
+      if (n <= 65536 || !topk_request(plan, &topk_slot, &topk_f64, &topk_desc, &k_want)) topk_slot = -1;
       // A large result that needs no host-side work (no post-aggregation, having, ordering or sketches)
       // is turned into its columns on the device and copied straight into pinned result buffers.
       {
@@ -759,6 +745,18 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
         SDO_CUDA(cudaStreamSynchronize(s));
         st->d2h_bytes += (size_t)n * (ns + 1) * 8 + rows.hll_bytes + rows.hll_stats.size() * 8;
         rows.n = n;
+        if (!plan.n_hll) {
+          // top-k candidates gathered from several ranks are padded with the empty key where a share held fewer than K groups
+          size_t w = 0;
+          for (size_t i = 0; i < (size_t)n; i++)
+            if (rows.keys[i] != ~0ull) {
+              if (w != i) { rows.keys[w] = rows.keys[i]; memmove(&rows.slots[w * ns], &rows.slots[i * ns], (size_t)ns * 8); }
+              w++;
+            }
+          rows.keys.resize(w);
+          rows.slots.resize(w * ns);
+          rows.n = w;
+        }
       }
     }
     cudaEventElapsedTime(&ms_h2d, ctx->ev[0], ctx->ev[1]);
@@ -999,6 +997,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   // not apply; those tables are not available here, so such values are the raw estimate and the caller is told how many
   std::string hll_note;
   if (plan.n_hll) hll_note = ",\"hllBiasCorrected\":false,\"hllUncorrectedValues\":" + std::to_string((unsigned long long)hll_uncorrected);
+  if (st->shard_merge) hll_note += std::string(",\"shardMerge\":\"") + st->shard_merge + "\",\"exchangeBytes\":" + std::to_string((unsigned long long)st->exchange_bytes);
   char buf[1200];
   snprintf(buf, sizeof buf,
            "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
@@ -1142,10 +1141,11 @@ Result* Engine::finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st
            "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
            "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
            "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":false,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu,\"jit\":%s,\"jitCompileMs\":%.3f,"
-           "\"columnar\":true}",
+           "\"columnar\":true%s}",
            strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row, (long long)plan.algorithmic_bytes,
            (unsigned long long)n, (unsigned long long)n, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms, st->launches, st->h2d_bytes, st->d2h_bytes,
-           plan.spans.size(), plan.seg_index.size(), (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms);
+           plan.spans.size(), plan.seg_index.size(), (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms,
+           st->shard_merge ? (std::string(",\"shardMerge\":\"") + st->shard_merge + "\",\"exchangeBytes\":" + std::to_string((unsigned long long)st->exchange_bytes)).c_str() : "");
   res->stats = buf;
   (void)q;
   return res.release();
@@ -1567,59 +1567,245 @@ void Engine::comm_init(const void* id, int rank, int world) {
   comm_world_ = world;
 }
 
-// Scan the local segments, all-gather the raw partial tables (one contiguous blob per rank: aggregate slots + HLL
-// registers), fold them in rank order on `root`, finish there.  Everything is queued on one stream by this call.
-Result* Engine::execute_sharded(const char* json, size_t len, int root) {
+// ---- a query's turn on the communicator ------------------------------------------------------------------------------
+// Collectives of one communicator must be issued in the same order on every rank.  A sharded query holds the turn from
+// its first collective to its last (its scan runs before that, concurrently with other queries).  Callers that run
+// several sharded queries at once give each a turn number -- the same number on every rank, consecutive from 0 -- and
+// the engine issues their collectives in that order; without a number (turn < 0) the caller keeps the ranks in step.
+struct Engine::CommTurn {
+  Engine* e;
+  int64_t turn;
+  bool held = false;
+  CommTurn(Engine* e_, int64_t turn_) : e(e_), turn(turn_) {}
+  void acquire() {
+    std::unique_lock<std::mutex> lk(e->turn_mu_);
+    auto ready = [&] { return !e->turn_busy_ && (turn < 0 || e->next_turn_ == turn); };
+    if (turn >= 0 && turn < e->next_turn_) throw Invalid("sdo_query_execute_sharded_at: turn " + std::to_string((long long)turn) + " has already been taken");
+    if (!e->turn_cv_.wait_for(lk, std::chrono::seconds(120), ready))
+      throw std::runtime_error("sharded query: turn " + std::to_string((long long)turn) + " never came (the turn before it was not issued on this rank)");
+    e->turn_busy_ = true;
+    held = true;
+  }
+  ~CommTurn() {
+    std::unique_lock<std::mutex> lk(e->turn_mu_);
+    if (held) {
+      e->turn_busy_ = false;
+      if (turn >= 0) e->next_turn_ = turn + 1;
+    } else if (turn >= 0 && turn >= e->next_turn_) {
+      // the query failed before its first collective: give the turn up so that later ones do not wait for it
+      e->turn_cv_.wait_for(lk, std::chrono::seconds(120), [&] { return !e->turn_busy_ && e->next_turn_ == turn; });
+      if (e->next_turn_ == turn) e->next_turn_ = turn + 1;
+    }
+    e->turn_cv_.notify_all();
+  }
+};
+
+// which merge a sharded query takes: decided from quantities that are the same on every rank (key space after dictionary
+// alignment, slots, sketches, forced strategy) -- never from this rank's row counts
+enum class ShardMerge { Gather, Reduce, Sparse };
+static ShardMerge shard_merge_mode(const Plan& plan, const PlanOptions& opt, uint64_t blob_bytes) {
+  static const uint64_t gather_max = [] { const char* v = getenv("SDO_GATHER_MAX_BYTES"); return v ? (uint64_t)atoll(v) : (256ull << 10); }();
+  static const uint64_t reduce_max = [] { const char* v = getenv("SDO_REDUCE_MAX_BYTES"); return v ? (uint64_t)atoll(v) : (64ull << 20); }();
+  const bool dense_everywhere = plan.spec.gpu_strategy != "hash" && plan.spec.gpu_strategy != "partition" &&
+                                (plan.n_keys <= opt.global_max_keys || (plan.dev_dims.empty() && plan.n_keys <= (1ull << 31)));
+  if (!dense_everywhere || plan.spec.gpu_shard_merge == "sparse") return ShardMerge::Sparse;
+  if (plan.spec.gpu_shard_merge == "gather") return ShardMerge::Gather;
+  if (plan.spec.gpu_shard_merge == "reduce") return ShardMerge::Reduce;
+  if (blob_bytes <= gather_max) return ShardMerge::Gather;
+  if (blob_bytes <= reduce_max) return ShardMerge::Reduce;
+  return ShardMerge::Sparse;
+}
+
+// One sharded query: scan the local segments, merge the partial aggregates over NCCL, finish.  Everything is queued on
+// one stream by this call.  Three merges (merge algebra of PostAggregate.scala:39-60):
+//  * Gather: small dense tables -- one all-gather of the raw partial blobs (aggregate slots + HLL registers), folded in
+//    rank order on `root` (bit-reproducible);
+//  * Reduce: larger dense tables -- the table is transposed to [slot][key] so that every slot is one contiguous run with
+//    one operator, then one ncclReduce per slot (int64 / float64 sum, int64 min / max) and one uint8 max over the HLL
+//    registers, all in one NCCL group, to `root`;
+//  * Sparse: hash tables and key spaces too large to reduce densely -- every rank turns its groups into (key, slots)
+//    rows, splits them by owner = mix(key) mod world, exchanges them with grouped ncclSend / ncclRecv, merges what it
+//    receives and owns a disjoint share of the groups.  A query that wants the top K by one aggregate takes the top K
+//    of every share, gathers the K * world candidates and finishes on `root`; any other query returns every rank's share
+//    on that rank (*out is non-NULL everywhere; the caller concatenates, as Spark unions partitions).
+Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t turn_no) {
   if (!comm_) throw Invalid("sdo_query_execute_sharded: sdo_engine_comm_init has not been called on this engine");
   if (root < 0 || root >= comm_world_) throw Invalid("sdo_query_execute_sharded: root out of range");
   const double t0 = now_ms();
+  CommTurn turn(this, turn_no);
   std::shared_lock<std::shared_mutex> lk;
   std::shared_ptr<const Plan> plan_ptr = plan_for(json, len, &lk);
   RunningQuery running(this, plan_ptr->spec.query_id);
   // every rank must produce the same table layout even when its own shard has no matching rows: scan zero units
-  Plan empty_variant;
+  Plan variant;
   const Plan* plan = plan_ptr.get();
   if (plan->always_false) {
-    empty_variant = scan_nothing_variant(*plan);
-    plan = &empty_variant;
+    variant = scan_nothing_variant(*plan);
+    plan = &variant;
   }
-  // the same decision on every rank, from the plan alone: dense table + registers within the gather limit
   const uint64_t cells = plan->n_keys * (uint64_t)plan->n_slots;
   const uint64_t blob = round_up(std::max<uint64_t>(cells, 1) * 8, 256) + (plan->n_hll ? plan->n_keys * (uint64_t)plan->n_hll * HLL_M : 0);
-  if (plan->strategy == STRAT_HASH || blob > (4ull << 20))
-    throw Unsupported("sdo_query_execute_sharded handles dense key spaces with at most 4 MB of partial state; use sdo_query_partial for this query");
+  const ShardMerge mode = shard_merge_mode(*plan, opt_, blob);
+  if (mode == ShardMerge::Sparse && plan->n_hll) throw Unsupported("cardinality aggregations over a sparse key space cannot be merged across GPUs");
+  if (mode == ShardMerge::Sparse && plan->strategy != STRAT_HASH && plan->strategy != STRAT_GLOBAL && plan->strategy != STRAT_PARTITION) {
+    // a forced sparse merge of a small key space (tests): the rows come out of a hash table
+    variant = *plan;
+    variant.strategy = STRAT_HASH;
+    plan = &variant;
+  }
   QueryCtx* ctx = acquire_ctx();
   ScanState st;
   st.plan_ms = now_ms() - t0;
   Result* r = nullptr;
-  void* gathered = nullptr;
+  std::vector<void*> temps;  // stream-ordered allocations of this call
+  auto dev_alloc = [&](size_t bytes) {
+    void* p = nullptr;
+    SDO_CUDA(cudaMallocAsync(&p, std::max<size_t>(bytes, 16), ctx->stream));
+    temps.push_back(p);
+    return p;
+  };
   try {
     cudaStream_t s = ctx->stream;
     run_scan(ctx, *plan, &st);
-    st.merged = true;
-    if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
-    gathered = take_scratch(ctx, blob * comm_world_);
-    const bool gathered_in_scratch = gathered != nullptr;
-    if (!gathered) SDO_CUDA(cudaMallocAsync(&gathered, blob * comm_world_, s));
-    {
-      std::lock_guard<std::mutex> g(comm_mu_);
+    const int ns = plan->n_slots;
+    st.shard_merge = mode == ShardMerge::Gather ? "gather" : mode == ShardMerge::Reduce ? "reduce" : "sparse";
+    if (mode != ShardMerge::Sparse) st.merged = true;  // the table will hold other ranks' groups too
+    if (mode == ShardMerge::Gather) {
+      if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
+      void* gathered = take_scratch(ctx, blob * comm_world_);
+      if (!gathered) gathered = dev_alloc(blob * comm_world_);
+      turn.acquire();
       nccl_all_gather_bytes(comm_, st.table, gathered, blob, s);
-    }
-    if (comm_rank_ == root) {
-      launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)plan->n_slots,
-                            plan->n_slots, st.params, st.table, s);
-      st.launches += 1;
-      if (!gathered_in_scratch) SDO_CUDA(cudaFreeAsync(gathered, s));
-      gathered = nullptr;
-      r = finalize(ctx, *plan, &st, t0);
+      if (comm_rank_ == root) {
+        launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)ns, ns, st.params, st.table, s);
+        st.launches += 1;
+        r = finalize(ctx, *plan, &st, t0);
+      } else {
+        SDO_CUDA(cudaStreamSynchronize(s));
+      }
+    } else if (mode == ShardMerge::Reduce) {
+      if (st.dense_blob_bytes != blob) throw std::runtime_error("internal: partial blob size differs from the plan's");
+      unsigned long long* tr = (unsigned long long*)dev_alloc(std::max<uint64_t>(cells, 1) * 8);
+      launch_slot_transpose(st.table, tr, plan->n_keys, ns, true, s);
+      turn.acquire();
+      nccl_group_start();
+      for (int x = 0; x < ns; x++) {
+        const int op = plan->slot_op[x];
+        nccl_reduce(comm_, tr + (uint64_t)x * plan->n_keys, tr + (uint64_t)x * plan->n_keys, plan->n_keys, op == SLOT_SUM_F64 ? NcclType::F64 : NcclType::I64,
+                    op == SLOT_MIN_I64 ? NcclOp::Min : op == SLOT_MAX_I64 ? NcclOp::Max : NcclOp::Sum, root, s);
+      }
+      if (plan->n_hll) nccl_reduce(comm_, st.hll, st.hll, plan->n_keys * (uint64_t)plan->n_hll * HLL_M, NcclType::U8, NcclOp::Max, root, s);
+      nccl_group_end();
+      st.launches += 2;
+      if (comm_rank_ == root) {
+        launch_slot_transpose(tr, st.table, plan->n_keys, ns, false, s);
+        r = finalize(ctx, *plan, &st, t0);
+      } else {
+        SDO_CUDA(cudaStreamSynchronize(s));
+      }
     } else {
-      if (!gathered_in_scratch) SDO_CUDA(cudaFreeAsync(gathered, s));
-      gathered = nullptr;
+      // ---- sparse: rows, split by owner, exchanged, merged ----
+      const int W = comm_world_;
+      if (W > 64) throw Unsupported("the sparse merge handles at most 64 ranks");
+      if (!st.rows_valid) compact_rows(ctx, *plan, &st);
+      const uint64_t n = st.n_rows;
+      unsigned long long* counts = (unsigned long long*)dev_alloc((2 * 64 + 64 * 64) * 8);  // [0,64) counts, [64,128) cursors, then every rank's counts
+      SDO_CUDA(cudaMemsetAsync(counts, 0, 2 * 64 * 8, s));
+      launch_partition_rows(st.rows_keys, st.rows_slots, n, ns, W, nullptr, nullptr, counts, nullptr, s);
+      turn.acquire();
+      unsigned long long* all_counts = counts + 128;
+      nccl_all_gather_bytes(comm_, counts, all_counts, 64 * 8, s);
+      std::vector<unsigned long long> h((size_t)64 * W);
+      SDO_CUDA(cudaMemcpyAsync(h.data(), all_counts, h.size() * 8, cudaMemcpyDeviceToHost, s));
       SDO_CUDA(cudaStreamSynchronize(s));
+      st.d2h_bytes += h.size() * 8;
+      unsigned long long cur[64] = {0}, send_off[65] = {0}, recv_off[65] = {0};
+      for (int d = 0; d < W; d++) send_off[d + 1] = send_off[d] + h[(size_t)comm_rank_ * 64 + d];   // rows this rank sends to d
+      for (int src = 0; src < W; src++) recv_off[src + 1] = recv_off[src] + h[(size_t)src * 64 + comm_rank_];  // rows src sends here
+      if (send_off[W] != n) throw std::runtime_error("internal: partition counts do not add up");
+      for (int d = 0; d < W; d++) cur[d] = send_off[d];
+      SDO_CUDA(cudaMemcpyAsync(counts + 64, cur, (size_t)W * 8, cudaMemcpyHostToDevice, s));
+      unsigned long long* pk = (unsigned long long*)dev_alloc(std::max<uint64_t>(n, 1) * 8);
+      unsigned long long* ps = (unsigned long long*)dev_alloc(std::max<uint64_t>(n, 1) * ns * 8);
+      launch_partition_rows(st.rows_keys, st.rows_slots, n, ns, W, pk, ps, counts, counts + 64, s);
+      const uint64_t m = recv_off[W];
+      unsigned long long* rk = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * 8);
+      unsigned long long* rs = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * ns * 8);
+      nccl_group_start();
+      for (int p = 0; p < W; p++) {
+        const uint64_t sn = send_off[p + 1] - send_off[p], rn = recv_off[p + 1] - recv_off[p];
+        if (p == comm_rank_) {
+          if (sn != rn) throw std::runtime_error("internal: self exchange counts differ");
+          if (sn) {
+            SDO_CUDA(cudaMemcpyAsync(rk + recv_off[p], pk + send_off[p], sn * 8, cudaMemcpyDeviceToDevice, s));
+            SDO_CUDA(cudaMemcpyAsync(rs + recv_off[p] * ns, ps + send_off[p] * ns, sn * ns * 8, cudaMemcpyDeviceToDevice, s));
+          }
+          continue;
+        }
+        if (sn) {
+          nccl_send_bytes(comm_, pk + send_off[p], sn * 8, p, s);
+          nccl_send_bytes(comm_, ps + send_off[p] * ns, sn * ns * 8, p, s);
+        }
+        if (rn) {
+          nccl_recv_bytes(comm_, rk + recv_off[p], rn * 8, p, s);
+          nccl_recv_bytes(comm_, rs + recv_off[p] * ns, rn * ns * 8, p, s);
+        }
+      }
+      nccl_group_end();
+      st.launches += 3;
+      st.exchange_bytes = (n - (send_off[comm_rank_ + 1] - send_off[comm_rank_])) * (uint64_t)(ns + 1) * 8;
+      merge_received_rows(ctx, *plan, &st, rk, rs, m);  // this rank's share, as rows
+      // top K by one aggregate: K candidates per share, gathered, finished on root
+      int tk_slot = -1, tk_f64 = 0, tk_desc = 1;
+      int64_t k_want = 0;
+      if (topk_request(*plan, &tk_slot, &tk_f64, &tk_desc, &k_want)) {
+        const int k = (int)k_want;
+        unsigned long long* cand_k = (unsigned long long*)dev_alloc((size_t)k * 8 * W);
+        unsigned long long* cand_s = (unsigned long long*)dev_alloc((size_t)k * ns * 8 * W);
+        unsigned long long* mine_k = (unsigned long long*)dev_alloc((size_t)k * 8);
+        unsigned long long* mine_s = (unsigned long long*)dev_alloc((size_t)k * ns * 8);
+        if (st.n_rows > (uint64_t)k) {
+          const size_t se = topk_scratch_elems(st.n_rows, k);
+          unsigned long long *sa = (unsigned long long*)dev_alloc(se * 8), *sb = (unsigned long long*)dev_alloc(se * 8), *oi = (unsigned long long*)dev_alloc((size_t)k * 8);
+          launch_topk(st.rows_keys, st.rows_slots, st.n_rows, ns, tk_slot, tk_f64, tk_desc, k, sa, sb, oi, s);
+          launch_gather_rows(st.rows_keys, st.rows_slots, oi, (uint64_t)k, ns, mine_k, mine_s, s);
+          st.launches += 2;
+        } else {
+          // fewer groups than K: all of them, padded with the empty key
+          SDO_CUDA(cudaMemsetAsync(mine_k, 0xff, (size_t)k * 8, s));
+          SDO_CUDA(cudaMemsetAsync(mine_s, 0, (size_t)k * ns * 8, s));
+          if (st.n_rows) {
+            SDO_CUDA(cudaMemcpyAsync(mine_k, st.rows_keys, st.n_rows * 8, cudaMemcpyDeviceToDevice, s));
+            SDO_CUDA(cudaMemcpyAsync(mine_s, st.rows_slots, st.n_rows * ns * 8, cudaMemcpyDeviceToDevice, s));
+          }
+        }
+        nccl_group_start();
+        nccl_all_gather_bytes(comm_, mine_k, cand_k, (size_t)k * 8, s);
+        nccl_all_gather_bytes(comm_, mine_s, cand_s, (size_t)k * ns * 8, s);
+        nccl_group_end();
+        if (comm_rank_ == root) {
+          // the candidates replace the share: finalize orders them on the host and cuts at K
+          SDO_CUDA(cudaFreeAsync(st.rows_keys, s));
+          SDO_CUDA(cudaFreeAsync(st.rows_slots, s));
+          st.rows_keys = st.rows_slots = nullptr;
+          SDO_CUDA(cudaMallocAsync((void**)&st.rows_keys, (size_t)k * 8 * W, s));
+          SDO_CUDA(cudaMallocAsync((void**)&st.rows_slots, (size_t)k * ns * 8 * W, s));
+          SDO_CUDA(cudaMemcpyAsync(st.rows_keys, cand_k, (size_t)k * 8 * W, cudaMemcpyDeviceToDevice, s));
+          SDO_CUDA(cudaMemcpyAsync(st.rows_slots, cand_s, (size_t)k * ns * 8 * W, cudaMemcpyDeviceToDevice, s));
+          st.n_rows = (uint64_t)k * W;
+          r = finalize(ctx, *plan, &st, t0);
+        } else {
+          SDO_CUDA(cudaStreamSynchronize(s));
+        }
+      } else {
+        r = finalize(ctx, *plan, &st, t0);  // this rank's share of the groups
+      }
     }
+    for (void* p : temps) cudaFreeAsync(p, s);
+    temps.clear();
   } catch (...) {
     cudaStreamSynchronize(ctx->stream);
-    if (gathered && !((char*)gathered >= ctx->scratch && (char*)gathered < ctx->scratch + ctx->scratch_bytes)) cudaFreeAsync(gathered, ctx->stream);
+    for (void* p : temps) cudaFreeAsync(p, ctx->stream);
     free_state(ctx, &st);
     release_ctx(ctx);
     throw;
@@ -1627,6 +1813,55 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root) {
   free_state(ctx, &st);
   release_ctx(ctx);
   return r;
+}
+
+// Which single aggregate a query wants the top K groups of (TopN with a numeric metric, or a limitSpec over one
+// aggregate column; K <= 1024, no having): the shapes a device top-k serves.
+bool Engine::topk_request(const Plan& plan, int* slot, int* is_f64, int* desc_out, int64_t* k_want) {
+  const QuerySpec& q = plan.spec;
+  if (q.has_having || plan.n_hll) return false;
+  std::string col;
+  bool desc = true;
+  int64_t k = 0;
+  if (q.type == QuerySpec::TopN && q.metric.kind == TopNMetric::Numeric) { col = q.metric.metric; desc = !q.metric.inverted; k = q.threshold; }
+  else if (q.type == QuerySpec::GroupBy && q.limit.present && q.limit.columns.size() == 1) { col = q.limit.columns[0].dimension; desc = !q.limit.columns[0].ascending; k = q.limit.limit; }
+  if (col.empty() || k <= 0 || k > 1024) return false;
+  for (auto& a : plan.aggs)
+    if (a.name == col && a.hll_index < 0 && !a.const_times_count) {
+      *slot = a.slot;
+      *is_f64 = (a.kind == AggregationSpec::DoubleSum) ? 1 : 0;  // min / max doubles are already order-preserving ints
+      *desc_out = desc ? 1 : 0;
+      *k_want = k;
+      return true;
+    }
+  return false;
+}
+
+// Fold (key, slots) rows received from other ranks (and this rank's own) into one group per key: a fresh hash table
+// sized for the rows, then compaction back to rows.  Leaves st->rows_* = this rank's share.
+void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n) {
+  cudaStream_t s = ctx->stream;
+  const int ns = plan.n_slots;
+  for (void* q : {(void*)st->table, (void*)st->hkeys, (void*)st->rows_keys, (void*)st->rows_slots})
+    if (q && !((char*)q >= ctx->scratch && (char*)q < ctx->scratch + ctx->scratch_bytes)) SDO_CUDA(cudaFreeAsync(q, s));
+  st->table = nullptr; st->hkeys = nullptr; st->rows_keys = nullptr; st->rows_slots = nullptr;
+  st->table_preinit = false;
+  const uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, n + n / 2));
+  const uint32_t stride = (uint32_t)pow2_ceil((uint64_t)ns + 1);
+  SDO_CUDA(cudaMallocAsync((void**)&st->table, cap * (uint64_t)stride * 8, s));
+  st->params.hkeys = st->table;
+  st->params.hmask = cap - 1;
+  st->params.hstride = stride;
+  st->params.table = st->table;
+  st->table_rows = cap;
+  st->strategy = STRAT_HASH;
+  SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
+  launch_fill_hash(st->table, cap, stride, ns, st->params, s);
+  launch_merge_rows(keys, slots, n, st->params, s);
+  st->launches += 2;
+  st->rows_valid = false;
+  st->merged = true;
+  compact_rows(ctx, plan, st);
 }
 
 Partial* Engine::partial(const char* json, size_t len) {
@@ -1730,30 +1965,7 @@ void Engine::partial_merge_rows(Partial* p, const void* keys, const void* slots,
   if (!p->st.rows_valid) throw Invalid("sdo_partial_merge_rows applies to sparse partials only");
   if (p->plan.n_hll) throw Unsupported("cardinality aggregations cannot be merged on the sparse path");
   SDO_CUDA(cudaSetDevice(device_));
-  cudaStream_t s = p->ctx->stream;
-  ScanState& st = p->st;
-  const int ns = p->plan.n_slots;
-  // fresh table sized for the received rows
-  for (void* q : {(void*)st.table, (void*)st.hkeys, (void*)st.rows_keys, (void*)st.rows_slots})
-    if (q) SDO_CUDA(cudaFreeAsync(q, s));
-  st.table = nullptr; st.hkeys = nullptr; st.rows_keys = nullptr; st.rows_slots = nullptr;
-  uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, (uint64_t)n + (uint64_t)n / 2));
-  const uint32_t stride = (uint32_t)pow2_ceil((uint64_t)ns + 1);
-  SDO_CUDA(cudaMallocAsync((void**)&st.table, cap * (uint64_t)stride * 8, s));
-  st.params.hkeys = st.table;
-  st.params.hmask = cap - 1;
-  st.params.hstride = stride;
-  st.params.table = st.table;
-  st.table_rows = cap;
-  st.strategy = STRAT_HASH;
-  SDO_CUDA(cudaMemsetAsync(p->ctx->counters, 0, COUNTER_BYTES, s));
-  launch_fill_hash(st.table, cap, stride, ns, st.params, s);
-  launch_merge_rows((const unsigned long long*)keys, (const unsigned long long*)slots, (uint64_t)n, st.params, s);
-  st.launches += 2;
-  st.rows_valid = false;
-  // rows_scanned bounds the compaction buffer
-  p->plan.rows_scanned = std::max<int64_t>(p->plan.rows_scanned, n);
-  compact_rows(p->ctx, p->plan, &st);
+  merge_received_rows(p->ctx, p->plan, &p->st, (const unsigned long long*)keys, (const unsigned long long*)slots, (uint64_t)n);
 }
 
 Result* Engine::partial_finish(Partial* p) {

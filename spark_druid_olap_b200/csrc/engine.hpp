@@ -4,6 +4,7 @@
 // kernels on its HBM-resident segments and returns a columnar result.
 #pragma once
 #include <atomic>
+#include <condition_variable>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -102,6 +103,8 @@ struct ScanState {
   double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
   bool rows_valid = false;
+  const char* shard_merge = nullptr;  // sharded execution: which merge ran (gather / reduce / sparse)
+  uint64_t exchange_bytes = 0;        // sparse merge: bytes of rows this rank sent to other ranks
 };
 
 class Engine;
@@ -126,7 +129,12 @@ class Engine {
   void cancel(const std::string& query_id);
   // sharded execution with the merge inside the library (dense key spaces, small tables)
   void comm_init(const void* id, int rank, int world);
-  Result* execute_sharded(const char* json, size_t len, int root);
+  // turn >= 0: this query's position in the communicator's collective order (same on every rank, consecutive from 0)
+  Result* execute_sharded(const char* json, size_t len, int root, int64_t turn = -1);
+  int64_t next_turn() {
+    std::lock_guard<std::mutex> lk(turn_mu_);
+    return next_turn_;
+  }
   Partial* partial(const char* json, size_t len);
   void partial_view(Partial* p, void* view_out);
   void partial_export(Partial* p, void* dst_dev, int64_t dst_bytes);
@@ -157,7 +165,15 @@ class Engine {
   PinnedPool pinned_pool_;
   void* comm_ = nullptr;  // ncclComm_t of this engine's rank (sdo_engine_comm_init)
   int comm_rank_ = 0, comm_world_ = 1;
-  std::mutex comm_mu_;    // collectives of one communicator must be issued in the same order on every rank
+  // collectives of one communicator must be issued in the same order on every rank: one query at a time holds the turn
+  struct CommTurn;
+  std::mutex turn_mu_;
+  std::condition_variable turn_cv_;
+  bool turn_busy_ = false;
+  int64_t next_turn_ = 0;
+  std::mutex comm_mu_;
+  static bool topk_request(const Plan& plan, int* slot, int* is_f64, int* desc, int64_t* k_want);
+  void merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n);
   Result* finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
 
   QueryCtx* acquire_ctx();

@@ -598,6 +598,23 @@ __global__ void merge_gathered_kernel(const unsigned long long* __restrict__ gat
     }
   }
 }
+// dense tables are [key][slot]; a collective reduction wants one operator over a contiguous run: [slot][key] and back
+__global__ void slot_transpose_kernel(const unsigned long long* __restrict__ in, unsigned long long* __restrict__ out, uint64_t n_keys, int ns, int to_slot_major) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x, n = n_keys * (uint64_t)ns;
+  for (; i < n; i += step) {
+    // i walks the OUTPUT so that writes are coalesced
+    if (to_slot_major) { const uint64_t s = i / n_keys, k = i - s * n_keys; out[i] = in[k * ns + s]; }
+    else { const uint64_t k = i / ns, s = i - k * ns; out[i] = in[s * n_keys + k]; }
+  }
+}
+void launch_slot_transpose(const unsigned long long* in, unsigned long long* out, uint64_t n_keys, int n_slots, bool to_slot_major, cudaStream_t st) {
+  const uint64_t n = n_keys * (uint64_t)n_slots;
+  if (!n) return;
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 16);
+  slot_transpose_kernel<<<grid, 256, 0, st>>>(in, out, n_keys, n_slots, to_slot_major ? 1 : 0);
+  SDO_CUDA(cudaGetLastError());
+}
 void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size_t blob_bytes, size_t table_bytes, uint64_t cells, int n_slots,
                            const ScanParams& p, unsigned long long* table, cudaStream_t st) {
   const uint64_t words = blob_bytes / 8;

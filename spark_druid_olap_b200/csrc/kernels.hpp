@@ -133,6 +133,8 @@ enum Strategy : int32_t {
   STRAT_SPAN = 4,   // no grouping dimension (timeseries): the key is constant over a span, so a thread keeps private
                     // accumulators for its warp's current key only and the warp merges them into the direct-indexed
                     // HBM table when it moves to another key -- no atomics, votes or shuffles per row
+  STRAT_PARTITION = 5,  // high-cardinality keys: rows are first split by key range into windows whose slice of the direct
+                        // table stays in L2, then aggregated window by window (partition_kernels.cu); never a scan_kernel<>
 };
 
 struct ScanParams {
@@ -241,6 +243,8 @@ void launch_partition_rows(const unsigned long long* keys, const unsigned long l
 // dense multi-GPU merge: fold n_ranks gathered blobs (table + HLL registers each) into this rank's table
 void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size_t blob_bytes, size_t table_bytes, uint64_t cells, int n_slots,
                            const ScanParams& p, unsigned long long* table, cudaStream_t st);
+// [key][slot] <-> [slot][key] (the layout a per-slot ncclReduce needs)
+void launch_slot_transpose(const unsigned long long* in, unsigned long long* out, uint64_t n_keys, int n_slots, bool to_slot_major, cudaStream_t st);
 void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
 
 // select queries: per-unit counts of passing rows; then, for the units that hold the wanted page, the passing rows with

@@ -426,6 +426,9 @@ QuerySpec parse_query_spec(const Json& j) {
       throw Invalid("context.gpuTicketRows must be 512, 1024, 2048 or 4096");
     q.gpu_hll_place = c->get_str("gpuHllPlace", "");
     if (!q.gpu_hll_place.empty() && q.gpu_hll_place != "global" && q.gpu_hll_place != "shared") throw Invalid("context.gpuHllPlace must be 'global' or 'shared'");
+    q.gpu_shard_merge = c->get_str("gpuShardMerge", "");
+    if (!q.gpu_shard_merge.empty() && q.gpu_shard_merge != "gather" && q.gpu_shard_merge != "reduce" && q.gpu_shard_merge != "sparse")
+      throw Invalid("context.gpuShardMerge must be 'gather', 'reduce' or 'sparse'");
     if (c->has("gpuJit")) q.gpu_jit = c->get_bool("gpuJit", false) ? 1 : 0;
     if (const Json* tb = c->find("gpuTimeBoundary")) {
       if (!tb->is_arr() || tb->arr.size() != 2 || !tb->arr[0].is_num() || !tb->arr[1].is_num()) throw Invalid("context.gpuTimeBoundary must be [minMs, maxMs]");

@@ -124,6 +124,7 @@ struct QuerySpec {
   std::string gpu_strategy;  // context.gpuStrategy: force lane|block|global|hash (tests)
   int gpu_ticket_rows = 0;   // context.gpuTicketRows: 512 | 1024 | 2048 | 4096 rows per warp ticket (tests, profiling); 0 = by shape
   std::string gpu_hll_place; // context.gpuHllPlace: force the HLL registers into global|shared memory (tests, profiling)
+  std::string gpu_shard_merge;  // context.gpuShardMerge: force the cross-GPU merge of a sharded query: gather | reduce | sparse (tests)
   int gpu_jit = -1;          // context.gpuJit: true / false force the run-time specialised kernel on / off (-1 = engine decides)
   // context.gpuTimeBoundary = [minMs, maxMs]: the datasource's time range over ALL shards, set by the
   // sharded host layer so that every rank numbers time-derived keys the same way

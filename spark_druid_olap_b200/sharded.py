@@ -1,17 +1,18 @@
-"""Sharded execution: one engine (process) per GPU, partial aggregates merged over NCCL.
+"""Sharded execution: one engine (process) per GPU, partial aggregates merged over NCCL INSIDE the library.
 
 Replaces what the reference does when it queries historicals directly: one partial query per
 (server, segment group) partition (DruidRDD.scala:244-269) and a Spark-side re-aggregation of the
 partials (sources/druid/DruidStrategy.scala:353-359) with the merge algebra of
 sources/druid/PostAggregate.scala:39-60 (count/sum -> sum, min -> min, max -> max; HLL -> register max).
 
-Dense key spaces: every rank holds the same fixed-layout table, so the merge is an all-reduce per
-slot class (int64 sum, float64 sum, int64 min, int64 max) plus a uint8 max for HLL registers.
-Sparse key spaces: rows are split by owner = mix(key) % world, exchanged with one all-to-all, and
-merged into the owner's hash table; every rank then finishes its disjoint share.
-
-The tensor-level functions work on any device/backend (the CPU tests drive them over gloo);
-execute_sharded binds them to an engine's device buffers without copies.
+This module is set-up glue around the C ABI, which a JVM host would do the same way over its own channel:
+  * align_datasource: give every rank the same id space (sdo_dimension_dictionary / sdo_dimension_extend);
+  * global_time_boundary / prepare_query: number time-derived keys on one grid (context.gpuTimeBoundary);
+  * init_comm: hand every engine the NCCL unique id (sdo_comm_unique_id / sdo_engine_comm_init);
+  * execute_sharded: ONE call, sdo_query_execute_sharded[_at] -- scan, merge (all-gather + fold, per-slot
+    ncclReduce, or hash-partitioned ncclSend / ncclRecv exchange) and finish are queued by the library.
+torch.distributed is used for the set-up steps only (an object all-gather of dictionaries, a max over time
+boundaries, the broadcast of the unique id); no collective of a query goes through it.
 """
 import json
 import os
@@ -21,74 +22,8 @@ import torch.distributed as dist
 
 import spark_druid_olap_b200 as sdo
 
-SLOT_SUM_I64, SLOT_SUM_F64, SLOT_MIN_I64, SLOT_MAX_I64 = 0, 1, 2, 3
-
-
-class _DevArray:
-    """Zero-copy view of engine-owned device memory for torch (CUDA array interface)."""
-
-    def __init__(self, ptr, nbytes):
-        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 2}
-
-
-def device_bytes(ptr, nbytes, device):
-    return torch.as_tensor(_DevArray(ptr, nbytes), device=device)
-
-
-def merge_dense_table(table, slot_ops, group=None):
-    """All-reduce a [n_keys, n_slots] int64-typed table in place, one collective per slot class."""
-    n_slots = table.shape[1]
-    assert len(slot_ops) == n_slots
-    for op, red, as_float in ((SLOT_SUM_I64, dist.ReduceOp.SUM, False), (SLOT_SUM_F64, dist.ReduceOp.SUM, True),
-                              (SLOT_MIN_I64, dist.ReduceOp.MIN, False), (SLOT_MAX_I64, dist.ReduceOp.MAX, False)):
-        cols = [i for i, o in enumerate(slot_ops) if o == op]
-        if not cols:
-            continue
-        buf = table[:, cols].contiguous()
-        if as_float:
-            fb = buf.view(torch.float64)
-            dist.all_reduce(fb, op=red, group=group)
-        else:
-            dist.all_reduce(buf, op=red, group=group)
-        table[:, cols] = buf
-    return table
-
-
-def merge_hll(registers, group=None):
-    """Register-wise max of HLL++ sketches (uint8), in place."""
-    dist.all_reduce(registers, op=dist.ReduceOp.MAX, group=group)
-    return registers
-
-
-def exchange_sparse(keys, slots, counts, group=None):
-    """All-to-all of (key, slots) rows already grouped by destination rank.
-    keys [n] int64, slots [n, n_slots] int64, counts: rows per destination.  Returns (keys, slots) received."""
-    world = dist.get_world_size(group)
-    dev = keys.device
-    send = torch.tensor(counts, dtype=torch.int64, device=dev)
-    recv = torch.empty(world, dtype=torch.int64, device=dev)
-    dist.all_to_all_single(recv, send, group=group)
-    rc = [int(x) for x in recv.tolist()]
-    n_slots = slots.shape[1]
-    rkeys = torch.empty(sum(rc), dtype=torch.int64, device=dev)
-    dist.all_to_all_single(rkeys, keys, output_split_sizes=rc, input_split_sizes=list(counts), group=group)
-    rslots = torch.empty((sum(rc), n_slots), dtype=torch.int64, device=dev)
-    dist.all_to_all_single(rslots, slots.contiguous(), output_split_sizes=rc, input_split_sizes=list(counts), group=group)
-    return rkeys, rslots
-
-
 _boundary_cache = {}
 _aligned = set()
-_buffers = {}
-GATHER_MAX_BYTES = 4 << 20  # dense partials up to this size are merged by all-gather + one fold kernel
-
-
-def _gather_buffers(dev, nbytes, world):
-    """Reusable (local, gathered) byte tensors for the small-table merge."""
-    key = (dev.index, nbytes, world)
-    if key not in _buffers:
-        _buffers[key] = (torch.empty(nbytes, dtype=torch.uint8, device=dev), torch.empty(nbytes * world, dtype=torch.uint8, device=dev))
-    return _buffers[key]
 
 
 def align_datasource(engine, datasource, group=None, force=False):
@@ -190,71 +125,23 @@ def prepare_query(engine, query, group=None):
     return _prepared[key]
 
 
-def execute_sharded(engine, query, group=None, root=0, force_exchange=False):
-    """Run `query` over every rank's local segments and return the merged Result on `root`
-    (dense key spaces) or this rank's share of the groups (sparse key spaces; see `sparse` flag).
-    Returns (result_or_None, info)."""
+def execute_sharded(engine, query, group=None, root=0, turn=None):
+    """Run `query` over every rank's local segments with the merge inside the library (sdo_query_execute_sharded).
+    Returns (result_or_None, info).  Dense key spaces and top-K queries: the merged result on `root`, None elsewhere.
+    Sparse key spaces without a top-K: every rank gets its disjoint share of the groups (the caller unions them, as Spark
+    unions partitions).  `turn` (>= 0, the same on every rank, consecutive per engine) orders the collectives of queries
+    that run concurrently on one engine; None = the caller issues sharded queries one at a time, in the same order."""
     import ctypes as C
-    world = dist.get_world_size(group)
-    rank = dist.get_rank(group)
-    if world > 1:
-        query = prepare_query(engine, query, group)
-        if _comms.get(id(engine)) == (world, id(group)) and not force_exchange:
-            # merge inside the library: scan + NCCL all-gather + fold queued by one C call
-            out = C.c_void_p()
-            status = sdo.lib().sdo_query_execute_sharded(engine._h, query, len(query), root, C.byref(out))
-            if status == sdo.SDO_OK:
-                return (sdo.Result(out) if rank == root else None), {"dense": True, "native": True, "n_keys": -1, "n_slots": -1, "merge_bytes": -1}
-            if status != sdo.SDO_UNSUPPORTED or b"sdo_query_partial" not in sdo.lib().sdo_last_error():
-                sdo._check(status)
-            # a shape for the host-side merge below (every rank takes the same branch: the decision is made from the plan)
-    part = engine.partial(query)
-    try:
-        v = part.view()
-        dev = torch.device("cuda", engine.device)
-        stream = torch.cuda.ExternalStream(part.stream(), device=dev)
-        info = {"dense": bool(v.dense), "n_keys": int(v.n_keys), "n_slots": int(v.n_slots), "merge_bytes": 0}
-        with torch.cuda.stream(stream):
-            if v.dense and (world > 1 or force_exchange) and 0 < v.blob_bytes <= GATHER_MAX_BYTES:
-                # small table: one all-gather of the raw blobs (any mix of sum / min / max slots and HLL registers),
-                # folded in rank order by one kernel on the root
-                nb = int(v.blob_bytes)
-                local, gathered = _gather_buffers(dev, nb, world)
-                part.export(local.data_ptr(), nb)
-                dist.all_gather_into_tensor(gathered, local, group=group)
-                info["merge_bytes"] += nb * (world - 1)
-                if rank == root:
-                    part.merge_gathered(gathered.data_ptr(), world)
-                    return part.finish(), info
-                stream.synchronize()
-                return None, info
-            if v.dense:
-                ops = [v.slot_ops[i] for i in range(v.n_slots)]
-                if world > 1 and v.n_keys > 0:
-                    nb = v.n_keys * v.n_slots * 8
-                    table = device_bytes(v.slots, nb, dev).view(torch.int64).view(v.n_keys, v.n_slots)
-                    merge_dense_table(table, ops, group)
-                    info["merge_bytes"] += nb
-                    if v.n_hll and v.hll:
-                        hb = v.n_keys * v.n_hll * 512
-                        merge_hll(device_bytes(v.hll, hb, dev), group)
-                        info["merge_bytes"] += hb
-                stream.synchronize()
-                if rank == root:
-                    return part.finish(), info
-                return None, info
-            # sparse: hash-partitioned all-to-all, every rank keeps the groups it owns
-            # (force_exchange runs the partition / exchange / merge steps even on one rank: tests)
-            if world > 1 or force_exchange:
-                counts = part.partition(world)
-                v = part.view()
-                n = int(v.n_keys)
-                keys = device_bytes(v.keys, max(n, 1) * 8, dev).view(torch.int64)[:n]
-                slots = device_bytes(v.slots, max(n, 1) * v.n_slots * 8, dev).view(torch.int64)[:n * v.n_slots].view(n, v.n_slots)
-                rkeys, rslots = exchange_sparse(keys, slots, counts, group)
-                info["merge_bytes"] += (n - counts[rank]) * (1 + v.n_slots) * 8
-                stream.synchronize()
-                part.merge_rows(rkeys.data_ptr(), rslots.data_ptr(), int(rkeys.shape[0]))
-            return part.finish(), info
-    finally:
-        part.free()
+    if id(engine) not in _comms:
+        init_comm(engine, group)
+    qb = prepare_query(engine, query, group)
+    out = C.c_void_p()
+    L = sdo.lib()
+    if turn is None:
+        sdo._check(L.sdo_query_execute_sharded(engine._h, qb, len(qb), root, C.byref(out)))
+    else:
+        sdo._check(L.sdo_query_execute_sharded_at(engine._h, qb, len(qb), root, int(turn), C.byref(out)))
+    if not out:
+        return None, {"native": True, "merge": None}
+    res = sdo.Result(out)
+    return res, {"native": True, "merge": res.stats.get("shardMerge"), "merge_bytes": res.stats.get("exchangeBytes", 0)}

@@ -24,7 +24,7 @@ def oracle_table(flat_tables):
     if not isinstance(flat_tables, (list, tuple)):
         flat_tables = [flat_tables]
     t0 = flat_tables[0]
-    cat = lambda c: np.concatenate([t.data[c] for t in flat_tables])
+    cat = (lambda c: t0.data[c]) if len(flat_tables) == 1 else (lambda c: np.concatenate([t.data[c] for t in flat_tables]))  # one shard: no copy
     dims, metrics = {}, {}
     for c, k in t0.kinds.items():
         if k == tpch.KIND_STR_DIM:

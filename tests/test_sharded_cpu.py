@@ -1,5 +1,5 @@
-"""Host-side merge logic of the sharded path on 2 ranks over gloo (CPU): the same tensor functions the GPU path
-runs over NCCL.  Mirrors the reference's broker-vs-historical equivalence test (HistoricalServerTest.scala:177-230):
+"""Host-side merge logic (tests/host_merge.py) on 2 ranks over gloo (CPU): the merge algebra the library applies over NCCL,
+stated with tensors.  Mirrors the reference's broker-vs-historical equivalence test (HistoricalServerTest.scala:177-230):
 N per-shard partial queries + merge must equal the one merged query."""
 import json
 import os
@@ -32,7 +32,8 @@ def _worker(rank, world, port, tmp):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
-    from spark_druid_olap_b200 import sharded, tpch
+    import host_merge as sharded
+    from spark_druid_olap_b200 import tpch
     cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "ps_availqty", "o_custkey", "o_orderkey", "count"]
     mine = H.oracle_table(tpch.FlatTable(SF, cols, rank, world))
     whole = H.oracle_table([tpch.FlatTable(SF, cols, r, world) for r in range(world)])

@@ -43,51 +43,40 @@ else:
     eng.load("tpch", mine.engine_columns(), partition=rank)
     whole = H.oracle_table([tpch.FlatTable(sf, cols, r, world) for r in range(world)])
 ok = True
-# second pass: the same dense shapes with the merge inside the library (sdo_query_execute_sharded)
-passes = [("host-merge", False), ("native-merge", True)]
-for pass_name, native in passes:
-  if native:
+import host_merge  # noqa: E402
+# two passes: the host-side merge over the partial API (tests/host_merge.py), then the merge inside the library
+for pass_name in ("host-merge", "library"):
+  if pass_name == "library":
     sharded.init_comm(eng)
   for name, spec, ordered in [("q1", Q.q1_style(), False), ("q1_block", Q.q1_style("block"), False), ("ts_month_hll", Q.timeseries("P1M"), False),
                               ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
-                              ("by_orderkey_global", Q.by_orderkey("global"), False), ("q3", Q.q3(), False)] * int(os.environ.get("CHECK_REPEAT", "1")):
+                              ("by_orderkey_global", Q.by_orderkey("global"), False), ("by_orderkey", Q.by_orderkey(), False), ("q3", Q.q3(), False),
+                              ("q3_limit10", Q.q3(10), True), ("q1_reduce", Q.q1_style(), False), ("ts_day_reduce", Q.timeseries("P1D"), False),
+                              ("q5_sparse", Q.q5(), False)] * int(os.environ.get("CHECK_REPEAT", "1")):
       if os.environ.get("CHECK_ONLY") and name not in os.environ["CHECK_ONLY"].split(","):
           continue
       q = json.loads(spec.to_json())
-      print(f'[rank {rank}] {name} ...', flush=True)
-      res, info = sharded.execute_sharded(eng, q)
-      print(f'[rank {rank}] {name} engine done', flush=True)
+      if name.endswith("_reduce") or name.endswith("_sparse"):
+          if pass_name != "library":
+              continue
+          q["context"] = dict(q.get("context") or {"queryId": name}, gpuShardMerge=name.rsplit("_", 1)[1])
+      if pass_name == "host-merge" and name == "q3_limit10":
+          continue  # the host-side merge returns per-rank shares; a limit applies per share there
+      res, info = (sharded.execute_sharded(eng, q) if pass_name == "library" else host_merge.execute_host_merge(eng, q))
       want = orc.execute(whole, q)
+      # dense merges and top-K queries end on rank 0, sparse merges leave every rank a disjoint share: compare the union
+      parts = [None] * world
+      dist.all_gather_object(parts, H.engine_rows(res) if res is not None else [])
       try:
-          if info["dense"]:
-              if rank == 0:
-                  H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered, what=name)
-          else:
-              # sparse: every rank holds a disjoint share; gather and compare the union
-              parts = [None] * world
-              rows_here = H.engine_rows(res)
-              cnt_col = [k for k in rows_here[0] if k in ('n',)] if rows_here else []
-              print(f'[rank {rank}] {name}: {len(rows_here)} result rows, sum n = {sum(r[cnt_col[0]] for r in rows_here) if cnt_col else None}, local rows {mine.n_rows}, info {info}', flush=True)
-              dist.all_gather_object(parts, rows_here)
-              if rank == 0:
-                  allrows = [r for p in parts for r in p]
-                  keys = [r.get('o_orderkey') for r in allrows]
-                  print(f'union {len(allrows)} rows, distinct keys {len(set(keys))}, want {len(want)}', flush=True)
-                  H.assert_rows_equal(allrows, want, what=name)
           if rank == 0:
-              print(f"OK   {name:22s} [{pass_name}{' in library' if info.get('native') else ''}] dense={info['dense']} keys={info['n_keys']} merge_bytes={info['merge_bytes']}")
+              holders = sum(1 for p in parts if p)
+              allrows = [r for p in parts for r in p]
+              H.assert_rows_equal(allrows, want, ordered=ordered and holders <= 1, what=name)
+              print(f"OK   {name:22s} [{pass_name}] merge={info.get('merge', 'dense' if info.get('dense') else 'sparse')} rows={len(allrows)} from {holders} rank(s) "
+                    f"bytes={info.get('merge_bytes')}", flush=True)
       except AssertionError as e:
           ok = False
-          print(f"FAIL {name} [{pass_name}] rank {rank}: {e}")
-          if rank == 0 and info["dense"] and res is not None:
-              # what differs: groups only on one side, and groups whose exact columns differ
-              got_rows = H.engine_rows(res)
-              dim = [k for k in want[0] if isinstance(want[0][k], str)]
-              gk = {tuple(r[d] for d in dim): r for r in got_rows}
-              wk = {tuple(r[d] for d in dim): r for r in want}
-              only_g, only_w = sorted(set(gk) - set(wk))[:5], sorted(set(wk) - set(gk))[:5]
-              diff = [(k, gk[k], wk[k]) for k in sorted(set(gk) & set(wk)) if any(gk[k][c] != wk[k][c] for c in wk[k] if not isinstance(wk[k][c], float))][:5]
-              print(f"  rows got {len(got_rows)} want {len(want)}; only in result {only_g}; only in oracle {only_w}; exact-column mismatches {diff}", flush=True)
+          print(f"FAIL {name} [{pass_name}] rank {rank}: {e}", flush=True)
 flag = torch.tensor([0 if ok else 1], device="cuda")
 dist.all_reduce(flag)
 if rank == 0:
