@@ -15,7 +15,7 @@ CSRC = os.path.join(HERE, "csrc")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 
-ENGINE_SRCS = ["kernels.cu", "noalloc.cu", "jit.cpp", "comm.cpp", "minijs.cpp", "spec.cpp", "store.cpp", "plan.cpp", "engine.cpp", "capi.cpp"]
+ENGINE_SRCS = ["kernels.cu", "select_kernels.cu", "noalloc.cu", "jit.cpp", "comm.cpp", "minijs.cpp", "spec.cpp", "store.cpp", "plan.cpp", "engine.cpp", "capi.cpp"]
 ENGINE_HDRS = ["scan_kernel.cuh", "jit.hpp", "common.hpp", "json.hpp", "timeutil.hpp", "spec.hpp", "store.hpp", "plan.hpp", "kernels.hpp",
                "engine.hpp", "xxh64.hpp", os.path.join("..", "..", "include", "sdo_engine.h")]
 ENGINE_LIB = os.path.join(HERE, "libsdo_engine.so")

@@ -494,6 +494,21 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   }
 }
 
+// The group table of a finished scan as the top-k select reads it: compacted rows, hash buckets or a direct table.
+static SelView select_view(const ScanState& st, int ns, int slot, int is_f64, int desc) {
+  SelView v{};
+  v.is_f64 = is_f64;
+  v.desc = desc;
+  if (st.rows_valid) {
+    v.kind = SEL_ROWS; v.base = st.rows_slots; v.keys = st.rows_keys; v.n = st.n_rows; v.stride = (uint32_t)ns; v.slot_off = (uint32_t)slot; v.slot0_off = 0;
+  } else if (st.strategy == STRAT_HASH) {
+    v.kind = SEL_HASH; v.base = st.table; v.n = st.table_rows; v.stride = st.params.hstride; v.slot_off = 1u + (uint32_t)slot; v.slot0_off = 1;
+  } else {
+    v.kind = SEL_DENSE; v.base = st.table; v.n = st.table_rows; v.stride = (uint32_t)ns; v.slot_off = (uint32_t)slot; v.slot0_off = 0;
+  }
+  return v;
+}
+
 // Gather the occupied groups of a large dense table or a hash table into row arrays.
 void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   cudaStream_t s = ctx->stream;
@@ -636,6 +651,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   rows.ns = ns;
   rows.pool = &pinned_pool_;
   bool device_topk = false;
+  uint64_t groups_total = 0;  // groups in the table when only the top k came back
   float ms_h2d = 0, ms_scan = 0, ms_dev = 0;
 
   if (!plan.always_false) {
@@ -675,12 +691,51 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
       }
       rows.n = rows.keys.size();
     } else {
-      if (!st->rows_valid) compact_rows(ctx, plan, st);
-      uint64_t n = st->n_rows;
       // device top-k when only a few rows of a large result are wanted
       int topk_slot = -1, topk_f64 = 0, topk_desc = 1;
       int64_t k_want = 0;
-      if (n <= 65536 || !topk_request(plan, &topk_slot, &topk_f64, &topk_desc, &k_want)) topk_slot = -1;
+      if (!topk_request(plan, &topk_slot, &topk_f64, &topk_desc, &k_want)) topk_slot = -1;
+      // First choice: radix select over the table as it stands (compacted rows, direct table or hash table) -- no
+      // compaction pass, a tournament over the few candidates only.  Ties beyond the candidate list fall through.
+      if (topk_slot >= 0 && (st->rows_valid ? st->n_rows : st->table_rows) > 65536) {
+        const int k = (int)k_want;
+        SDO_CUDA(cudaEventRecord(ctx->ev[3], s));
+        unsigned long long *gk = nullptr, *gs = nullptr;
+        void* scratch = nullptr;
+        SDO_CUDA(cudaMallocAsync((void**)&gk, (size_t)k * 8, s));
+        SDO_CUDA(cudaMallocAsync((void**)&gs, (size_t)k * ns * 8, s));
+        SDO_CUDA(cudaMallocAsync(&scratch, select_scratch_bytes(k), s));
+        launch_select_topk(select_view(*st, ns, topk_slot, topk_f64, topk_desc), ns, k, scratch, gk, gs, s);
+        st->launches += 16;
+        SelState sel;
+        rows.keys.assign((size_t)k, 0);
+        rows.slots.assign((size_t)k * ns, 0);
+        SDO_CUDA(cudaMemcpyAsync(rows.keys.data(), gk, (size_t)k * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaMemcpyAsync(rows.slots.data(), gs, (size_t)k * ns * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaMemcpyAsync(&sel, scratch, sizeof sel, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaEventRecord(ctx->ev[4], s));
+        SDO_CUDA(cudaStreamSynchronize(s));
+        st->d2h_bytes += (size_t)k * (ns + 1) * 8 + sizeof sel;
+        for (void* p : {(void*)gk, (void*)gs, scratch}) SDO_CUDA(cudaFreeAsync(p, s));
+        if (!sel.overflow) {
+          size_t w = 0;  // fewer than k groups: the rest is padding
+          for (size_t i = 0; i < (size_t)k; i++)
+            if (rows.keys[i] != ~0ull) {
+              rows.keys[w] = rows.keys[i];
+              memmove(&rows.slots[w * ns], &rows.slots[i * ns], (size_t)ns * 8);
+              w++;
+            }
+          rows.keys.resize(w);
+          rows.slots.resize(w * ns);
+          rows.n = w;
+          groups_total = sel.live;
+          device_topk = true;
+        }
+      }
+      if (!device_topk) {
+      if (!st->rows_valid) compact_rows(ctx, plan, st);
+      uint64_t n = st->n_rows;
+      if (n <= 65536) topk_slot = -1;
       // A large result that needs no host-side work (no post-aggregation, having, ordering or sketches)
       // is turned into its columns on the device and copied straight into pinned result buffers.
       {
@@ -720,6 +775,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
         rows.keys.resize(w);
         rows.slots.resize(w * ns);
         rows.n = w;
+        groups_total = n;
         device_topk = true;
       } else {
         rows.keys.assign((size_t)n, 0);
@@ -758,6 +814,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
           rows.n = w;
         }
       }
+    }  // !device_topk
     }
     cudaEventElapsedTime(&ms_h2d, ctx->ev[0], ctx->ev[1]);
     cudaEventElapsedTime(&ms_scan, ctx->ev[1], ctx->ev[2]);
@@ -1005,7 +1062,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
            "\"h2dBytes\":%zu,\"d2hBytes\":%zu,\"deviceTopK\":%s,\"spans\":%zu,\"segments\":%zu,\"keySpace\":%llu,\"jit\":%s,\"jitCompileMs\":%.3f,"
            "\"planMs\":%.4f,\"assembleMs\":%.4f%s}",
            plan.always_false ? "none" : strategy_name(st->strategy), device_, (long long)plan.rows_scanned, plan.bytes_per_row,
-           (long long)plan.algorithmic_bytes, (unsigned long long)n, (unsigned long long)m, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms,
+           (long long)plan.algorithmic_bytes, (unsigned long long)(groups_total ? groups_total : n), (unsigned long long)m, ms_scan, ms_dev, ms_h2d, now_ms() - t_start_ms,
            st->launches, st->h2d_bytes, st->d2h_bytes, device_topk ? "true" : "false", plan.spans.size(), plan.seg_index.size(),
            (unsigned long long)plan.n_keys, st->jit ? "true" : "false", st->jit_compile_ms, st->plan_ms, now_ms() - t_assemble, hll_note.c_str());
   res->stats = buf;
@@ -1754,17 +1811,31 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       nccl_group_end();
       st.launches += 3;
       st.exchange_bytes = (n - (send_off[comm_rank_ + 1] - send_off[comm_rank_])) * (uint64_t)(ns + 1) * 8;
-      merge_received_rows(ctx, *plan, &st, rk, rs, m);  // this rank's share, as rows
       // top K by one aggregate: K candidates per share, gathered, finished on root
       int tk_slot = -1, tk_f64 = 0, tk_desc = 1;
       int64_t k_want = 0;
-      if (topk_request(*plan, &tk_slot, &tk_f64, &tk_desc, &k_want)) {
+      const bool want_topk = topk_request(*plan, &tk_slot, &tk_f64, &tk_desc, &k_want);
+      merge_received_rows(ctx, *plan, &st, rk, rs, m, /*compact=*/!want_topk);  // this rank's share (rows, or the merged hash table)
+      if (want_topk) {
         const int k = (int)k_want;
         unsigned long long* cand_k = (unsigned long long*)dev_alloc((size_t)k * 8 * W);
         unsigned long long* cand_s = (unsigned long long*)dev_alloc((size_t)k * ns * 8 * W);
         unsigned long long* mine_k = (unsigned long long*)dev_alloc((size_t)k * 8);
         unsigned long long* mine_s = (unsigned long long*)dev_alloc((size_t)k * ns * 8);
-        if (st.n_rows > (uint64_t)k) {
+        bool selected = false;
+        if (st.table_rows > 65536) {
+          // radix select over the merged hash table in place; ties beyond the candidate list fall back to the tournament
+          void* scratch = dev_alloc(select_scratch_bytes(k));
+          launch_select_topk(select_view(st, ns, tk_slot, tk_f64, tk_desc), ns, k, scratch, mine_k, mine_s, s);
+          st.launches += 16;
+          SelState sel;
+          SDO_CUDA(cudaMemcpyAsync(&sel, scratch, sizeof sel, cudaMemcpyDeviceToHost, s));
+          SDO_CUDA(cudaStreamSynchronize(s));
+          selected = !sel.overflow;
+        }
+        if (!selected) compact_rows(ctx, *plan, &st);
+        if (selected) {
+        } else if (st.n_rows > (uint64_t)k) {
           const size_t se = topk_scratch_elems(st.n_rows, k);
           unsigned long long *sa = (unsigned long long*)dev_alloc(se * 8), *sb = (unsigned long long*)dev_alloc(se * 8), *oi = (unsigned long long*)dev_alloc((size_t)k * 8);
           launch_topk(st.rows_keys, st.rows_slots, st.n_rows, ns, tk_slot, tk_f64, tk_desc, k, sa, sb, oi, s);
@@ -1785,9 +1856,10 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
         nccl_group_end();
         if (comm_rank_ == root) {
           // the candidates replace the share: finalize orders them on the host and cuts at K
-          SDO_CUDA(cudaFreeAsync(st.rows_keys, s));
-          SDO_CUDA(cudaFreeAsync(st.rows_slots, s));
+          if (st.rows_keys) SDO_CUDA(cudaFreeAsync(st.rows_keys, s));
+          if (st.rows_slots) SDO_CUDA(cudaFreeAsync(st.rows_slots, s));
           st.rows_keys = st.rows_slots = nullptr;
+          st.rows_valid = true;
           SDO_CUDA(cudaMallocAsync((void**)&st.rows_keys, (size_t)k * 8 * W, s));
           SDO_CUDA(cudaMallocAsync((void**)&st.rows_slots, (size_t)k * ns * 8 * W, s));
           SDO_CUDA(cudaMemcpyAsync(st.rows_keys, cand_k, (size_t)k * 8 * W, cudaMemcpyDeviceToDevice, s));
@@ -1839,7 +1911,7 @@ bool Engine::topk_request(const Plan& plan, int* slot, int* is_f64, int* desc_ou
 
 // Fold (key, slots) rows received from other ranks (and this rank's own) into one group per key: a fresh hash table
 // sized for the rows, then compaction back to rows.  Leaves st->rows_* = this rank's share.
-void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n) {
+void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n, bool compact) {
   cudaStream_t s = ctx->stream;
   const int ns = plan.n_slots;
   for (void* q : {(void*)st->table, (void*)st->hkeys, (void*)st->rows_keys, (void*)st->rows_slots})
@@ -1861,7 +1933,7 @@ void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st,
   st->launches += 2;
   st->rows_valid = false;
   st->merged = true;
-  compact_rows(ctx, plan, st);
+  if (compact) compact_rows(ctx, plan, st);
 }
 
 Partial* Engine::partial(const char* json, size_t len) {

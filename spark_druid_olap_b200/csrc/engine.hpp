@@ -173,7 +173,7 @@ class Engine {
   int64_t next_turn_ = 0;
   std::mutex comm_mu_;
   static bool topk_request(const Plan& plan, int* slot, int* is_f64, int* desc, int64_t* k_want);
-  void merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n);
+  void merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n, bool compact = true);
   Result* finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
 
   QueryCtx* acquire_ctx();

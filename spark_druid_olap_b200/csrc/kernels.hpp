@@ -215,6 +215,36 @@ void launch_topk(const unsigned long long* keys, const unsigned long long* slots
                  int descending, int k, unsigned long long* scratch_a, unsigned long long* scratch_b, unsigned long long* out_idx,
                  cudaStream_t st);
 size_t topk_scratch_elems(uint64_t n, int k);
+// Radix select in front of the tournament (select_kernels.cu): finds the groups at or above the k-th order value of any
+// group table IN PLACE -- compacted rows, a direct-indexed table (live = row count != 0, key = index) or a hash table
+// (live = key set) -- and runs the tournament over those candidates only.
+enum SelKind : int32_t { SEL_ROWS = 0, SEL_DENSE = 1, SEL_HASH = 2 };
+struct SelView {
+  const unsigned long long* base;  // ROWS: slots [n][stride]; DENSE: table [n][stride]; HASH: buckets [n][stride] = [key | slots ...]
+  const unsigned long long* keys;  // ROWS only
+  uint64_t n;
+  uint32_t stride;     // words per row / bucket
+  uint32_t slot_off;   // word of the ordering aggregate inside a row / bucket
+  uint32_t slot0_off;  // word of slot 0 inside a row / bucket (ROWS / DENSE: 0, HASH: 1)
+  int32_t kind, is_f64, desc;
+};
+struct SelState {  // device-resident search state, zeroed before the first pass
+  unsigned long long prefix;   // digits fixed so far (most significant first)
+  unsigned long long k_rem;    // rank still to find below the prefix
+  unsigned long long live;     // live groups in the table
+  unsigned long long n_cand;   // candidates appended
+  unsigned long long above;    // live groups whose fixed digits rank strictly above the prefix
+  int32_t shift;               // candidates are the live groups with (ord >> shift) >= (prefix >> shift)
+  int32_t done;
+  int32_t overflow;            // more candidates than SEL_CAP (ties): the caller falls back to the full tournament
+  int32_t pad;
+};
+constexpr uint32_t SEL_CAP = 1u << 16;
+size_t select_scratch_bytes(int k);
+// Queues: select passes, candidate collection, tournament over the candidates, gather of the k winners into
+// out_keys[k] / out_slots[k][n_slots] (padding: key ~0).  `scratch` holds select_scratch_bytes(k); its first bytes are the
+// SelState (read `overflow` and `live` after the stream has drained).
+void launch_select_topk(const SelView& v, int n_slots, int k, void* scratch, unsigned long long* out_keys, unsigned long long* out_slots, cudaStream_t st);
 void launch_gather_rows(const unsigned long long* keys, const unsigned long long* slots, const unsigned long long* idx, uint64_t k, int ns,
                         unsigned long long* out_keys, unsigned long long* out_slots, cudaStream_t st);
 // Large results: turn compacted (key, slots) rows into the result's columns on the device, so the host

@@ -58,3 +58,37 @@ def test_c_oracle_hll_registers_exact(tables):
 def test_shapes_outside_c_oracle_fall_back(tables):
     tbl, ct = tables
     assert c_oracle.execute(ct, json.loads(Q.q7().to_json())) is None  # timeFormat dimension: numpy oracle only
+
+
+def test_c_oracle_equals_numpy_oracle_at_sf1(native_libs):
+    """BASELINE config 1's own scale (SF1, 6 M rows): the two independent CPU statements agree on the Q1-style query and on
+    the reference's q1.json shape, so the oracle the GPU tests trust at SF1 / SF10 is not only checked on toy tables."""
+    from spark_druid_olap_b200 import tpch
+    cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "ps_supplycost", "ps_availqty", "count", "o_orderkey"]
+    tbl = H.oracle_table(tpch.FlatTable(1.0, cols))
+    ct = c_oracle.CTable(tbl)
+    for spec in (Q.q1_style(), Q.basic_agg()):
+        q = json.loads(spec.to_json())
+        got, gr = c_oracle.execute(ct, q, return_registers=True)
+        want, wr = orc.execute(tbl, q, return_registers=True)
+        H.assert_rows_equal(got, want, what=spec.queryType)
+        for k in wr:
+            assert np.array_equal(gr[k], wr[k])
+
+
+@pytest.mark.parametrize("name,mk,ordered", [c for c in CASES if c[0] in ("q1", "q5", "q3", "ts_day", "ts_month", "agg_zoo", "js_aggs", "by_orderkey")], ids=lambda c: c if isinstance(c, str) else "")
+def test_merged_shard_partials_equal_the_whole_table(native_libs, name, mk, ordered):
+    """bench.py's parity gate runs the C oracle one generator shard at a time and merges the partial groups
+    (PostAggregate.scala:39-60: count / sum -> sum, min -> min, max -> max, HLL -> register max): three shards merged must
+    give exactly what one run over the concatenated table gives."""
+    from spark_druid_olap_b200 import tpch
+    cols = H.TEST_COLUMNS + ["order_year"]
+    shards = [tpch.FlatTable(SF, cols, i, 3) for i in range(3)]
+    whole = c_oracle.CTable(H.oracle_table(shards))
+    q = json.loads(mk().to_json())
+    parts = [c_oracle.execute_partial(c_oracle.CTable(H.oracle_table(t)), q) for t in shards]
+    got, gr = c_oracle.merge_partials(q, parts, return_registers=True)
+    want, wr = c_oracle.execute(whole, q, return_registers=True)
+    H.assert_rows_equal(got, want, ordered=ordered, what=name)
+    for k in wr:
+        assert np.array_equal(gr[k], wr[k])
