@@ -449,6 +449,14 @@ def main():
         L.sdo_result_free(h)
         return out
 
+    # A shape's first queries run on the ahead-of-time kernel while its specialised kernel compiles in the background
+    # (csrc/jit.cpp): touch every shape once, wait for the compiler, then measure the steady state.
+    for n in names:
+        free(run_raw(n))
+    t_settle = time.perf_counter()
+    while L.sdo_jit_pending() > 0 and time.perf_counter() - t_settle < 60:
+        time.sleep(0.05)
+    sync()
     warm = max(args.warmup, 3)
     for _ in range(warm):
         step()
@@ -486,12 +494,13 @@ def main():
                 free(run_raw(n))
             sc, dv, e2 = [], [], []
             st = None
+            sync()
             for _ in range(6):
-                sync()
+                if world == 1:
+                    sync()
                 t1 = time.perf_counter()
                 r = run_raw(n)
-                sync()
-                e2.append((time.perf_counter() - t1) * 1e3)
+                e2.append((time.perf_counter() - t1) * 1e3)  # the C-ABI call: it returns when the result is in host memory
                 if r is not None:
                     res = r if isinstance(r, sdo.Result) else sdo.Result(r)
                     st = res.stats

@@ -131,6 +131,10 @@ int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_o
  *     timestamp inside the query intervals, empty ones with the aggregators' identities; at most
  *     65536 buckets); groupBy never zero-fills, as in Druid. */
 int sdo_query_execute(sdo_engine* e, const char* query_json, size_t len, sdo_result** out);
+/* Query shapes whose specialised scan kernel is still compiling on a background thread.  Queries of such a shape run on
+ * the ahead-of-time kernel meanwhile (no query waits for the compiler unless its context says gpuJit: true); a benchmark
+ * that wants steady-state numbers waits for 0.  No reference counterpart. */
+int sdo_jit_pending(void);
 /* Plan only (no device work): returns a JSON description of the spans, compiled filter,
  * key layout, strategy and algorithmic bytes.  No reference counterpart beyond
  * EXPLAIN DRUID REWRITE (sparklinedata/commands/DruidMetadataCommands.scala:49). */

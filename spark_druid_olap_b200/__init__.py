@@ -112,6 +112,7 @@ def lib():
         "sdo_query_execute_sharded": (C.c_int, [vp, cp, sz, C.c_int, C.POINTER(vp)]),
         "sdo_query_execute_sharded_at": (C.c_int, [vp, cp, sz, C.c_int, i64, C.POINTER(vp)]),
         "sdo_engine_comm_next_turn": (C.c_int, [vp, C.POINTER(i64)]),
+        "sdo_jit_pending": (C.c_int, []),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)
@@ -128,7 +129,7 @@ EXPORTED_SYMBOLS = [
     "sdo_result_stats_json", "sdo_result_free", "sdo_query_partial", "sdo_partial_view_get", "sdo_partial_partition",
     "sdo_partial_merge_rows", "sdo_partial_stream", "sdo_partial_finish", "sdo_partial_free", "sdo_groupby_sum_noalloc",
     "sdo_dimension_dictionary", "sdo_dimension_extend", "sdo_partial_export", "sdo_partial_merge_gathered",
-    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded", "sdo_query_execute_sharded_at", "sdo_engine_comm_next_turn", "sdo_datasource_save", "sdo_datasource_restore",
+    "sdo_comm_unique_id", "sdo_engine_comm_init", "sdo_query_execute_sharded", "sdo_query_execute_sharded_at", "sdo_engine_comm_next_turn", "sdo_jit_pending", "sdo_datasource_save", "sdo_datasource_restore",
 ]
 
 NOALLOC_MAX_KEYS = 24

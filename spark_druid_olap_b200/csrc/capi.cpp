@@ -6,6 +6,7 @@
 
 #include "../../include/sdo_engine.h"
 #include "engine.hpp"
+#include "jit.hpp"
 
 using namespace sdo;
 
@@ -277,6 +278,8 @@ int sdo_query_execute_sharded_at(sdo_engine* e, const char* query_json, size_t l
     if (r) *out = new sdo_result{r};
   });
 }
+
+int sdo_jit_pending(void) { return jit_pending(); }
 
 int sdo_engine_comm_next_turn(sdo_engine* e, int64_t* turn_out) {
   if (!e || !turn_out) return bad("sdo_engine_comm_next_turn: NULL argument");

@@ -360,7 +360,10 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   if (strat == STRAT_HASH) {
     // size the table from an exact count of passing rows when a filter can shrink it
     uint64_t rows_upper = (uint64_t)plan.rows_scanned;
-    if (p.n_ops > 0) {
+    const int64_t known = plan.passing_rows.v.load();
+    if (p.n_ops > 0 && known >= 0) {
+      rows_upper = (uint64_t)known;  // counted by an earlier run of this cached plan
+    } else if (p.n_ops > 0) {
       ScanParams c = p;
       c.n_dims = 0;
       c.n_aggs = 0;
@@ -383,6 +386,7 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
       st->launches += 2;
       st->d2h_bytes += 8;
       rows_upper = cnt;
+      plan.passing_rows.v.store((int64_t)cnt);
     }
     uint64_t groups_upper = std::min<uint64_t>(plan.n_keys, rows_upper);
     uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, groups_upper + groups_upper / 2));
@@ -464,7 +468,10 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
     bool want = plan.spec.gpu_jit > 0 || (plan.spec.gpu_jit < 0 && !env_off && (env_on || plan.rows_scanned >= opt_.jit_min_rows));
     if (want) {
       double ms = 0;
-      jk = jit_get(strat, p, &ms);
+      // only a query that asks for the specialised kernel waits for the compiler; the others run ahead-of-time code
+      // until the background compilation of their shape has finished
+      static const char* sync_env = getenv("SDO_JIT_SYNC");
+      jk = jit_get(strat, p, &ms, plan.spec.gpu_jit > 0 || (sync_env && sync_env[0] == '1'));
       st->jit_compile_ms = ms;
     }
   }
@@ -472,6 +479,14 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   int grid = 0;
   if (jk) grid = jit_blocks_per_sm(jk, smem) * sm_count_;
   if (grid <= 0) { jk = nullptr; st->jit = false; grid = scan_grid_size(strat, smem, sm_count_); }
+  // Other scans in flight on this engine: a persistent grid at full occupancy would make every later kernel wait for this
+  // one's last block, so a short query queued behind a long one takes the long one's time.  Each scan takes its share of the
+  // resident blocks instead (never less than one block per SM) and the kernels run side by side.
+  if (!st->counted) { st->counted = true; st->others_at_launch = scans_in_flight_.fetch_add(1); }
+  if (st->others_at_launch > 0 && grid > sm_count_) {
+    const int per_sm = grid / sm_count_;
+    grid = std::max(1, per_sm / std::min(per_sm, st->others_at_launch + 1)) * sm_count_;
+  }
   // a block's 8 warps each draw quarter-unit tickets: no more blocks than there is work for
   const uint32_t n_chunks = (uint32_t)((((uint64_t)plan.n_units << (12 - p.ticket_shift)) + 7) / 8);
   grid = (int)std::max<uint32_t>(1, std::min<uint32_t>((uint32_t)grid, n_chunks));
@@ -542,6 +557,7 @@ void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
 }
 
 void Engine::free_state(QueryCtx* ctx, ScanState* st) {
+  if (st->counted) { st->counted = false; scans_in_flight_.fetch_sub(1); }
   if (device_ < 0) return;
   cudaStream_t s = ctx->stream;
   void* ptrs[] = {st->blob, st->table, st->hkeys, st->hll_in_table ? nullptr : (void*)st->hll, st->partials, st->rows_keys, st->rows_slots, st->rows_hll, st->hll_stats};

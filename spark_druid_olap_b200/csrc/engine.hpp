@@ -103,6 +103,8 @@ struct ScanState {
   double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
   bool rows_valid = false;
+  bool counted = false;               // this scan is in the engine's in-flight count
+  int others_at_launch = 0;           // scans already in flight when this one was launched
   const char* shard_merge = nullptr;  // sharded execution: which merge ran (gather / reduce / sparse)
   uint64_t exchange_bytes = 0;        // sparse merge: bytes of rows this rank sent to other ranks
 };
@@ -147,6 +149,7 @@ class Engine {
  private:
   int device_;
   int sm_count_ = 148;
+  std::atomic<int> scans_in_flight_{0};
   Store store_;
   PlanOptions opt_;
   std::mutex ctx_mu_;

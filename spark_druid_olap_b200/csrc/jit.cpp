@@ -2,7 +2,10 @@
 // compiled by NVRTC for sm_100a with the query SHAPE (filter program, column widths, aggregator list,
 // strategy) spelled out as constexpr tables, so the interpreter's loops unroll and its dispatch folds away.
 // Values (id ranges, bitsets, strides, pointers) stay run-time parameters: one compiled shape serves every
-// query of that shape, and shapes are cached for the life of the process.
+// query of that shape.  Shapes are cached for the life of the process and their cubins on disk (SDO_JIT_CACHE_DIR, default
+// ~/.cache/sdo_engine/jit, keyed by a hash of shape + kernel sources), and a new shape compiles on a background thread
+// while the queries that need it run on the ahead-of-time kernel: no query waits for the compiler unless it asks to
+// (context.gpuJit = true).
 //
 // NVRTC and the driver API are loaded with dlopen, so the library itself has no link-time dependency on
 // them (it must load on a machine without a GPU for planning-only use).  If either is missing or a
@@ -13,13 +16,21 @@
 #include <dlfcn.h>
 #include <nvrtc.h>
 
+#include <sys/stat.h>
+#include <unistd.h>
+
 #include <chrono>
+#include <condition_variable>
 #include <cstdio>
 #include <cstdlib>
 #include <fstream>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <sstream>
+#include <thread>
+
+#include "xxh64.hpp"
 
 namespace sdo {
 namespace {
@@ -59,7 +70,7 @@ bool read_file(const std::string& path, std::string* out) {
 }
 
 Api& api() {
-  static Api a;
+  static Api& a = *new Api;  // never destroyed: a background compilation may still read it while the process exits
   static std::once_flag once;
   std::call_once(once, [] {
     void* rtc = open_any({"libnvrtc.so.12", "libnvrtc.so", "/usr/local/cuda/lib64/libnvrtc.so.12", "/usr/local/cuda/lib64/libnvrtc.so"});
@@ -148,9 +159,97 @@ std::string prelude(int strategy, const ScanParams& p) {
   return s;
 }
 
-std::mutex g_mu;
-std::map<std::string, JitKernel> g_cache;  // keyed by the prelude text (= the shape)
+// One cache entry per shape (keyed by the prelude text).  A shape is compiled once per process -- by the query that first
+// needs it (wait = true) or by a background thread while queries of that shape run on the ahead-of-time kernel -- and its
+// cubin is kept on disk, keyed by a hash of everything that went into it, so a later process loads it in about a millisecond.
+struct Entry {
+  enum State { Compiling, Compiled, Ready, Failed } state = Compiling;
+  std::string cubin;   // Compiled: waiting for a query thread (which has the CUDA context) to load it
+  JitKernel kernel;    // Ready
+  double compile_ms = 0;
+};
+// (heap objects that are never destroyed: a detached compile thread may outlive static destruction at process exit)
+std::mutex& g_mu = *new std::mutex;
+std::condition_variable& g_cv = *new std::condition_variable;
+std::map<std::string, std::shared_ptr<Entry>>& g_cache = *new std::map<std::string, std::shared_ptr<Entry>>;
 bool g_warned = false;
+
+void warn_once(const std::string& m) {
+  if (!g_warned) {
+    fprintf(stderr, "[sdo] run-time kernel specialisation unavailable (%s); using the ahead-of-time kernels\n", m.c_str());
+    g_warned = true;
+  }
+}
+
+std::string cache_dir() {
+  const char* d = getenv("SDO_JIT_CACHE_DIR");
+  if (d && *d) return d;
+  const char* x = getenv("XDG_CACHE_HOME");
+  if (x && *x) return std::string(x) + "/sdo_engine/jit";
+  const char* h = getenv("HOME");
+  return std::string(h && *h ? h : "/tmp") + "/.cache/sdo_engine/jit";
+}
+void make_dirs(const std::string& path) {
+  for (size_t i = 1; i <= path.size(); i++)
+    if (i == path.size() || path[i] == '/') mkdir(path.substr(0, i).c_str(), 0755);
+}
+std::string cache_file(const Api& a, const std::string& src) {
+  // everything the cubin depends on: the shape, the kernel sources, the target
+  uint64_t h = xxh64_bytes(src.data(), src.size(), 1);
+  h = xxh64_bytes(a.src_kernel.data(), a.src_kernel.size(), h);
+  h = xxh64_bytes(a.src_params.data(), a.src_params.size(), h);
+  h = xxh64_bytes(a.src_xxh.data(), a.src_xxh.size(), h);
+  char name[64];
+  snprintf(name, sizeof name, "/sm_100a-%016llx.cubin", (unsigned long long)h);
+  return cache_dir() + name;
+}
+
+// NVRTC only: needs no CUDA context, so it can run on any thread
+bool compile_cubin(Api& a, const std::string& src, std::string* cubin, std::string* err) {
+  nvrtcProgram prog = nullptr;
+  const char* hdr_src[] = {a.src_kernel.c_str(), a.src_params.c_str(), a.src_xxh.c_str()};
+  const char* hdr_name[] = {"scan_kernel.cuh", "kernels.hpp", "xxh64.hpp"};
+  if (a.CreateProgram(&prog, src.c_str(), "sdo_scan_jit.cu", 3, hdr_src, hdr_name) != NVRTC_SUCCESS) { *err = "nvrtcCreateProgram"; return false; }
+  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo"};
+  if (a.CompileProgram(prog, 3, opts) != NVRTC_SUCCESS) {
+    size_t n = 0;
+    a.GetProgramLogSize(prog, &n);
+    std::string log(n, 0);
+    if (n) a.GetProgramLog(prog, &log[0]);
+    a.DestroyProgram(&prog);
+    *err = "nvrtc compile error: " + log.substr(0, 2000);
+    return false;
+  }
+  size_t n = 0;
+  if (a.GetCUBINSize(prog, &n) != NVRTC_SUCCESS || !n) { a.DestroyProgram(&prog); *err = "nvrtcGetCUBINSize"; return false; }
+  cubin->assign(n, 0);
+  a.GetCUBIN(prog, &(*cubin)[0]);
+  a.DestroyProgram(&prog);
+  return true;
+}
+
+// cubin from the disk cache, else compiled (and written to the cache); fills the entry, takes g_mu only to publish
+void produce(Api& a, const std::string& src, std::shared_ptr<Entry> e) {
+  const auto t0 = std::chrono::steady_clock::now();
+  static const bool no_disk = [] { const char* v = getenv("SDO_JIT_DISK_CACHE"); return v && v[0] == '0'; }();
+  const std::string file = cache_file(a, src);
+  std::string cubin, err;
+  bool ok = !no_disk && read_file(file, &cubin) && cubin.size() > 64;
+  if (!ok) {
+    ok = compile_cubin(a, src, &cubin, &err);
+    if (ok && !no_disk) {
+      make_dirs(cache_dir());
+      const std::string tmp = file + "." + std::to_string((long long)getpid()) + ".tmp";
+      std::ofstream f(tmp, std::ios::binary);
+      if (f && f.write(cubin.data(), (std::streamsize)cubin.size()) && (f.close(), true)) rename(tmp.c_str(), file.c_str());
+    }
+  }
+  std::lock_guard<std::mutex> lk(g_mu);
+  e->compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+  if (ok) { e->cubin = std::move(cubin); e->state = Entry::Compiled; }
+  else { e->state = Entry::Failed; warn_once(err); }
+  g_cv.notify_all();
+}
 
 }  // namespace
 
@@ -160,53 +259,59 @@ bool jit_available(std::string* why) {
   return a.ok;
 }
 
-const JitKernel* jit_get(int strategy, const ScanParams& p, double* compile_ms) {
+// wait = true: compile now if the shape is new (the caller pays, *compile_ms says how much).  wait = false: a new shape
+// starts compiling on a background thread and nullptr comes back -- the caller runs the ahead-of-time kernel this time.
+const JitKernel* jit_get(int strategy, const ScanParams& p, double* compile_ms, bool wait) {
   if (compile_ms) *compile_ms = 0;
   Api& a = api();
   if (!a.ok) return nullptr;
   const std::string src = prelude(strategy, p);
-  std::lock_guard<std::mutex> lk(g_mu);
+  std::unique_lock<std::mutex> lk(g_mu);
+  std::shared_ptr<Entry> e;
   auto it = g_cache.find(src);
-  if (it != g_cache.end()) return it->second.func ? &it->second : nullptr;
-  auto t0 = std::chrono::steady_clock::now();
-  JitKernel k;
-  auto fail = [&](const std::string& m) -> const JitKernel* {
-    if (!g_warned) {
-      fprintf(stderr, "[sdo] run-time kernel specialisation unavailable (%s); using the ahead-of-time kernels\n", m.c_str());
-      g_warned = true;
+  if (it == g_cache.end()) {
+    e = std::make_shared<Entry>();
+    g_cache[src] = e;
+    if (wait) {
+      lk.unlock();
+      produce(a, src, e);
+      lk.lock();
+      if (compile_ms) *compile_ms = e->compile_ms;
+    } else {
+      std::thread([&a, src, e] { produce(a, src, e); }).detach();
+      return nullptr;
     }
-    g_cache[src] = JitKernel();  // remember the failure: do not retry this shape
-    return nullptr;
-  };
-  nvrtcProgram prog = nullptr;
-  const char* hdr_src[] = {a.src_kernel.c_str(), a.src_params.c_str(), a.src_xxh.c_str()};
-  const char* hdr_name[] = {"scan_kernel.cuh", "kernels.hpp", "xxh64.hpp"};
-  if (a.CreateProgram(&prog, src.c_str(), "sdo_scan_jit.cu", 3, hdr_src, hdr_name) != NVRTC_SUCCESS) return fail("nvrtcCreateProgram");
-  const char* opts[] = {"--gpu-architecture=sm_100a", "-std=c++17", "-lineinfo"};
-  nvrtcResult rc = a.CompileProgram(prog, 3, opts);
-  if (rc != NVRTC_SUCCESS) {
-    size_t n = 0;
-    a.GetProgramLogSize(prog, &n);
-    std::string log(n, 0);
-    if (n) a.GetProgramLog(prog, &log[0]);
-    a.DestroyProgram(&prog);
-    return fail("nvrtc compile error: " + log.substr(0, 2000));
+  } else {
+    e = it->second;
+    if (e->state == Entry::Compiling) {
+      if (!wait) return nullptr;
+      g_cv.wait(lk, [&] { return e->state != Entry::Compiling; });
+    }
   }
-  size_t n = 0;
-  if (a.GetCUBINSize(prog, &n) != NVRTC_SUCCESS || !n) { a.DestroyProgram(&prog); return fail("nvrtcGetCUBINSize"); }
-  std::string cubin(n, 0);
-  a.GetCUBIN(prog, &cubin[0]);
-  a.DestroyProgram(&prog);
-  CUmodule mod = nullptr;
-  CUfunction fn = nullptr;
-  if (a.ModuleLoadData(&mod, cubin.data()) != CUDA_SUCCESS) return fail("cuModuleLoadData");
-  if (a.ModuleGetFunction(&fn, mod, "sdo_scan_jit") != CUDA_SUCCESS) return fail("cuModuleGetFunction");
-  a.FuncSetAttribute(fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, 227 * 1024 - 64);
-  k.func = (void*)fn;
-  k.compile_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-  if (compile_ms) *compile_ms = k.compile_ms;
-  auto ins = g_cache.emplace(src, k);
-  return &ins.first->second;
+  if (e->state == Entry::Compiled) {
+    // load the module on this thread: it has the device's context current
+    CUmodule mod = nullptr;
+    CUfunction fn = nullptr;
+    if (a.ModuleLoadData(&mod, e->cubin.data()) != CUDA_SUCCESS || a.ModuleGetFunction(&fn, mod, "sdo_scan_jit") != CUDA_SUCCESS) {
+      e->state = Entry::Failed;
+      warn_once("cuModuleLoadData / cuModuleGetFunction");
+    } else {
+      a.FuncSetAttribute(fn, CU_FUNC_ATTRIBUTE_MAX_DYNAMIC_SHARED_SIZE_BYTES, 227 * 1024 - 64);
+      e->kernel.func = (void*)fn;
+      e->kernel.compile_ms = e->compile_ms;
+      e->state = Entry::Ready;
+    }
+    e->cubin.clear();
+    e->cubin.shrink_to_fit();
+  }
+  return e->state == Entry::Ready ? &e->kernel : nullptr;
+}
+
+int jit_pending() {
+  std::lock_guard<std::mutex> lk(g_mu);
+  int n = 0;
+  for (auto& kv : g_cache) n += kv.second->state == Entry::Compiling;
+  return n;
 }
 
 int jit_blocks_per_sm(const JitKernel* k, size_t smem) {

@@ -4,6 +4,7 @@
 // decides about output cardinality (sources/druid/DruidQueryCostModel.scala:691-716: product of
 // dimension cardinalities capped by row count) -- here that number picks the aggregation strategy.
 #pragma once
+#include <atomic>
 #include <memory>
 #include <string>
 #include <vector>
@@ -54,8 +55,19 @@ struct HostLeaf {
   std::vector<uint32_t> bitset;  // BITSET payload
 };
 
+// a value several queries of one cached plan may read and set (copying a plan copies the value)
+struct SharedCount {
+  std::atomic<int64_t> v{-1};
+  SharedCount() = default;
+  SharedCount(const SharedCount& o) : v(o.v.load()) {}
+  SharedCount& operator=(const SharedCount& o) { v.store(o.v.load()); return *this; }
+};
+
 struct Plan {
   QuerySpec spec;
+  // rows that pass the filter, counted by the first hash-strategy run of this plan (sizes the hash table): later runs of
+  // the cached plan skip the count pass.  The plan cache drops a plan when its datasource changes, and the count with it.
+  mutable SharedCount passing_rows;
   std::shared_ptr<DataSource> ds;
   uint64_t ds_version = 0;          // datasource version this plan was made against
   std::vector<int> seg_index;       // used segments -> index in ds->segments

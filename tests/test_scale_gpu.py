@@ -137,3 +137,33 @@ def test_sf10_q1_style_sums_of_ten_million_addends(sf10):
     for jit in (False, True):
         res, _ = _check(sf10, Q.q1_style(), jit)
         assert max(res["count_order"]) > 14_000_000
+
+
+def test_new_shape_runs_ahead_of_time_code_while_its_kernel_compiles(sf1):
+    """A query shape the process has not seen does not wait for NVRTC (about a second): it runs on the ahead-of-time kernel
+    while its specialised kernel compiles on a background thread, and later queries of the shape pick that up.  Same rows
+    either way.  (context.gpuJit = true is the one way to make a query wait for the compiler.)"""
+    import time
+    eng, tbl, ct, ds = sf1
+    spec = Q.GroupByQuerySpec(Q.DS, [Q.DefaultDimensionSpec("l_linestatus"), Q.DefaultDimensionSpec("s_region")], None, None, "all",
+                              Q.SelectorFilterSpec("c_mktsegment", "MACHINERY"),
+                              [Q.agg("doubleMax", "mx", "l_discount"), Q.agg("longSum", "avail", "ps_availqty"), Q.agg("doubleSum", "cost", "ps_supplycost")],
+                              None, Q.ALL_TIME, None)
+    q = json.loads(spec.to_json())
+    q["dataSource"] = ds
+    want = c_oracle.execute(ct, q, THREADS)
+    t0 = time.perf_counter()
+    first = eng.execute(q)
+    first_ms = (time.perf_counter() - t0) * 1e3
+    H.assert_rows_equal(H.engine_rows(first), want)
+    if first.stats["jit"]:
+        pytest.skip("the shape's cubin was already in the disk cache")
+    assert first_ms < 200, f"the first query of a new shape took {first_ms:.0f} ms: it waited for the compiler"
+    deadline = time.perf_counter() + 60
+    while time.perf_counter() < deadline:
+        res = eng.execute(q)
+        H.assert_rows_equal(H.engine_rows(res), want)
+        if res.stats["jit"]:
+            break
+        time.sleep(0.05)
+    assert res.stats["jit"] is True, "the background compilation never delivered the specialised kernel"
