@@ -458,7 +458,10 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   // Rows per ticket (measured on SF10, ms at 512 / 1024 / 2048 / 4096 rows): month timeseries + HLL 0.44 / 0.25 / 0.18 /
   // 0.17 (a warp merges its cached sketch into HBM per ticket), TopN with a selective filter 0.127 / 0.094 / 0.088 /
   // 0.134, hash group-by + limit 0.064 / 0.079 / 0.133 / 0.237, 15 M-group direct table 1.77 / 1.89 / 2.26 / 2.53.
-  p.ticket_shift = p.hll_mode == HLL_IN_SMEM_SPAN ? 12 : (strat == STRAT_HASH || strat == STRAT_GLOBAL) ? 9 : (p.n_ops > 0 || strat == STRAT_SPAN ? 11 : 10);
+  // On SF100 (600 M rows) the filtered TopN runs 0.552 ms at 2048 rows per ticket and 0.539 at 4096: long scans amortise the
+  // ticket draw, short ones need the finer tail.
+  p.ticket_shift = p.hll_mode == HLL_IN_SMEM_SPAN ? 12 : (strat == STRAT_HASH || strat == STRAT_GLOBAL) ? 9
+                   : (p.n_ops > 0 || strat == STRAT_SPAN ? (plan.rows_scanned >= (1ll << 28) ? 12 : 11) : 10);
   if (plan.spec.gpu_ticket_rows) p.ticket_shift = plan.spec.gpu_ticket_rows == 512 ? 9 : plan.spec.gpu_ticket_rows == 1024 ? 10 : plan.spec.gpu_ticket_rows == 2048 ? 11 : 12;
   // run-time specialised kernel for this query shape (large scans, or when the query asks for it)
   const JitKernel* jk = nullptr;

@@ -108,9 +108,10 @@ std::string table(const char* name, int n, F f) {
 }
 
 std::string prelude(int strategy, const ScanParams& p) {
-  static const char* nv_env = getenv("SDO_JIT_NV");  // experiment knob: vectors per dense-path accumulate call
-  static const char* wt_env = getenv("SDO_JIT_WARP_TICKETS");  // experiment knob: 0 = block tickets
-  std::string s = std::string("#define SDO_JIT 1\n") + "#define SDO_WARP_TICKETS " + (wt_env && *wt_env == '0' ? "0" : "1") + "\n#define SDO_DENSE_NV " + std::string(nv_env && *nv_env ? nv_env : "1") + "\nnamespace sdo { namespace jit {\n";
+  const char* nv_env = getenv("SDO_JIT_NV");  // experiment knob: vectors per dense-path accumulate call
+  const char* wt_env = getenv("SDO_JIT_WARP_TICKETS");  // experiment knob: 0 = block tickets
+  const char* rf_env = getenv("SDO_JIT_HLL_READ_FIRST");  // experiment knob: 0 = always issue the shared-memory atomicMax
+  std::string s = std::string("#define SDO_JIT 1\n") + (rf_env && *rf_env == '0' ? "#define SDO_HLL_READ_FIRST 0\n" : "") + "#define SDO_WARP_TICKETS " + (wt_env && *wt_env == '0' ? "0" : "1") + "\n#define SDO_DENSE_NV " + std::string(nv_env && *nv_env ? nv_env : (strategy == STRAT_SPAN ? "4" : "1")) + "\nnamespace sdo { namespace jit {\n";
   s += "constexpr int n_ops = " + std::to_string(p.n_ops) + ";\n";
   s += table<int>("op_code", p.n_ops, [&](int i) { return p.op_code[i]; });
   s += table<int>("op_arg", p.n_ops, [&](int i) { return p.op_arg[i]; });
@@ -148,12 +149,17 @@ std::string prelude(int strategy, const ScanParams& p) {
   s += "constexpr int ignore_key_base = " + std::to_string(p.ignore_key_base) + ";\n";
   s += "constexpr int n_cols = " + std::to_string(p.n_cols) + ";\n";
   s += "}}\n#include \"scan_kernel.cuh\"\n";
-  static const char* mb_env = getenv("SDO_JIT_MINBLOCKS");  // experiment knob: resident blocks per SM the compiler aims for
+  const char* mb_env = getenv("SDO_JIT_MINBLOCKS");  // experiment knob: resident blocks per SM the compiler aims for
   // Registers per thread follow from the blocks per SM the compiler is told to fit (measured on SF10): wide shapes
   // (seven aggregates, six of them expressions) are fastest at 3 blocks / 85 registers -- 0.71 ms vs 0.86 at 4 and 1.17
   // at 6, the rest being spills; narrow ones (one or two aggregates, no sketch) gain a few percent at 6 blocks / 40 registers.
   const int weight = p.n_aggs + 2 * p.n_exprs + p.n_dims;
-  const std::string min_blocks = mb_env && *mb_env ? mb_env : (weight >= 8 ? "3" : (weight >= 3 || p.n_hll > 0) ? "4" : "6");
+  // The span strategy folds a call's rows in registers and touches its shared-memory cell once per call: all 16 rows of a
+  // pass in one call at 6 blocks per SM (SF100 day timeseries + HLL: 1.26 ms before, 0.99 ms folded 4 rows at a time,
+  // 0.90 ms = the HBM roofline with 16).  A narrow filtered shape (TopN over one sum) gains 4 % at 8 blocks.
+  const std::string min_blocks = mb_env && *mb_env ? mb_env
+                                 : strategy == STRAT_SPAN && weight < 8 ? "6"
+                                 : (weight >= 8 ? "3" : (weight >= 3 || p.n_hll > 0) ? "4" : (p.n_ops > 0 ? "8" : "6"));
   s += "extern \"C\" __global__ void __launch_bounds__(256, " + min_blocks + ") sdo_scan_jit(const __grid_constant__ sdo::ScanParams p, const uint32_t* __restrict__ coarse) {\n";
   s += "  sdo::scan_body<" + std::to_string(strategy) + ">(p, coarse);\n}\n";
   return s;
