@@ -357,7 +357,16 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   st->strategy = strat;
   const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;
 
-  if (strat == STRAT_HASH) {
+  if (strat == STRAT_EMIT) {
+    // no table: the surviving rows come out as groups of one row each (bounded by the rows in the spans)
+    const uint64_t cap = (uint64_t)std::max<int64_t>(plan.rows_scanned, 1);
+    SDO_CUDA(cudaMallocAsync((void**)&st->rows_keys, cap * 8, s));
+    SDO_CUDA(cudaMallocAsync((void**)&st->rows_slots, cap * (uint64_t)plan.n_slots * 8, s));
+    p.emit_keys = st->rows_keys;
+    p.emit_slots = st->rows_slots;
+    p.emit_cap = cap;
+    st->table_rows = 0;
+  } else if (strat == STRAT_HASH) {
     // size the table from an exact count of passing rows when a filter can shrink it
     uint64_t rows_upper = (uint64_t)plan.rows_scanned;
     const int64_t known = plan.passing_rows.v.load();
@@ -399,7 +408,7 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
     p.hmask = cap - 1;
     p.hstride = stride;
     p.table = st->table;
-  } else {
+  } else if (strat != STRAT_EMIT) {
     st->table_rows = plan.n_keys;
     // dense table and its HLL registers share one block: a partial is then a single contiguous blob
     const size_t tb = round_up(std::max<uint64_t>(cells, 1) * 8, 256);
@@ -505,6 +514,15 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   }
   SDO_CUDA(cudaEventRecord(ctx->ev[2], s));
   st->launches += 1;
+  if (strat == STRAT_EMIT) {
+    struct { unsigned int c[4]; unsigned long long n; } host;
+    SDO_CUDA(cudaMemcpyAsync(&host, ctx->counters, 24, cudaMemcpyDeviceToHost, s));
+    SDO_CUDA(cudaStreamSynchronize(s));
+    st->d2h_bytes += 24;
+    if (host.c[1]) throw std::runtime_error("internal: more rows emitted than the spans hold");
+    st->n_rows = host.n;
+    st->rows_valid = true;
+  }
   if (strat == STRAT_LANE) {
     launch_reduce_partials(st->partials, grid, (uint32_t)cells, plan.n_slots, p, st->table, s);
     st->launches += 1;
@@ -1682,7 +1700,7 @@ enum class ShardMerge { Gather, Reduce, Sparse };
 static ShardMerge shard_merge_mode(const Plan& plan, const PlanOptions& opt, uint64_t blob_bytes) {
   static const uint64_t gather_max = [] { const char* v = getenv("SDO_GATHER_MAX_BYTES"); return v ? (uint64_t)atoll(v) : (256ull << 10); }();
   static const uint64_t reduce_max = [] { const char* v = getenv("SDO_REDUCE_MAX_BYTES"); return v ? (uint64_t)atoll(v) : (64ull << 20); }();
-  const bool dense_everywhere = plan.spec.gpu_strategy != "hash" && plan.spec.gpu_strategy != "partition" &&
+  const bool dense_everywhere = plan.spec.gpu_strategy != "hash" && plan.spec.gpu_strategy != "emit" &&
                                 (plan.n_keys <= opt.global_max_keys || (plan.dev_dims.empty() && plan.n_keys <= (1ull << 31)));
   if (!dense_everywhere || plan.spec.gpu_shard_merge == "sparse") return ShardMerge::Sparse;
   if (plan.spec.gpu_shard_merge == "gather") return ShardMerge::Gather;
@@ -1723,11 +1741,20 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
   const uint64_t blob = round_up(std::max<uint64_t>(cells, 1) * 8, 256) + (plan->n_hll ? plan->n_keys * (uint64_t)plan->n_hll * HLL_M : 0);
   const ShardMerge mode = shard_merge_mode(*plan, opt_, blob);
   if (mode == ShardMerge::Sparse && plan->n_hll) throw Unsupported("cardinality aggregations over a sparse key space cannot be merged across GPUs");
-  if (mode == ShardMerge::Sparse && plan->strategy != STRAT_HASH && plan->strategy != STRAT_GLOBAL && plan->strategy != STRAT_PARTITION) {
-    // a forced sparse merge of a small key space (tests): the rows come out of a hash table
-    variant = *plan;
-    variant.strategy = STRAT_HASH;
-    plan = &variant;
+  if (mode == ShardMerge::Sparse) {
+    // Key spaces that are sparse on their own account (not forced for a test) have about as many groups as rows on every
+    // rank: aggregating locally would pay a pass of atomics here and a second one at the owner for nothing, so the rows
+    // themselves are exchanged (STRAT_EMIT) and aggregated once, where they are owned.
+    bool emit = plan->spec.gpu_strategy == "emit" || (plan->spec.gpu_strategy.empty() && plan->spec.gpu_shard_merge.empty());
+    std::vector<int> writers(plan->n_slots, 0);
+    for (auto& a : plan->dev_aggs) writers[a.slot]++;
+    for (int x = 1; x < plan->n_slots; x++) emit = emit && writers[x] == 1;
+    if (emit || (plan->strategy != STRAT_HASH && plan->strategy != STRAT_GLOBAL)) {
+      // (else: a forced sparse merge of a small key space: the groups come out of a hash table)
+      variant = *plan;
+      variant.strategy = emit ? STRAT_EMIT : STRAT_HASH;
+      plan = &variant;
+    }
   }
   QueryCtx* ctx = acquire_ctx();
   ScanState st;

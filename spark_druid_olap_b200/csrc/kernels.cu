@@ -77,6 +77,7 @@ int scan_grid_size(int strategy, size_t smem_bytes, int sm_count) {
     case STRAT_BLOCK: nb = occupancy<STRAT_BLOCK>(smem_bytes); break;
     case STRAT_GLOBAL: nb = occupancy<STRAT_GLOBAL>(smem_bytes); break;
     case STRAT_SPAN: nb = occupancy<STRAT_SPAN>(smem_bytes); break;
+    case STRAT_EMIT: nb = occupancy<STRAT_EMIT>(smem_bytes); break;
     default: nb = occupancy<STRAT_HASH>(smem_bytes); break;
   }
   if (nb < 1) nb = 1;
@@ -91,6 +92,7 @@ void launch_scan(int strategy, const ScanParams& p, int grid, size_t smem, cudaS
     case STRAT_BLOCK: opt_in_shared_memory<STRAT_BLOCK>(); scan_kernel<STRAT_BLOCK><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     case STRAT_GLOBAL: opt_in_shared_memory<STRAT_GLOBAL>(); scan_kernel<STRAT_GLOBAL><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     case STRAT_SPAN: opt_in_shared_memory<STRAT_SPAN>(); scan_kernel<STRAT_SPAN><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
+    case STRAT_EMIT: opt_in_shared_memory<STRAT_EMIT>(); scan_kernel<STRAT_EMIT><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
     default: opt_in_shared_memory<STRAT_HASH>(); scan_kernel<STRAT_HASH><<<grid, SCAN_THREADS, smem, st>>>(p, coarse); break;
   }
   SDO_CUDA(cudaGetLastError());

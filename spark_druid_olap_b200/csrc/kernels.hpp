@@ -133,8 +133,9 @@ enum Strategy : int32_t {
   STRAT_SPAN = 4,   // no grouping dimension (timeseries): the key is constant over a span, so a thread keeps private
                     // accumulators for its warp's current key only and the warp merges them into the direct-indexed
                     // HBM table when it moves to another key -- no atomics, votes or shuffles per row
-  STRAT_PARTITION = 5,  // high-cardinality keys: rows are first split by key range into windows whose slice of the direct
-                        // table stays in L2, then aggregated window by window (partition_kernels.cu); never a scan_kernel<>
+  STRAT_EMIT = 5,   // no aggregation at all: every surviving row is written out as a group of its own, [key | 1 | slot inputs],
+                    // for the cross-GPU exchange of high-cardinality group-bys (rows ~ groups: aggregating locally first
+                    // would cost a second pass of atomics at the owner and shrink nothing)
 };
 
 struct ScanParams {
@@ -175,6 +176,10 @@ struct ScanParams {
   uint32_t rep_mask;
   uint32_t rep_stride;
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
+  // EMIT: output rows (same layout as compacted groups: keys[n], slots[n][n_slots]); the cursor is the u64 at counters + 4
+  unsigned long long* emit_keys;
+  unsigned long long* emit_slots;
+  uint64_t emit_cap;
 };
 
 #ifndef __CUDACC_RTC__

@@ -17,6 +17,7 @@ const char* strategy_name(int s) {
     case STRAT_GLOBAL: return "global";
     case STRAT_SPAN: return "span";
     case STRAT_HASH: return "hash";
+    case STRAT_EMIT: return "emit";
   }
   return "?";
 }
@@ -898,7 +899,8 @@ Plan make_plan(const QuerySpec& spec, std::shared_ptr<DataSource> ds_ptr, const 
     why = "key space of " + std::to_string(plan.n_keys) + " keys is dense relative to " + std::to_string(plan.rows_scanned) + " rows: direct table of " + std::to_string(cells * 8) + " bytes in HBM";
   }
   else { strat = STRAT_HASH; why = "key space of " + std::to_string(plan.n_keys) + " keys is sparse: open-addressing hash table"; }
-  if (!spec.gpu_strategy.empty()) {
+  // "emit" is a request to the sharded layer (exchange raw rows instead of local groups), not a local strategy
+  if (!spec.gpu_strategy.empty() && spec.gpu_strategy != "emit") {
     const std::string& g = spec.gpu_strategy;
     int forced = g == "lane" ? STRAT_LANE : g == "block" ? STRAT_BLOCK : g == "global" ? STRAT_GLOBAL : g == "hash" ? STRAT_HASH : g == "span" ? STRAT_SPAN : -1;
     if (forced == STRAT_SPAN && !plan.dev_dims.empty()) throw Invalid("gpuStrategy span: the query has grouping dimensions");

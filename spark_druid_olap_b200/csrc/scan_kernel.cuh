@@ -338,6 +338,18 @@ struct Acc<STRAT_HASH> : AtomicOps {
   __device__ __forceinline__ void countn(unsigned long long* q, int c) const { atomicAdd(q, (unsigned long long)c); }
 };
 
+template <>
+struct Acc<STRAT_EMIT> : AtomicOps {  // nothing is accumulated: accumulate() hands the rows to emit_rows()
+  typedef uint64_t key_t;
+  unsigned long long* base;
+  int ns;
+  unsigned int* hll_sm;
+  static constexpr int SLOT_STRIDE = 1;
+  __device__ __forceinline__ unsigned long long* at(key_t) const { return base; }
+  __device__ __forceinline__ void count1(unsigned long long*) const {}
+  __device__ __forceinline__ void countn(unsigned long long*, int) const {}
+};
+
 // find-or-claim the slot of `key` (linear probing).  Returns HASH_EMPTY if the table is full.
 __device__ __forceinline__ uint64_t hash_claim(unsigned long long* hkeys, uint64_t mask, uint32_t stride, uint64_t key) {
   uint64_t h = mix64(key) & mask;
@@ -558,6 +570,82 @@ __device__ __forceinline__ void eval_expr_m(const ScanParams& p, int e, const vo
   }
 }
 
+// STRAT_EMIT: write the rows of `r0` with a bit in m out as groups of one row each: key, slot 0 = 1, and for every
+// aggregator the value its slot would have received (its identity where the aggregator's own filter fails).
+// WARP = all 32 lanes are here: one cursor bump per warp; otherwise (row-by-row path under divergence) one per row.
+template <int N, int NV, bool WARP>
+__device__ __forceinline__ void emit_rows(const ScanParams& p, const void* const* cols, const uint64_t (&key)[N * NV], const RowSet<NV>& r0, uint32_t m) {
+  constexpr int R = N * NV;
+  const int ns = Q_N_SLOTS;
+  unsigned long long* cursor = (unsigned long long*)(p.counters + 4);
+  const int c = __popc(m);
+  unsigned long long pos0;
+  if (WARP) {
+    int incl = c;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, incl, off);
+      if ((int)(threadIdx.x & 31u) >= off) incl += t;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31u) == 0 && total) base = atomicAdd(cursor, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    pos0 = base + (unsigned long long)(incl - c);
+  } else {
+    if (!c) return;
+    pos0 = atomicAdd(cursor, (unsigned long long)c);
+  }
+  if (!c) return;
+  if (pos0 + (unsigned long long)c > p.emit_cap) { p.counters[1] = 1; return; }
+  unsigned long long pos[R];
+  {
+    unsigned long long q = pos0;
+#pragma unroll
+    for (int i = 0; i < R; i++) { pos[i] = q; q += (m >> i) & 1u; }
+  }
+#pragma unroll
+  for (int i = 0; i < R; i++)
+    if ((m >> i) & 1u) { p.emit_keys[pos[i]] = key[i]; p.emit_slots[pos[i] * ns] = 1ull; }
+  Q_UNROLL
+  for (int a = 0; a < Q_N_AGGS; a++) {
+    uint32_t ma = m;
+    if (Q_AGG_LEAF(a) >= 0) ma &= leaf_test_m<N, NV>(p, Q_AGG_LEAF(a), cols, r0);
+    const int slot = Q_AGG_SLOT(a);
+    const unsigned long long ident = p.slot_init[slot];
+    const void* col = Q_AGG_OP(a) >= AGG_SUM_EXPR ? nullptr : cols[Q_AGG_COL(a)];
+    unsigned long long out[R];
+    const int op = Q_AGG_OP(a);
+    const bool from_f64 = op == AGG_SUM_F64 || op == AGG_MIN_F64 || op == AGG_MAX_F64 || op == AGG_SUM_I64_F64 || op == AGG_MIN_I64_F64 || op == AGG_MAX_I64_F64;
+    const bool from_i64 = op == AGG_SUM_I64 || op == AGG_MIN_I64 || op == AGG_MAX_I64 || op == AGG_SUM_F64_I64 || op == AGG_MIN_F64_I64 || op == AGG_MAX_F64_I64;
+    double vf[R];
+    long long vi[R];
+#pragma unroll
+    for (int i = 0; i < R; i++) { vf[i] = 0.0; vi[i] = 0; }
+    if (from_f64) load_f64_m<N, NV>(col, r0, vf);
+    else if (from_i64) load_i64_m<N, NV>(col, r0, vi);
+    else if (op >= AGG_SUM_EXPR) eval_expr_m<N, NV>(p, Q_AGG_COL(a), cols, r0, vf);
+#pragma unroll
+    for (int i = 0; i < R; i++) {
+      long long w;
+      switch (op) {
+        case AGG_SUM_F64: case AGG_SUM_EXPR: w = __double_as_longlong(vf[i]); break;            // the double itself
+        case AGG_MIN_F64: case AGG_MAX_F64: case AGG_MIN_EXPR: case AGG_MAX_EXPR: w = f64_to_ord(vf[i]); break;  // order-preserving int64
+        case AGG_SUM_I64: case AGG_MIN_I64: case AGG_MAX_I64: w = vi[i]; break;
+        case AGG_SUM_F64_I64: w = __double_as_longlong((double)vi[i]); break;
+        case AGG_MIN_F64_I64: case AGG_MAX_F64_I64: w = f64_to_ord((double)vi[i]); break;
+        case AGG_SUM_I64_F64: case AGG_MIN_I64_F64: case AGG_MAX_I64_F64: w = (long long)vf[i]; break;
+        case AGG_COUNT_IF: w = 1; break;
+        default: w = (long long)ident; break;
+      }
+      out[i] = (unsigned long long)w;
+    }
+#pragma unroll
+    for (int i = 0; i < R; i++)
+      if ((m >> i) & 1u) p.emit_slots[pos[i] * ns + slot] = ((ma >> i) & 1u) ? out[i] : ident;
+  }
+}
+
 // Aggregate the rows of `r0` (N = 4: vector loads; N = 1: scalar loads); bit v * N + i of m = row (v, i) takes part.
 // WARP = called by all 32 lanes together (lanes without rows pass m = 0): lets a warp whose surviving
 // rows all share one key (time buckets, sorted low-cardinality keys) fold them with shuffles and
@@ -582,6 +670,10 @@ __device__ __forceinline__ void accumulate(const ScanParams& p, const void* cons
     const key_t stride = (key_t)p.dims[d].stride;
 #pragma unroll
     for (int i = 0; i < R; i++) key[i] += (key_t)ids[i] * stride;
+  }
+  if constexpr (STRAT == STRAT_EMIT) {
+    emit_rows<N, NV, WARP>(p, cols, key, r0, m);
+    return;
   }
   if (STRAT == STRAT_HASH) {
 #pragma unroll
@@ -857,6 +949,8 @@ __device__ __forceinline__ void scan_body(const ScanParams& p, const uint32_t* _
   } else if (STRAT == STRAT_HASH) {
     acc.base = p.table + 1;  // word 0 of a bucket is its key
     acc.ns = (int)p.hstride;
+  } else if (STRAT == STRAT_EMIT) {
+    acc.base = nullptr;
   } else {
     acc.base = p.table;
   }

@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 
 SF = 0.02
 COLS = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "o_orderkey", "o_custkey", "o_orderdate", "o_shippriority",
-        "c_mktsegment", "s_region", "s_nation", "count"]
+        "c_mktsegment", "s_region", "s_nation", "count", "ps_availqty", "ps_supplycost", "l_shipmode", "c_region"]
 
 
 @pytest.fixture(scope="module")
@@ -130,6 +130,29 @@ def test_sparse_partition_exchange_merge_on_one_rank(dist_engine, mk, ordered):
     res, info = sharded.execute_sharded(eng, q)
     assert info["merge"] == "sparse"
     H.assert_rows_equal(H.engine_rows(res), want, ordered=ordered)
+
+
+def _zoo_without_sketches(strategy):
+    q = json.loads(Q.agg_zoo(strategy).to_json())
+    q["aggregations"] = [a for a in q["aggregations"] if a["type"] != "cardinality"]
+    q["dimensions"] = [{"type": "default", "dimension": "o_custkey", "outputName": "o_custkey"}]
+    return q
+
+
+@pytest.mark.parametrize("shape", ["by_orderkey", "q3", "q3_limit10", "q5", "zoo", "q5_topn"])
+def test_row_exchange_on_one_rank(dist_engine, shape):
+    """The exchange of raw rows (what a sharded group-by over a sparse key space does: no local aggregation, every surviving
+    row travels as a group of one to the rank that owns its key and is aggregated once there), with a single owner.
+    The zoo has min / max, cross-type sums and filtered aggregators: a row's slot carries the aggregator's identity where
+    its own filter fails."""
+    from spark_druid_olap_b200 import sharded
+    eng, tbl, name = dist_engine
+    spec = {"by_orderkey": lambda: Q.by_orderkey("emit"), "q3": lambda: Q.q3(None, "emit"), "q3_limit10": lambda: Q.q3(10, "emit"), "q5": lambda: Q.q5("emit"),
+            "q5_topn": lambda: Q.q5_topn(10, "emit"), "zoo": lambda: _zoo_without_sketches("emit")}[shape]()
+    q = _with_ds(spec, name) if hasattr(spec, "to_json") else dict(spec, dataSource=name)
+    res, info = sharded.execute_sharded(eng, q)
+    assert info["merge"] == "sparse"
+    H.assert_rows_equal(H.engine_rows(res), orc.execute(tbl, q), ordered=shape in ("q3_limit10", "q5_topn"), what=shape)
 
 
 def test_turns_order_concurrent_sharded_queries(dist_engine):

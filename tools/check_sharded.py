@@ -23,7 +23,7 @@ rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 cols = ["l_returnflag", "l_linestatus", "l_quantity", "l_extendedprice", "l_discount", "o_orderkey", "o_custkey", "o_orderdate", "o_shippriority",
-        "c_mktsegment", "s_region", "s_nation", "count"]
+        "c_mktsegment", "s_region", "s_nation", "count", "ps_availqty", "ps_supplycost", "l_shipmode", "c_region"]
 eng = sdo.Engine(local)
 eng.create_datasource("tpch")
 if os.environ.get("CHECK_SKEW"):
@@ -52,10 +52,13 @@ for pass_name in ("host-merge", "library"):
                               ("ts_day_hll", Q.timeseries("P1D"), False), ("q5t", Q.q5_topn(), True), ("by_orderkey_hash", Q.by_orderkey("hash"), False),
                               ("by_orderkey_global", Q.by_orderkey("global"), False), ("by_orderkey", Q.by_orderkey(), False), ("q3", Q.q3(), False),
                               ("q3_limit10", Q.q3(10), True), ("q1_reduce", Q.q1_style(), False), ("ts_day_reduce", Q.timeseries("P1D"), False),
-                              ("q5_sparse", Q.q5(), False)] * int(os.environ.get("CHECK_REPEAT", "1")):
+                              ("q5_sparse", Q.q5(), False), ("by_orderkey_emit", Q.by_orderkey("emit"), False), ("q3_emit", Q.q3(None, "emit"), False),
+                              ("q3_limit10_emit", Q.q3(10, "emit"), True), ("q5t_emit", Q.q5_topn(10, "emit"), True)] * int(os.environ.get("CHECK_REPEAT", "1")):
       if os.environ.get("CHECK_ONLY") and name not in os.environ["CHECK_ONLY"].split(","):
           continue
       q = json.loads(spec.to_json())
+      if name.endswith("_emit") and pass_name != "library":
+          continue
       if name.endswith("_reduce") or name.endswith("_sparse"):
           if pass_name != "library":
               continue
