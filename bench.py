@@ -518,6 +518,10 @@ def main():
                 e = {"strategy": st["strategy"], "rows_scanned": int(tot[0]), "bytes_per_row": pl["bytesPerRow"], "algorithmic_bytes": int(tot[1]),
                      "scan_ms": scan, "scan_ms_min": min(sc), "device_ms": sum(dv) / len(dv), "e2e_ms": float(e2t[0]), "e2e_ms_min": -float(e2t[1]),
                      "rows_per_s_e2e": int(tot[0]) / (float(e2t[0]) / 1e3), "launches": st["launches"], "result_rows": st.get("resultRows")}
+                if st.get("shardPhasesMs"):
+                    e["merge"], e["phases_ms_rank0"], e["exchange_bytes_rank0"] = st.get("shardMerge"), st["shardPhasesMs"], st.get("exchangeBytes")
+                elif st.get("shardMerge"):
+                    e["merge"] = st["shardMerge"]
                 if world == 1:
                     e["achieved_gbs_algorithmic"] = int(tot[1]) / (scan / 1e3) / 1e9
                     traffic, src = measured_traffic(n, sf_total)

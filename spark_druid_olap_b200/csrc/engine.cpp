@@ -358,13 +358,24 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;
 
   if (strat == STRAT_EMIT) {
-    // no table: the surviving rows come out as groups of one row each (bounded by the rows in the spans)
-    const uint64_t cap = (uint64_t)std::max<int64_t>(plan.rows_scanned, 1);
-    SDO_CUDA(cudaMallocAsync((void**)&st->rows_keys, cap * 8, s));
-    SDO_CUDA(cudaMallocAsync((void**)&st->rows_slots, cap * (uint64_t)plan.n_slots * 8, s));
+    // No table: the surviving rows come out as groups of one row each, n_slots - 1 words per row, split by owner when the
+    // caller (a sharded query) names the owners.  A region holds its fair share of the rows and a quarter more; keys
+    // skewed beyond that raise the overflow flag and the scan is repeated with regions that hold everything.
+    const uint64_t cap_all = (uint64_t)std::max<int64_t>(plan.rows_scanned, 1);
+    const int owners = std::max(1, st->emit_owners);
+    const int nsr = plan.n_slots - 1;
+    st->emit_cap = owners > 1 && !st->emit_full_regions ? std::min<uint64_t>(cap_all, cap_all / owners + cap_all / (4 * owners) + 65536) : cap_all;
+    SDO_CUDA(cudaMallocAsync((void**)&st->rows_keys, (uint64_t)owners * st->emit_cap * 8, s));
+    SDO_CUDA(cudaMallocAsync((void**)&st->rows_slots, std::max<uint64_t>((uint64_t)owners * st->emit_cap * nsr, 1) * 8, s));
+    st->emit_cursors_dev = (unsigned long long*)take_scratch(ctx, 64 * 8);
+    if (!st->emit_cursors_dev) throw std::runtime_error("internal: context scratch exhausted");
+    SDO_CUDA(cudaMemsetAsync(st->emit_cursors_dev, 0, 64 * 8, s));
     p.emit_keys = st->rows_keys;
     p.emit_slots = st->rows_slots;
-    p.emit_cap = cap;
+    p.emit_cursors = st->emit_cursors_dev;
+    p.emit_cap = st->emit_cap;
+    p.emit_owners = owners;
+    p.emit_interleave = st->emit_interleave;
     st->table_rows = 0;
   } else if (strat == STRAT_HASH) {
     // size the table from an exact count of passing rows when a filter can shrink it
@@ -515,13 +526,31 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   SDO_CUDA(cudaEventRecord(ctx->ev[2], s));
   st->launches += 1;
   if (strat == STRAT_EMIT) {
-    struct { unsigned int c[4]; unsigned long long n; } host;
-    SDO_CUDA(cudaMemcpyAsync(&host, ctx->counters, 24, cudaMemcpyDeviceToHost, s));
+    const int owners = std::max(1, st->emit_owners);
+    unsigned long long cur[64];
+    unsigned int flags[4];
+    SDO_CUDA(cudaMemcpyAsync(cur, st->emit_cursors_dev, (size_t)owners * 8, cudaMemcpyDeviceToHost, s));
+    SDO_CUDA(cudaMemcpyAsync(flags, ctx->counters, 16, cudaMemcpyDeviceToHost, s));
     SDO_CUDA(cudaStreamSynchronize(s));
-    st->d2h_bytes += 24;
-    if (host.c[1]) throw std::runtime_error("internal: more rows emitted than the spans hold");
-    st->n_rows = host.n;
-    st->rows_valid = true;
+    st->d2h_bytes += (size_t)owners * 8 + 16;
+    if (flags[1]) {
+      if (owners == 1 || st->emit_full_regions) throw std::runtime_error("internal: more rows emitted than the spans hold");
+      // skewed owners: once more with regions that hold every row
+      SDO_CUDA(cudaFreeAsync(st->rows_keys, s));
+      SDO_CUDA(cudaFreeAsync(st->rows_slots, s));
+      st->rows_keys = st->rows_slots = nullptr;
+      if (st->blob && !((char*)st->blob >= ctx->scratch && (char*)st->blob < ctx->scratch + ctx->scratch_bytes)) SDO_CUDA(cudaFreeAsync(st->blob, s));
+      st->blob = nullptr;
+      ctx->scratch_used = 0;
+      SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
+      st->emit_full_regions = true;
+      return run_scan(ctx, plan, st);
+    }
+    st->emit_counts.assign(cur, cur + owners);
+    st->n_rows = 0;
+    for (int o = 0; o < owners; o++) st->n_rows += cur[o];
+    st->emit_regions = owners > 1;
+    st->rows_valid = owners == 1;
   }
   if (strat == STRAT_LANE) {
     launch_reduce_partials(st->partials, grid, (uint32_t)cells, plan.n_slots, p, st->table, s);
@@ -541,6 +570,8 @@ static SelView select_view(const ScanState& st, int ns, int slot, int is_f64, in
     v.kind = SEL_HASH; v.base = st.table; v.n = st.table_rows; v.stride = st.params.hstride; v.slot_off = 1u + (uint32_t)slot; v.slot0_off = 1;
   } else {
     v.kind = SEL_DENSE; v.base = st.table; v.n = st.table_rows; v.stride = (uint32_t)ns; v.slot_off = (uint32_t)slot; v.slot0_off = 0;
+    v.key_off = st.dense_key_off;
+    v.key_mul = st.dense_key_mul;
   }
   return v;
 }
@@ -560,7 +591,7 @@ void Engine::compact_rows(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   if (plan.n_hll) SDO_CUDA(cudaMallocAsync((void**)&src, std::max<uint64_t>(cap_rows, 1) * 8, s));
   SDO_CUDA(cudaMemsetAsync(counter, 0, 8, s));
   if (st->strategy == STRAT_HASH) launch_compact_hash(st->table, st->table_rows, ns, st->params.hstride, st->rows_keys, st->rows_slots, src, counter, s);
-  else launch_compact_dense(st->table, st->table_rows, ns, st->rows_keys, st->rows_slots, src, counter, s);
+  else launch_compact_dense(st->table, st->table_rows, ns, st->rows_keys, st->rows_slots, src, counter, s, st->dense_key_off, st->dense_key_mul);
   st->launches += 1;
   struct { unsigned int c[4]; unsigned long long n; } host;
   SDO_CUDA(cudaMemcpyAsync(&host, ctx->counters, 24, cudaMemcpyDeviceToHost, s));
@@ -722,7 +753,7 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
       }
       for (uint64_t k = 0; k < st->table_rows; k++) {
         if (t[k * ns] == 0 && !plan.zero_fill) continue;
-        rows.keys.push_back(k);
+        rows.keys.push_back(k * st->dense_key_mul + st->dense_key_off);
         rows.slots.insert(rows.slots.end(), t + k * ns, t + (k + 1) * ns);
         if (hb) rows.hll_set.push_back(k * plan.n_hll);
       }
@@ -1091,8 +1122,8 @@ Result* Engine::finalize(QueryCtx* ctx, const Plan& plan, ScanState* st, double 
   // not apply; those tables are not available here, so such values are the raw estimate and the caller is told how many
   std::string hll_note;
   if (plan.n_hll) hll_note = ",\"hllBiasCorrected\":false,\"hllUncorrectedValues\":" + std::to_string((unsigned long long)hll_uncorrected);
-  if (st->shard_merge) hll_note += std::string(",\"shardMerge\":\"") + st->shard_merge + "\",\"exchangeBytes\":" + std::to_string((unsigned long long)st->exchange_bytes);
-  char buf[1200];
+  if (st->shard_merge) hll_note += std::string(",\"shardMerge\":\"") + st->shard_merge + "\",\"exchangeBytes\":" + std::to_string((unsigned long long)st->exchange_bytes) + st->extra_stats;
+  char buf[1600];
   snprintf(buf, sizeof buf,
            "{\"strategy\":\"%s\",\"device\":%d,\"rowsScanned\":%lld,\"bytesPerRow\":%d,\"algorithmicBytes\":%lld,\"groups\":%llu,"
            "\"resultRows\":%llu,\"scanKernelMs\":%.6f,\"deviceMs\":%.6f,\"h2dMs\":%.6f,\"totalMs\":%.6f,\"launches\":%d,"
@@ -1769,6 +1800,13 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
   };
   try {
     cudaStream_t s = ctx->stream;
+    if (plan->strategy == STRAT_EMIT && comm_world_ > 1 && comm_world_ <= 64) {
+      // the scan writes every row straight into its owner's region.  Keys whose round-robin share (key mod world) fits a
+      // direct-indexed table are dealt out that way -- the owner then merges by plain indexing; others by hash.
+      const uint64_t per_rank = (plan->n_keys + (uint64_t)comm_world_ - 1) / (uint64_t)comm_world_;
+      st.emit_owners = comm_world_;
+      st.emit_interleave = plan->n_keys <= (1ull << 40) && per_rank * (uint64_t)plan->n_slots * 8 <= (16ull << 30) ? 1 : 0;
+    }
     run_scan(ctx, *plan, &st);
     const int ns = plan->n_slots;
     st.shard_merge = mode == ShardMerge::Gather ? "gather" : mode == ShardMerge::Reduce ? "reduce" : "sparse";
@@ -1810,58 +1848,130 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       // ---- sparse: rows, split by owner, exchanged, merged ----
       const int W = comm_world_;
       if (W > 64) throw Unsupported("the sparse merge handles at most 64 ranks");
-      if (!st.rows_valid) compact_rows(ctx, *plan, &st);
+      // phase marks on the stream (scan | rows ready | split by owner | exchanged | merged | top-k): reported in the stats
+      cudaEvent_t mark[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+      int n_marks = 0;
+      auto mark_here = [&] { if (n_marks < 6) { SDO_CUDA(cudaEventCreate(&mark[n_marks])); SDO_CUDA(cudaEventRecord(mark[n_marks++], s)); } };
+      struct MarkGuard { cudaEvent_t* m; ~MarkGuard() { for (int i = 0; i < 6; i++) if (m[i]) cudaEventDestroy(m[i]); } } mark_guard{mark};
+      auto phases = [&] {
+        std::string o = ",\"shardPhasesMs\":{";
+        static const char* names[] = {"rows", "split", "exchange", "merge", "topk"};
+        SDO_CUDA(cudaEventSynchronize(mark[n_marks - 1]));
+        for (int i = 1; i < n_marks; i++) {
+          float ms = 0;
+          cudaEventElapsedTime(&ms, mark[i - 1], mark[i]);
+          char b[64];
+          snprintf(b, sizeof b, "%s\"%s\":%.4f", i > 1 ? "," : "", names[i], ms);
+          o += b;
+        }
+        return o + "}";
+      };
+      SDO_CUDA(cudaEventRecord(ctx->ev[5], s));
+      const bool emit = st.strategy == STRAT_EMIT;
+      const int nsr = emit ? ns - 1 : ns;  // words per exchanged row (raw rows do not carry their count of 1)
+      if (!emit && !st.rows_valid) compact_rows(ctx, *plan, &st);
       const uint64_t n = st.n_rows;
-      unsigned long long* counts = (unsigned long long*)dev_alloc((2 * 64 + 64 * 64) * 8);  // [0,64) counts, [64,128) cursors, then every rank's counts
-      SDO_CUDA(cudaMemsetAsync(counts, 0, 2 * 64 * 8, s));
-      launch_partition_rows(st.rows_keys, st.rows_slots, n, ns, W, nullptr, nullptr, counts, nullptr, s);
-      turn.acquire();
-      unsigned long long* all_counts = counts + 128;
-      nccl_all_gather_bytes(comm_, counts, all_counts, 64 * 8, s);
-      std::vector<unsigned long long> h((size_t)64 * W);
-      SDO_CUDA(cudaMemcpyAsync(h.data(), all_counts, h.size() * 8, cudaMemcpyDeviceToHost, s));
-      SDO_CUDA(cudaStreamSynchronize(s));
-      st.d2h_bytes += h.size() * 8;
-      unsigned long long cur[64] = {0}, send_off[65] = {0}, recv_off[65] = {0};
-      for (int d = 0; d < W; d++) send_off[d + 1] = send_off[d] + h[(size_t)comm_rank_ * 64 + d];   // rows this rank sends to d
-      for (int src = 0; src < W; src++) recv_off[src + 1] = recv_off[src] + h[(size_t)src * 64 + comm_rank_];  // rows src sends here
-      if (send_off[W] != n) throw std::runtime_error("internal: partition counts do not add up");
-      for (int d = 0; d < W; d++) cur[d] = send_off[d];
-      SDO_CUDA(cudaMemcpyAsync(counts + 64, cur, (size_t)W * 8, cudaMemcpyHostToDevice, s));
-      unsigned long long* pk = (unsigned long long*)dev_alloc(std::max<uint64_t>(n, 1) * 8);
-      unsigned long long* ps = (unsigned long long*)dev_alloc(std::max<uint64_t>(n, 1) * ns * 8);
-      launch_partition_rows(st.rows_keys, st.rows_slots, n, ns, W, pk, ps, counts, counts + 64, s);
-      const uint64_t m = recv_off[W];
-      unsigned long long* rk = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * 8);
-      unsigned long long* rs = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * ns * 8);
-      nccl_group_start();
-      for (int p = 0; p < W; p++) {
-        const uint64_t sn = send_off[p + 1] - send_off[p], rn = recv_off[p + 1] - recv_off[p];
-        if (p == comm_rank_) {
-          if (sn != rn) throw std::runtime_error("internal: self exchange counts differ");
-          if (sn) {
-            SDO_CUDA(cudaMemcpyAsync(rk + recv_off[p], pk + send_off[p], sn * 8, cudaMemcpyDeviceToDevice, s));
-            SDO_CUDA(cudaMemcpyAsync(rs + recv_off[p] * ns, ps + send_off[p] * ns, sn * ns * 8, cudaMemcpyDeviceToDevice, s));
-          }
-          continue;
-        }
-        if (sn) {
-          nccl_send_bytes(comm_, pk + send_off[p], sn * 8, p, s);
-          nccl_send_bytes(comm_, ps + send_off[p] * ns, sn * ns * 8, p, s);
-        }
-        if (rn) {
-          nccl_recv_bytes(comm_, rk + recv_off[p], rn * 8, p, s);
-          nccl_recv_bytes(comm_, rs + recv_off[p] * ns, rn * ns * 8, p, s);
-        }
-      }
-      nccl_group_end();
-      st.launches += 3;
-      st.exchange_bytes = (n - (send_off[comm_rank_ + 1] - send_off[comm_rank_])) * (uint64_t)(ns + 1) * 8;
+      mark_here();  // [0] rows ready
       // top K by one aggregate: K candidates per share, gathered, finished on root
       int tk_slot = -1, tk_f64 = 0, tk_desc = 1;
       int64_t k_want = 0;
       const bool want_topk = topk_request(*plan, &tk_slot, &tk_f64, &tk_desc, &k_want);
-      merge_received_rows(ctx, *plan, &st, rk, rs, m, /*compact=*/!want_topk);  // this rank's share (rows, or the merged hash table)
+      unsigned long long* counts = (unsigned long long*)dev_alloc((2 * 64 + 64 * 64) * 8);  // [0,64) counts, [64,128) cursors, then every rank's counts
+      unsigned long long* all_counts = counts + 128;
+      SDO_CUDA(cudaMemsetAsync(counts, 0, 2 * 64 * 8, s));
+      std::vector<unsigned long long> h((size_t)64 * W);
+      unsigned long long send_off[65] = {0}, recv_off[65] = {0};
+      std::vector<RowSegment> segments;  // what this rank merges: its own rows for itself + what it received
+      if (emit && st.emit_regions) {
+        // the scan already wrote every row into its owner's region: the regions are the send buffers
+        SDO_CUDA(cudaMemcpyAsync(counts, st.emit_cursors_dev, (size_t)W * 8, cudaMemcpyDeviceToDevice, s));
+        turn.acquire();
+        nccl_all_gather_bytes(comm_, counts, all_counts, 64 * 8, s);
+        SDO_CUDA(cudaMemcpyAsync(h.data(), all_counts, h.size() * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaStreamSynchronize(s));
+        st.d2h_bytes += h.size() * 8;
+        for (int d = 0; d < W; d++)
+          if (h[(size_t)comm_rank_ * 64 + d] != st.emit_counts[d]) throw std::runtime_error("internal: emitted row counts changed under the exchange");
+        for (int src = 0; src < W; src++) recv_off[src + 1] = recv_off[src] + (src == comm_rank_ ? 0 : h[(size_t)src * 64 + comm_rank_]);
+        const uint64_t m = recv_off[W];
+        mark_here();  // [1] split by owner (nothing left to do)
+        unsigned long long* rk = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * 8);
+        unsigned long long* rs = (unsigned long long*)dev_alloc(std::max<uint64_t>(m * nsr, 1) * 8);
+        uint64_t sent = 0;
+        nccl_group_start();
+        for (int p = 0; p < W; p++) {
+          if (p == comm_rank_) continue;
+          const uint64_t sn = st.emit_counts[p], rn = recv_off[p + 1] - recv_off[p];
+          if (sn) {
+            nccl_send_bytes(comm_, st.rows_keys + (uint64_t)p * st.emit_cap, sn * 8, p, s);
+            if (nsr) nccl_send_bytes(comm_, st.rows_slots + (uint64_t)p * st.emit_cap * nsr, sn * nsr * 8, p, s);
+            sent += sn;
+          }
+          if (rn) {
+            nccl_recv_bytes(comm_, rk + recv_off[p], rn * 8, p, s);
+            if (nsr) nccl_recv_bytes(comm_, rs + recv_off[p] * nsr, rn * nsr * 8, p, s);
+          }
+        }
+        nccl_group_end();
+        mark_here();  // [2] exchanged
+        st.launches += 1;
+        st.exchange_bytes = sent * (uint64_t)(nsr + 1) * 8;
+        segments.push_back({st.rows_keys + (uint64_t)comm_rank_ * st.emit_cap, st.rows_slots + (uint64_t)comm_rank_ * st.emit_cap * nsr, st.emit_counts[comm_rank_]});
+        segments.push_back({rk, rs, m});
+      } else {
+        // groups (or raw rows in one stream): count per owner, scatter into runs, exchange the runs
+        launch_partition_rows(st.rows_keys, st.rows_slots, n, nsr, W, nullptr, nullptr, counts, nullptr, s);
+        turn.acquire();
+        nccl_all_gather_bytes(comm_, counts, all_counts, 64 * 8, s);
+        SDO_CUDA(cudaMemcpyAsync(h.data(), all_counts, h.size() * 8, cudaMemcpyDeviceToHost, s));
+        SDO_CUDA(cudaStreamSynchronize(s));
+        st.d2h_bytes += h.size() * 8;
+        unsigned long long cur[64] = {0};
+        for (int d = 0; d < W; d++) send_off[d + 1] = send_off[d] + h[(size_t)comm_rank_ * 64 + d];   // rows this rank sends to d
+        for (int src = 0; src < W; src++) recv_off[src + 1] = recv_off[src] + h[(size_t)src * 64 + comm_rank_];  // rows src sends here
+        if (send_off[W] != n) throw std::runtime_error("internal: partition counts do not add up");
+        for (int d = 0; d < W; d++) cur[d] = send_off[d];
+        SDO_CUDA(cudaMemcpyAsync(counts + 64, cur, (size_t)W * 8, cudaMemcpyHostToDevice, s));
+        unsigned long long* pk = (unsigned long long*)dev_alloc(std::max<uint64_t>(n, 1) * 8);
+        unsigned long long* ps = (unsigned long long*)dev_alloc(std::max<uint64_t>(n * nsr, 1) * 8);
+        launch_partition_rows(st.rows_keys, st.rows_slots, n, nsr, W, pk, ps, counts, counts + 64, s);
+        const uint64_t m = recv_off[W];
+        mark_here();  // [1] split by owner
+        unsigned long long* rk = (unsigned long long*)dev_alloc(std::max<uint64_t>(m, 1) * 8);
+        unsigned long long* rs = (unsigned long long*)dev_alloc(std::max<uint64_t>(m * nsr, 1) * 8);
+        nccl_group_start();
+        for (int p = 0; p < W; p++) {
+          const uint64_t sn = send_off[p + 1] - send_off[p], rn = recv_off[p + 1] - recv_off[p];
+          if (p == comm_rank_) {
+            if (sn != rn) throw std::runtime_error("internal: self exchange counts differ");
+            if (sn) {
+              SDO_CUDA(cudaMemcpyAsync(rk + recv_off[p], pk + send_off[p], sn * 8, cudaMemcpyDeviceToDevice, s));
+              if (nsr) SDO_CUDA(cudaMemcpyAsync(rs + recv_off[p] * nsr, ps + send_off[p] * nsr, sn * nsr * 8, cudaMemcpyDeviceToDevice, s));
+            }
+            continue;
+          }
+          if (sn) {
+            nccl_send_bytes(comm_, pk + send_off[p], sn * 8, p, s);
+            if (nsr) nccl_send_bytes(comm_, ps + send_off[p] * nsr, sn * nsr * 8, p, s);
+          }
+          if (rn) {
+            nccl_recv_bytes(comm_, rk + recv_off[p], rn * 8, p, s);
+            if (nsr) nccl_recv_bytes(comm_, rs + recv_off[p] * nsr, rn * nsr * 8, p, s);
+          }
+        }
+        nccl_group_end();
+        mark_here();  // [2] exchanged
+        st.launches += 3;
+        st.exchange_bytes = (n - (send_off[comm_rank_ + 1] - send_off[comm_rank_])) * (uint64_t)(nsr + 1) * 8;
+        segments.push_back({rk, rs, m});
+      }
+      // This rank's share: rows, or (top-K) the merged table as it stands.  Keys dealt out round-robin (key mod world) leave
+      // every rank a slice it can index directly -- no key storage, no probing; hashed keys go into a hash table.
+      if (emit && st.emit_regions && st.emit_interleave)
+        merge_received_rows_dense(ctx, *plan, &st, segments, (uint64_t)comm_rank_, (uint64_t)W, (plan->n_keys + (uint64_t)W - 1) / (uint64_t)W, emit, /*compact=*/!want_topk);
+      else
+        merge_received_rows(ctx, *plan, &st, segments, emit, /*compact=*/!want_topk);
+      mark_here();  // [3] merged
       if (want_topk) {
         const int k = (int)k_want;
         unsigned long long* cand_k = (unsigned long long*)dev_alloc((size_t)k * 8 * W);
@@ -1896,6 +2006,8 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
             SDO_CUDA(cudaMemcpyAsync(mine_s, st.rows_slots, st.n_rows * ns * 8, cudaMemcpyDeviceToDevice, s));
           }
         }
+        mark_here();  // [4] top-k of this share
+        st.extra_stats = phases();
         nccl_group_start();
         nccl_all_gather_bytes(comm_, mine_k, cand_k, (size_t)k * 8, s);
         nccl_all_gather_bytes(comm_, mine_s, cand_s, (size_t)k * ns * 8, s);
@@ -1916,6 +2028,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
           SDO_CUDA(cudaStreamSynchronize(s));
         }
       } else {
+        st.extra_stats = phases();
         r = finalize(ctx, *plan, &st, t0);  // this rank's share of the groups
       }
     }
@@ -1931,6 +2044,38 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
   free_state(ctx, &st);
   release_ctx(ctx);
   return r;
+}
+
+// The same into a direct-indexed table over this rank's interleaved share of the key space: key = row * key_mul + key_off.
+void Engine::merge_received_rows_dense(QueryCtx* ctx, const Plan& plan, ScanState* st, const std::vector<RowSegment>& segs, uint64_t key_off, uint64_t key_mul,
+                                       uint64_t n_keys, bool implicit_count, bool compact) {
+  cudaStream_t s = ctx->stream;
+  const int ns = plan.n_slots;
+  // (the segments may live in st->rows_*: those are released by the caller's free_state, not here)
+  unsigned long long* old_keys = st->rows_keys;
+  unsigned long long* old_slots = st->rows_slots;
+  for (void* q : {(void*)st->table, (void*)st->hkeys})
+    if (q && !((char*)q >= ctx->scratch && (char*)q < ctx->scratch + ctx->scratch_bytes)) SDO_CUDA(cudaFreeAsync(q, s));
+  st->table = nullptr; st->hkeys = nullptr;
+  st->table_preinit = false;
+  SDO_CUDA(cudaMallocAsync((void**)&st->table, std::max<uint64_t>(n_keys, 1) * (uint64_t)ns * 8, s));
+  st->params.table = st->table;
+  st->params.n_keys = n_keys;
+  st->table_rows = n_keys;
+  st->dense_key_off = key_off;
+  st->dense_key_mul = key_mul;
+  st->strategy = STRAT_GLOBAL;
+  SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
+  launch_fill_slots(st->table, n_keys, ns, nullptr, st->params, s);
+  for (auto& g : segs) launch_merge_rows_dense(g.keys, g.slots, g.n, st->params, key_off, key_mul, implicit_count, s);
+  st->launches += 1 + (int)segs.size();
+  st->rows_keys = nullptr; st->rows_slots = nullptr;
+  if (old_keys) SDO_CUDA(cudaFreeAsync(old_keys, s));   // stream-ordered: after the merges that read them
+  if (old_slots) SDO_CUDA(cudaFreeAsync(old_slots, s));
+  st->rows_valid = false;
+  st->emit_regions = false;
+  st->merged = true;
+  if (compact) compact_rows(ctx, plan, st);
 }
 
 // Which single aggregate a query wants the top K groups of (TopN with a numeric metric, or a limitSpec over one
@@ -1955,15 +2100,20 @@ bool Engine::topk_request(const Plan& plan, int* slot, int* is_f64, int* desc_ou
   return false;
 }
 
-// Fold (key, slots) rows received from other ranks (and this rank's own) into one group per key: a fresh hash table
-// sized for the rows, then compaction back to rows.  Leaves st->rows_* = this rank's share.
-void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n, bool compact) {
+// Fold (key, slots) rows -- this rank's own and those received from other ranks -- into one group per key: a fresh hash
+// table sized for the rows, then (compact) compaction back to rows.  Leaves st->rows_* = this rank's share.
+// implicit_count: raw rows of n_slots - 1 words, each counting 1.
+void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const std::vector<RowSegment>& segs, bool implicit_count, bool compact) {
   cudaStream_t s = ctx->stream;
   const int ns = plan.n_slots;
-  for (void* q : {(void*)st->table, (void*)st->hkeys, (void*)st->rows_keys, (void*)st->rows_slots})
+  unsigned long long* old_keys = st->rows_keys;
+  unsigned long long* old_slots = st->rows_slots;
+  for (void* q : {(void*)st->table, (void*)st->hkeys})
     if (q && !((char*)q >= ctx->scratch && (char*)q < ctx->scratch + ctx->scratch_bytes)) SDO_CUDA(cudaFreeAsync(q, s));
-  st->table = nullptr; st->hkeys = nullptr; st->rows_keys = nullptr; st->rows_slots = nullptr;
+  st->table = nullptr; st->hkeys = nullptr;
   st->table_preinit = false;
+  uint64_t n = 0;
+  for (auto& g : segs) n += g.n;
   const uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, n + n / 2));
   const uint32_t stride = (uint32_t)pow2_ceil((uint64_t)ns + 1);
   SDO_CUDA(cudaMallocAsync((void**)&st->table, cap * (uint64_t)stride * 8, s));
@@ -1975,9 +2125,13 @@ void Engine::merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st,
   st->strategy = STRAT_HASH;
   SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
   launch_fill_hash(st->table, cap, stride, ns, st->params, s);
-  launch_merge_rows(keys, slots, n, st->params, s);
-  st->launches += 2;
+  for (auto& g : segs) launch_merge_rows(g.keys, g.slots, g.n, st->params, s, implicit_count);
+  st->launches += 1 + (int)segs.size();
+  st->rows_keys = nullptr; st->rows_slots = nullptr;
+  if (old_keys) SDO_CUDA(cudaFreeAsync(old_keys, s));   // stream-ordered: after the merges that may read them
+  if (old_slots) SDO_CUDA(cudaFreeAsync(old_slots, s));
   st->rows_valid = false;
+  st->emit_regions = false;
   st->merged = true;
   if (compact) compact_rows(ctx, plan, st);
 }
@@ -2083,7 +2237,7 @@ void Engine::partial_merge_rows(Partial* p, const void* keys, const void* slots,
   if (!p->st.rows_valid) throw Invalid("sdo_partial_merge_rows applies to sparse partials only");
   if (p->plan.n_hll) throw Unsupported("cardinality aggregations cannot be merged on the sparse path");
   SDO_CUDA(cudaSetDevice(device_));
-  merge_received_rows(p->ctx, p->plan, &p->st, (const unsigned long long*)keys, (const unsigned long long*)slots, (uint64_t)n);
+  merge_received_rows(p->ctx, p->plan, &p->st, {{(const unsigned long long*)keys, (const unsigned long long*)slots, (uint64_t)n}}, false, true);
 }
 
 Result* Engine::partial_finish(Partial* p) {

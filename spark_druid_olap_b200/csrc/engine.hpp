@@ -103,9 +103,19 @@ struct ScanState {
   double* hll_stats = nullptr;    // per sketch (sum of 2^-register, zero registers), computed on the device
   uint64_t n_rows = 0;
   bool rows_valid = false;
+  uint64_t dense_key_mul = 1;         // ... and the key step between its rows (interleaved shares: the world size)
+  // STRAT_EMIT output split by owner: region o = rows_keys + o * emit_cap (emit_counts[o] rows)
+  int emit_owners = 0, emit_interleave = 0;
+  bool emit_regions = false;
+  bool emit_full_regions = false;     // retry after an owner's region overflowed: every region holds all rows
+  uint64_t emit_cap = 0;
+  std::vector<uint64_t> emit_counts;
+  unsigned long long* emit_cursors_dev = nullptr;
+  uint64_t dense_key_off = 0;         // dense table that holds a rank's slice of the key space: key of its row 0
   bool counted = false;               // this scan is in the engine's in-flight count
   int others_at_launch = 0;           // scans already in flight when this one was launched
   const char* shard_merge = nullptr;  // sharded execution: which merge ran (gather / reduce / sparse)
+  std::string extra_stats;            // more stats JSON members (", \"name\": value" ...)
   uint64_t exchange_bytes = 0;        // sparse merge: bytes of rows this rank sent to other ranks
 };
 
@@ -176,7 +186,10 @@ class Engine {
   int64_t next_turn_ = 0;
   std::mutex comm_mu_;
   static bool topk_request(const Plan& plan, int* slot, int* is_f64, int* desc, int64_t* k_want);
-  void merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const unsigned long long* keys, const unsigned long long* slots, uint64_t n, bool compact = true);
+  struct RowSegment { const unsigned long long* keys; const unsigned long long* slots; uint64_t n; };
+  void merge_received_rows(QueryCtx* ctx, const Plan& plan, ScanState* st, const std::vector<RowSegment>& segs, bool implicit_count, bool compact);
+  void merge_received_rows_dense(QueryCtx* ctx, const Plan& plan, ScanState* st, const std::vector<RowSegment>& segs, uint64_t key_off, uint64_t key_mul,
+                                 uint64_t n_keys, bool implicit_count, bool compact);
   Result* finalize_columnar(QueryCtx* ctx, const Plan& plan, ScanState* st, double t_start_ms);
 
   QueryCtx* acquire_ctx();

@@ -111,7 +111,7 @@ std::string prelude(int strategy, const ScanParams& p) {
   const char* nv_env = getenv("SDO_JIT_NV");  // experiment knob: vectors per dense-path accumulate call
   const char* wt_env = getenv("SDO_JIT_WARP_TICKETS");  // experiment knob: 0 = block tickets
   const char* rf_env = getenv("SDO_JIT_HLL_READ_FIRST");  // experiment knob: 0 = always issue the shared-memory atomicMax
-  std::string s = std::string("#define SDO_JIT 1\n") + (rf_env && *rf_env == '0' ? "#define SDO_HLL_READ_FIRST 0\n" : "") + "#define SDO_WARP_TICKETS " + (wt_env && *wt_env == '0' ? "0" : "1") + "\n#define SDO_DENSE_NV " + std::string(nv_env && *nv_env ? nv_env : (strategy == STRAT_SPAN ? "4" : "1")) + "\nnamespace sdo { namespace jit {\n";
+  std::string s = std::string("#define SDO_JIT 1\n") + (rf_env && *rf_env == '0' ? "#define SDO_HLL_READ_FIRST 0\n" : "") + "#define SDO_WARP_TICKETS " + (wt_env && *wt_env == '0' ? "0" : "1") + "\n#define SDO_DENSE_NV " + std::string(nv_env && *nv_env ? nv_env : (strategy == STRAT_SPAN || strategy == STRAT_EMIT ? "4" : "1")) + "\nnamespace sdo { namespace jit {\n";
   s += "constexpr int n_ops = " + std::to_string(p.n_ops) + ";\n";
   s += table<int>("op_code", p.n_ops, [&](int i) { return p.op_code[i]; });
   s += table<int>("op_arg", p.n_ops, [&](int i) { return p.op_arg[i]; });
@@ -158,6 +158,7 @@ std::string prelude(int strategy, const ScanParams& p) {
   // pass in one call at 6 blocks per SM (SF100 day timeseries + HLL: 1.26 ms before, 0.99 ms folded 4 rows at a time,
   // 0.90 ms = the HBM roofline with 16).  A narrow filtered shape (TopN over one sum) gains 4 % at 8 blocks.
   const std::string min_blocks = mb_env && *mb_env ? mb_env
+                                 : strategy == STRAT_EMIT ? "3"  // 16 rows per call keep keys, owners, ranks and positions live: 300 M rows 4.7 ms at 6 blocks (spills), 2.3 ms at 3
                                  : strategy == STRAT_SPAN && weight < 8 ? "6"
                                  : (weight >= 8 ? "3" : (weight >= 3 || p.n_hll > 0) ? "4" : (p.n_ops > 0 ? "8" : "6"));
   s += "extern \"C\" __global__ void __launch_bounds__(256, " + min_blocks + ") sdo_scan_jit(const __grid_constant__ sdo::ScanParams p, const uint32_t* __restrict__ coarse) {\n";

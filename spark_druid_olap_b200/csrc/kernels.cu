@@ -182,7 +182,7 @@ void launch_reduce_partials(const unsigned long long* partials, int n_blocks, ui
 template <bool HASH>
 __global__ void compact_kernel(const unsigned long long* __restrict__ table, uint64_t n, int ns, uint32_t stride,
                                unsigned long long* __restrict__ out_keys, unsigned long long* __restrict__ out_slots,
-                               unsigned long long* __restrict__ out_src, unsigned long long* counter) {
+                               unsigned long long* __restrict__ out_src, unsigned long long* counter, unsigned long long key_off, unsigned long long key_mul) {
   __shared__ unsigned long long s_base;
   __shared__ unsigned int s_warp[8];
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -200,22 +200,22 @@ __global__ void compact_kernel(const unsigned long long* __restrict__ table, uin
   __syncthreads();
   if (!occ) return;
   const unsigned long long o = s_base + s_warp[warp] + __popc(bal & ((1u << lane) - 1u));
-  out_keys[o] = HASH ? table[i * stride] : i;
+  out_keys[o] = HASH ? table[i * stride] : i * key_mul + key_off;
   if (out_src) out_src[o] = i;
   const unsigned long long* row = HASH ? table + i * stride + 1 : table + i * ns;
   for (int s = 0; s < ns; s++) out_slots[o * ns + s] = row[s];
 }
 void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int n_slots, unsigned long long* out_keys,
-                          unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st) {
+                          unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st, unsigned long long key_off, unsigned long long key_mul) {
   if (!n_keys) return;
-  compact_kernel<false><<<(unsigned)((n_keys + 255) / 256), 256, 0, st>>>(table, n_keys, n_slots, 0, out_keys, out_slots, out_src, counter);
+  compact_kernel<false><<<(unsigned)((n_keys + 255) / 256), 256, 0, st>>>(table, n_keys, n_slots, 0, out_keys, out_slots, out_src, counter, key_off, key_mul ? key_mul : 1);
   SDO_CUDA(cudaGetLastError());
 }
 void launch_compact_hash(const unsigned long long* table, uint64_t cap, int n_slots, uint32_t stride,
                          unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
                          unsigned long long* counter, cudaStream_t st) {
   if (!cap) return;
-  compact_kernel<true><<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(table, cap, n_slots, stride, out_keys, out_slots, out_src, counter);
+  compact_kernel<true><<<(unsigned)((cap + 255) / 256), 256, 0, st>>>(table, cap, n_slots, stride, out_keys, out_slots, out_src, counter, 0ull, 1ull);
   SDO_CUDA(cudaGetLastError());
 }
 __global__ void gather_hll_kernel(const uint8_t* __restrict__ hll, const unsigned long long* __restrict__ src, uint64_t n, int n_hll,
@@ -426,10 +426,12 @@ void launch_hll_lut_strings(const char* bytes, const int64_t* offsets, int64_t n
 // Owner rank of a key.  Rows are counted / placed with warp-aggregated shared-memory counters: one global atomic per
 // destination per block (count) or per 1024-row tile (scatter) -- per-row global atomics on n_ranks hot addresses
 // serialised at the L2 (14 ms for 18.75 M rows; 0.3 ms now).
-__device__ __forceinline__ unsigned owner_rank(unsigned long long key, int n_ranks) {
-  return (unsigned)((mix64(key * 0x9E3779B97F4A7C15ull) >> 32) % (unsigned)n_ranks);
+// key_range > 0: rank r owns keys [r * key_range, (r + 1) * key_range) -- its share of the groups is then a direct-indexed table
+__device__ __forceinline__ unsigned owner_rank(unsigned long long key, int n_ranks, unsigned long long key_range) {
+  if (key_range) return (unsigned)min((unsigned long long)(n_ranks - 1), key / key_range);
+  return shard_owner(key, (unsigned)n_ranks, 0);
 }
-__global__ void __launch_bounds__(256) partition_count_kernel(const unsigned long long* __restrict__ keys, uint64_t n, int n_ranks, unsigned long long* counts) {
+__global__ void __launch_bounds__(256) partition_count_kernel(const unsigned long long* __restrict__ keys, uint64_t n, int n_ranks, unsigned long long key_range, unsigned long long* counts) {
   __shared__ unsigned int s_hist[64];
   if (threadIdx.x < 64) s_hist[threadIdx.x] = 0;
   __syncthreads();
@@ -438,7 +440,7 @@ __global__ void __launch_bounds__(256) partition_count_kernel(const unsigned lon
   const uint64_t n_round = (n + step - 1) / step * step;  // whole warps take every iteration (match is a warp collective)
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += step) {
     const bool valid = i < n;
-    const unsigned r = valid ? owner_rank(keys[i], n_ranks) : 0xFFFFFFFFu;
+    const unsigned r = valid ? owner_rank(keys[i], n_ranks, key_range) : 0xFFFFFFFFu;
     const unsigned peers = __match_any_sync(0xffffffffu, r);
     if (valid && lane == (unsigned)__ffs(peers) - 1u) atomicAdd(&s_hist[r], (unsigned)__popc(peers));
   }
@@ -447,8 +449,8 @@ __global__ void __launch_bounds__(256) partition_count_kernel(const unsigned lon
 }
 constexpr int PART_ROWS = 4;  // rows per thread per tile
 __global__ void __launch_bounds__(256) partition_scatter_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots, uint64_t n,
-                                                                int ns, int n_ranks, unsigned long long* cursors, unsigned long long* __restrict__ out_keys,
-                                                                unsigned long long* __restrict__ out_slots) {
+                                                                int ns, int n_ranks, unsigned long long key_range, unsigned long long* cursors,
+                                                                unsigned long long* __restrict__ out_keys, unsigned long long* __restrict__ out_slots) {
   __shared__ unsigned int s_hist[64];
   __shared__ unsigned long long s_base[64];
   const unsigned lane = threadIdx.x & 31;
@@ -461,7 +463,7 @@ __global__ void __launch_bounds__(256) partition_scatter_kernel(const unsigned l
     for (int k = 0; k < PART_ROWS; k++) {
       const uint64_t i = t0 + (uint64_t)k * 256 + threadIdx.x;
       const bool valid = i < n;
-      const unsigned r = valid ? owner_rank(keys[i], n_ranks) : 0xFFFFFFFFu;
+      const unsigned r = valid ? owner_rank(keys[i], n_ranks, key_range) : 0xFFFFFFFFu;
       const unsigned peers = __match_any_sync(0xffffffffu, r);
       const int leader = __ffs(peers) - 1;
       unsigned base = 0;
@@ -487,29 +489,31 @@ __global__ void __launch_bounds__(256) partition_scatter_kernel(const unsigned l
 }
 void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
                            unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,
-                           unsigned long long* cursors_dev, cudaStream_t st) {
+                           unsigned long long* cursors_dev, cudaStream_t st, unsigned long long key_range) {
   // counts_dev must be zeroed by the caller; cursors_dev receives the exclusive prefix (host computes it between the two launches)
   if (!n) return;
   int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 8);
   if (!cursors_dev) {
-    partition_count_kernel<<<grid, 256, 0, st>>>(keys, n, n_ranks, counts_dev);
+    partition_count_kernel<<<grid, 256, 0, st>>>(keys, n, n_ranks, key_range, counts_dev);
   } else {
     grid = (int)std::min<uint64_t>((n + 256 * PART_ROWS - 1) / (256 * PART_ROWS), (uint64_t)sm_count() * 8);
-    partition_scatter_kernel<<<grid, 256, 0, st>>>(keys, slots, n, n_slots, n_ranks, cursors_dev, out_keys, out_slots);
+    partition_scatter_kernel<<<grid, 256, 0, st>>>(keys, slots, n, n_slots, n_ranks, key_range, cursors_dev, out_keys, out_slots);
   }
   SDO_CUDA(cudaGetLastError());
 }
 __global__ void merge_rows_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots, uint64_t n,
-                                  const __grid_constant__ ScanParams p) {
+                                  const __grid_constant__ ScanParams p, int implicit_count) {
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
-  const int ns = p.n_slots;
+  const int ns = p.n_slots, nsr = implicit_count ? ns - 1 : ns;
   for (; i < n; i += step) {
     uint64_t h = hash_claim(p.hkeys, p.hmask, p.hstride, keys[i]);
     if (h == HASH_EMPTY) { p.counters[1] = 1; continue; }
-    for (int s = 0; s < ns; s++) {
-      unsigned long long v = slots[i * ns + s];
-      unsigned long long* q = p.table + h * p.hstride + 1 + s;
+    unsigned long long* row = p.table + h * p.hstride + 1;
+    if (implicit_count) atomicAdd(row, 1ull);
+    for (int s = implicit_count ? 1 : 0; s < ns; s++) {
+      unsigned long long v = slots[i * nsr + (implicit_count ? s - 1 : s)];
+      unsigned long long* q = row + s;
       const int op = p.slot_op[s];
       if (op == SLOT_SUM_I64) atomicAdd(q, v);
       else if (op == SLOT_SUM_F64) atomicAdd((double*)q, __longlong_as_double(v));
@@ -518,10 +522,39 @@ __global__ void merge_rows_kernel(const unsigned long long* __restrict__ keys, c
     }
   }
 }
-void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st) {
+// rows merged into a direct-indexed table (no key storage, no probing): row of key k = (k - key_off) / key_mul
+__global__ void merge_rows_dense_kernel(const unsigned long long* __restrict__ keys, const unsigned long long* __restrict__ slots, uint64_t n,
+                                        const __grid_constant__ ScanParams p, unsigned long long key_off, unsigned long long key_mul, int implicit_count) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const uint64_t step = (uint64_t)gridDim.x * blockDim.x;
+  const int ns = p.n_slots, nsr = implicit_count ? ns - 1 : ns;
+  for (; i < n; i += step) {
+    const unsigned long long d = keys[i] - key_off, g = d / key_mul;
+    if (keys[i] < key_off || g * key_mul != d || g >= p.n_keys) { p.counters[1] = 1; continue; }
+    unsigned long long* row = p.table + g * ns;
+    if (implicit_count) atomicAdd(row, 1ull);
+    for (int s = implicit_count ? 1 : 0; s < ns; s++) {
+      const unsigned long long v = slots[i * nsr + (implicit_count ? s - 1 : s)];
+      unsigned long long* q = row + s;
+      const int op = p.slot_op[s];
+      if (op == SLOT_SUM_I64) atomicAdd(q, v);
+      else if (op == SLOT_SUM_F64) atomicAdd((double*)q, __longlong_as_double(v));
+      else if (op == SLOT_MIN_I64) atomicMin((long long*)q, (long long)v);
+      else atomicMax((long long*)q, (long long)v);
+    }
+  }
+}
+void launch_merge_rows_dense(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, unsigned long long key_off,
+                             unsigned long long key_mul, bool implicit_count, cudaStream_t st) {
   if (!n) return;
   int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 8);
-  merge_rows_kernel<<<grid, 256, 0, st>>>(keys, slots, n, p);
+  merge_rows_dense_kernel<<<grid, 256, 0, st>>>(keys, slots, n, p, key_off, key_mul ? key_mul : 1, implicit_count ? 1 : 0);
+  SDO_CUDA(cudaGetLastError());
+}
+void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st, bool implicit_count) {
+  if (!n) return;
+  int grid = (int)std::min<uint64_t>((n + 255) / 256, (uint64_t)sm_count() * 8);
+  merge_rows_kernel<<<grid, 256, 0, st>>>(keys, slots, n, p, implicit_count ? 1 : 0);
   SDO_CUDA(cudaGetLastError());
 }
 

@@ -177,10 +177,26 @@ struct ScanParams {
   uint32_t rep_stride;
   unsigned int* counters;       // [0] chunk ticket, [1] overflow flag
   // EMIT: output rows (same layout as compacted groups: keys[n], slots[n][n_slots]); the cursor is the u64 at counters + 4
+  // Rows carry n_slots - 1 words (slot 0, the row count, is 1 by construction and is not stored).  With emit_owners > 1 the
+  // rows are split on the way out by the rank that owns their key (interleaved: key mod owners, or by hash): owner o's rows
+  // go to keys[o * emit_cap ...] / slots[o * emit_cap * (n_slots - 1) ...] under cursor emit_cursors[o].
   unsigned long long* emit_keys;
   unsigned long long* emit_slots;
-  uint64_t emit_cap;
+  unsigned long long* emit_cursors;  // [max(emit_owners, 1)] rows written per owner
+  uint64_t emit_cap;                 // rows per owner region
+  int32_t emit_owners;               // 0 / 1: one stream
+  int32_t emit_interleave;           // 1: owner = key mod owners; 0: owner = mix(key) mod owners
 };
+// who owns a key in a sharded exchange (the same on device and host)
+#ifdef __CUDACC__
+__host__ __device__
+#endif
+inline unsigned shard_owner(unsigned long long key, unsigned owners, int interleave) {
+  if (interleave) return (unsigned)(key % owners);
+  unsigned long long x = key * 0x9E3779B97F4A7C15ull;
+  x ^= x >> 33; x *= 0xff51afd7ed558ccdull; x ^= x >> 33; x *= 0xc4ceb9fe1a85ec53ull; x ^= x >> 33;
+  return (unsigned)((x >> 32) % owners);
+}
 
 #ifndef __CUDACC_RTC__
 // ---- launchers (host) ---------------------------------------------------------------------------
@@ -208,7 +224,8 @@ void launch_reduce_partials(const unsigned long long* partials, int n_blocks, ui
                             unsigned long long* out, cudaStream_t st);
 // compaction of non-empty groups: dense tables (keyed by slot 0 > 0) and hash tables
 void launch_compact_dense(const unsigned long long* table, uint64_t n_keys, int n_slots, unsigned long long* out_keys,
-                          unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st);
+                          unsigned long long* out_slots, unsigned long long* out_src, unsigned long long* counter, cudaStream_t st,
+                          unsigned long long key_off = 0, unsigned long long key_mul = 1);  // out key = index * key_mul + key_off
 void launch_compact_hash(const unsigned long long* table, uint64_t cap, int n_slots, uint32_t stride,
                          unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* out_src,
                          unsigned long long* counter, cudaStream_t st);
@@ -231,6 +248,7 @@ struct SelView {
   uint32_t stride;     // words per row / bucket
   uint32_t slot_off;   // word of the ordering aggregate inside a row / bucket
   uint32_t slot0_off;  // word of slot 0 inside a row / bucket (ROWS / DENSE: 0, HASH: 1)
+  unsigned long long key_off, key_mul;  // DENSE: key of row i = i * key_mul + key_off (a rank's interleaved share of a key space); key_mul 0 = 1
   int32_t kind, is_f64, desc;
 };
 struct SelState {  // device-resident search state, zeroed before the first pass
@@ -274,13 +292,17 @@ void launch_materialize(const unsigned long long* keys, const unsigned long long
 // sparse multi-GPU merge helpers
 void launch_partition_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, int n_slots, int n_ranks,
                            unsigned long long* out_keys, unsigned long long* out_slots, unsigned long long* counts_dev,
-                           unsigned long long* cursors_dev, cudaStream_t st);
+                           unsigned long long* cursors_dev, cudaStream_t st, unsigned long long key_range = 0);  // key_range > 0: owner = key / key_range, else by hash
 // dense multi-GPU merge: fold n_ranks gathered blobs (table + HLL registers each) into this rank's table
 void launch_merge_gathered(const unsigned long long* gathered, int n_ranks, size_t blob_bytes, size_t table_bytes, uint64_t cells, int n_slots,
                            const ScanParams& p, unsigned long long* table, cudaStream_t st);
 // [key][slot] <-> [slot][key] (the layout a per-slot ncclReduce needs)
 void launch_slot_transpose(const unsigned long long* in, unsigned long long* out, uint64_t n_keys, int n_slots, bool to_slot_major, cudaStream_t st);
-void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st);
+// implicit_count: the rows are raw rows (STRAT_EMIT): n_slots - 1 words each, slot 0 += 1 per row
+void launch_merge_rows(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, cudaStream_t st, bool implicit_count = false);
+// the same into a direct-indexed table of p.n_keys rows: row of key k = (k - key_off) / key_mul (keys that do not map raise the overflow flag)
+void launch_merge_rows_dense(const unsigned long long* keys, const unsigned long long* slots, uint64_t n, const ScanParams& p, unsigned long long key_off,
+                             unsigned long long key_mul, bool implicit_count, cudaStream_t st);
 
 // select queries: per-unit counts of passing rows; then, for the units that hold the wanted page, the passing rows with
 // rank in [skip, skip + take) in row order; then a gather of each requested column

@@ -570,43 +570,92 @@ __device__ __forceinline__ void eval_expr_m(const ScanParams& p, int e, const vo
   }
 }
 
-// STRAT_EMIT: write the rows of `r0` with a bit in m out as groups of one row each: key, slot 0 = 1, and for every
-// aggregator the value its slot would have received (its identity where the aggregator's own filter fails).
-// WARP = all 32 lanes are here: one cursor bump per warp; otherwise (row-by-row path under divergence) one per row.
+// STRAT_EMIT: write the rows of `r0` with a bit in m out as groups of one row each: the key and, for every aggregator,
+// the value its slot would have received (its identity where the aggregator's own filter fails).  Slot 0, the row count,
+// is 1 by construction and is not stored: a row is n_slots - 1 words.  With emit_owners > 1 every row goes to the region
+// of the rank that owns its key.  WARP = all 32 lanes are here: cursor bumps are aggregated over the warp (per owner);
+// otherwise (row-by-row path under divergence) one bump per row.
 template <int N, int NV, bool WARP>
 __device__ __forceinline__ void emit_rows(const ScanParams& p, const void* const* cols, const uint64_t (&key)[N * NV], const RowSet<NV>& r0, uint32_t m) {
   constexpr int R = N * NV;
-  const int ns = Q_N_SLOTS;
-  unsigned long long* cursor = (unsigned long long*)(p.counters + 4);
-  const int c = __popc(m);
-  unsigned long long pos0;
-  if (WARP) {
-    int incl = c;
+  const int nsr = Q_N_SLOTS - 1;
+  unsigned long long pos[R];  // row index inside the output arrays (owner region included)
+  if (p.emit_owners > 1) {
+    const unsigned W = (unsigned)p.emit_owners;
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned own[R];
 #pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-      const int t = __shfl_up_sync(0xffffffffu, incl, off);
-      if ((int)(threadIdx.x & 31u) >= off) incl += t;
+    for (int i = 0; i < R; i++) own[i] = ((m >> i) & 1u) ? shard_owner(key[i], W, p.emit_interleave) : 0xFFFFFFFFu;
+    if (WARP && W <= 32) {
+      // One cursor bump per owner for all the rows of the call (16 per lane on the specialised kernel): lane o counts owner
+      // o's rows with ballots while every row learns its rank among them; W bumps per 512 rows instead of W per 32.
+      unsigned rank[R];
+      unsigned mine = 0;  // lane o: rows of owner o in this call
+      for (unsigned o = 0; o < W; o++) {
+        unsigned run = 0;
+#pragma unroll
+        for (int i = 0; i < R; i++) {
+          const unsigned b = __ballot_sync(0xffffffffu, own[i] == o);
+          if (own[i] == o) rank[i] = run + (unsigned)__popc(b & ((1u << lane) - 1u));
+          run += (unsigned)__popc(b);
+        }
+        if (lane == o) mine = run;
+      }
+      unsigned long long base = 0;
+      if (lane < W && mine) base = atomicAdd(p.emit_cursors + lane, (unsigned long long)mine);
+#pragma unroll
+      for (int i = 0; i < R; i++) {
+        const unsigned long long q = __shfl_sync(0xffffffffu, base, own[i] & 31u) + rank[i];
+        if (own[i] != 0xFFFFFFFFu && q >= p.emit_cap) { p.counters[1] = 1; m &= ~(1u << i); }
+        pos[i] = (unsigned long long)own[i] * p.emit_cap + q;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < R; i++) {
+        const bool on = own[i] != 0xFFFFFFFFu;
+        unsigned long long q = 0;
+        if (WARP) {
+          const unsigned peers = __match_any_sync(0xffffffffu, own[i]);
+          const int leader = __ffs(peers) - 1;
+          if (on && (int)lane == leader) q = atomicAdd(p.emit_cursors + own[i], (unsigned long long)__popc(peers));
+          q = __shfl_sync(0xffffffffu, q, leader);
+          q += (unsigned long long)__popc(peers & ((1u << lane) - 1u));
+        } else if (on) {
+          q = atomicAdd(p.emit_cursors + own[i], 1ull);
+        }
+        if (on && q >= p.emit_cap) { p.counters[1] = 1; m &= ~(1u << i); }
+        pos[i] = (unsigned long long)own[i] * p.emit_cap + q;
+      }
     }
-    const int total = __shfl_sync(0xffffffffu, incl, 31);
-    unsigned long long base = 0;
-    if ((threadIdx.x & 31u) == 0 && total) base = atomicAdd(cursor, (unsigned long long)total);
-    base = __shfl_sync(0xffffffffu, base, 0);
-    pos0 = base + (unsigned long long)(incl - c);
+    if (!m) return;
   } else {
+    const int c = __popc(m);
+    unsigned long long pos0;
+    if (WARP) {
+      int incl = c;
+#pragma unroll
+      for (int off = 1; off < 32; off <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, off);
+        if ((int)(threadIdx.x & 31u) >= off) incl += t;
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      unsigned long long base = 0;
+      if ((threadIdx.x & 31u) == 0 && total) base = atomicAdd(p.emit_cursors, (unsigned long long)total);
+      base = __shfl_sync(0xffffffffu, base, 0);
+      pos0 = base + (unsigned long long)(incl - c);
+    } else {
+      if (!c) return;
+      pos0 = atomicAdd(p.emit_cursors, (unsigned long long)c);
+    }
     if (!c) return;
-    pos0 = atomicAdd(cursor, (unsigned long long)c);
-  }
-  if (!c) return;
-  if (pos0 + (unsigned long long)c > p.emit_cap) { p.counters[1] = 1; return; }
-  unsigned long long pos[R];
-  {
+    if (pos0 + (unsigned long long)c > p.emit_cap) { p.counters[1] = 1; return; }
     unsigned long long q = pos0;
 #pragma unroll
     for (int i = 0; i < R; i++) { pos[i] = q; q += (m >> i) & 1u; }
   }
 #pragma unroll
   for (int i = 0; i < R; i++)
-    if ((m >> i) & 1u) { p.emit_keys[pos[i]] = key[i]; p.emit_slots[pos[i] * ns] = 1ull; }
+    if ((m >> i) & 1u) p.emit_keys[pos[i]] = key[i];
   Q_UNROLL
   for (int a = 0; a < Q_N_AGGS; a++) {
     uint32_t ma = m;
@@ -642,7 +691,7 @@ __device__ __forceinline__ void emit_rows(const ScanParams& p, const void* const
     }
 #pragma unroll
     for (int i = 0; i < R; i++)
-      if ((m >> i) & 1u) p.emit_slots[pos[i] * ns + slot] = ((ma >> i) & 1u) ? out[i] : ident;
+      if ((m >> i) & 1u) p.emit_slots[pos[i] * nsr + (slot - 1)] = ((ma >> i) & 1u) ? out[i] : ident;
   }
 }
 

@@ -30,7 +30,7 @@ __device__ __forceinline__ bool sel_live(const SelView& v, uint64_t i) {
   return v.keys[i] != ~0ull;
 }
 __device__ __forceinline__ unsigned long long sel_key(const SelView& v, uint64_t i) {
-  return v.kind == SEL_DENSE ? i : (v.kind == SEL_HASH ? v.base[i * v.stride] : v.keys[i]);
+  return v.kind == SEL_DENSE ? i * (v.key_mul ? v.key_mul : 1ull) + v.key_off : (v.kind == SEL_HASH ? v.base[i * v.stride] : v.keys[i]);
 }
 // order value: larger = ranks earlier
 __device__ __forceinline__ unsigned long long sel_ord(const SelView& v, uint64_t i) {
