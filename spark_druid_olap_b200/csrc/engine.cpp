@@ -98,6 +98,8 @@ Engine::~Engine() {
 }
 
 QueryCtx* Engine::acquire_ctx() {
+  // every query starts here: a caller thread that has never touched CUDA has device 0 current, whatever the engine's is
+  if (device_ >= 0) SDO_CUDA(cudaSetDevice(device_));
   {
     std::lock_guard<std::mutex> lk(ctx_mu_);
     if (!free_ctx_.empty()) {
@@ -1697,12 +1699,20 @@ void Engine::comm_init(const void* id, int rank, int world) {
 // its first collective to its last (its scan runs before that, concurrently with other queries).  Callers that run
 // several sharded queries at once give each a turn number -- the same number on every rank, consecutive from 0 -- and
 // the engine issues their collectives in that order; without a number (turn < 0) the caller keeps the ranks in step.
+static bool turn_trace() {
+  static const bool on = [] { const char* v = getenv("SDO_TURN_TRACE"); return v && v[0] == '1'; }();
+  return on;
+}
+#define SDO_TRACE(...) do { if (turn_trace()) { fprintf(stderr, "[sdo rank %d %.3f] ", comm_rank_trace, now_ms()); fprintf(stderr, __VA_ARGS__); fprintf(stderr, "\n"); fflush(stderr); } } while (0)
+static thread_local int comm_rank_trace = -1;
+
 struct Engine::CommTurn {
   Engine* e;
   int64_t turn;
   bool held = false;
-  CommTurn(Engine* e_, int64_t turn_) : e(e_), turn(turn_) {}
+  CommTurn(Engine* e_, int64_t turn_) : e(e_), turn(turn_) { comm_rank_trace = e->comm_rank_; }
   void acquire() {
+    SDO_TRACE("turn %lld wants the communicator (next %lld)", (long long)turn, (long long)e->next_turn_);
     std::unique_lock<std::mutex> lk(e->turn_mu_);
     auto ready = [&] { return !e->turn_busy_ && (turn < 0 || e->next_turn_ == turn); };
     if (turn >= 0 && turn < e->next_turn_) throw Invalid("sdo_query_execute_sharded_at: turn " + std::to_string((long long)turn) + " has already been taken");
@@ -1710,9 +1720,11 @@ struct Engine::CommTurn {
       throw std::runtime_error("sharded query: turn " + std::to_string((long long)turn) + " never came (the turn before it was not issued on this rank)");
     e->turn_busy_ = true;
     held = true;
+    SDO_TRACE("turn %lld holds the communicator", (long long)turn);
   }
   ~CommTurn() {
     std::unique_lock<std::mutex> lk(e->turn_mu_);
+    SDO_TRACE("turn %lld done (held %d)", (long long)turn, (int)held);
     if (held) {
       e->turn_busy_ = false;
       if (turn >= 0) e->next_turn_ = turn + 1;
@@ -1817,6 +1829,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       if (!gathered) gathered = dev_alloc(blob * comm_world_);
       turn.acquire();
       nccl_all_gather_bytes(comm_, st.table, gathered, blob, s);
+      SDO_TRACE("turn %lld gather queued", (long long)turn_no);
       if (comm_rank_ == root) {
         launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)ns, ns, st.params, st.table, s);
         st.launches += 1;
@@ -1914,6 +1927,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
         }
         nccl_group_end();
         mark_here();  // [2] exchanged
+        SDO_TRACE("turn %lld exchange queued (%llu rows in)", (long long)turn_no, (unsigned long long)m);
         st.launches += 1;
         st.exchange_bytes = sent * (uint64_t)(nsr + 1) * 8;
         segments.push_back({st.rows_keys + (uint64_t)comm_rank_ * st.emit_cap, st.rows_slots + (uint64_t)comm_rank_ * st.emit_cap * nsr, st.emit_counts[comm_rank_]});

@@ -80,6 +80,42 @@ for pass_name in ("host-merge", "library"):
       except AssertionError as e:
           ok = False
           print(f"FAIL {name} [{pass_name}] rank {rank}: {e}", flush=True)
+# callers on threads of their own (a JVM executor's task threads): a thread that has never touched CUDA has device 0
+# current, whatever the engine's device is -- every rank but 0 exercises that here; turn numbers order the merges
+import threading  # noqa: E402
+thread_out, thread_err = {}, []
+base = eng.sharded_next_turn()
+shapes_t = [("q1", Q.q1_style(), False), ("q5t", Q.q5_topn(), True), ("q3_limit10_emit", Q.q3(10, "emit"), True), ("ts_month_hll", Q.timeseries("P1M"), False)]
+
+
+def _call(i):
+    try:
+        name, spec, ordered = shapes_t[i % len(shapes_t)]
+        res, _ = sharded.execute_sharded(eng, json.loads(spec.to_json()), turn=base + i)
+        thread_out[i] = H.engine_rows(res) if res is not None else []
+        if i == 0:
+            thread_out["local"] = H.engine_rows(eng.execute(json.loads(Q.q1_style().to_json())))  # a plain query from a fresh thread
+    except Exception as ex:  # noqa: BLE001
+        thread_err.append(f"thread {i}: {ex!r}")
+
+
+ths = [threading.Thread(target=_call, args=(i,)) for i in reversed(range(8))]
+for th in ths:
+    th.start()
+for th in ths:
+    th.join(90)
+if thread_err or any(th.is_alive() for th in ths):
+    ok = False
+    print(f"FAIL threads rank {rank}: {thread_err[:2]} alive={sum(th.is_alive() for th in ths)}", flush=True)
+elif rank == 0:
+    try:
+        for i in range(8):
+            name, spec, ordered = shapes_t[i % len(shapes_t)]
+            H.assert_rows_equal(thread_out[i], orc.execute(whole, json.loads(spec.to_json())), ordered=ordered, what=f"thread {i} {name}")
+        print("OK   8 caller threads, turn-ordered merges", flush=True)
+    except AssertionError as e:
+        ok = False
+        print(f"FAIL threads: {e}", flush=True)
 flag = torch.tensor([0 if ok else 1], device="cuda")
 dist.all_reduce(flag)
 if rank == 0:
