@@ -39,14 +39,6 @@ def run_both(loaded, spec, ordered=False, what=""):
     return res, want
 
 
-def strategies_for(spec_fn):
-    # every strategy that can hold the key space must give the same answer
-    out = []
-    for s in (None, "lane", "block", "global", "hash"):
-        out.append(s)
-    return out
-
-
 @pytest.mark.parametrize("strategy", [None, "lane", "block", "global", "hash"])
 def test_q1_style_all_strategies(loaded, strategy):
     res, _ = run_both(loaded, Q.q1_style(strategy), what=f"q1[{strategy}]")
