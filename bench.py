@@ -311,6 +311,10 @@ def main():
                 t1 = time.perf_counter()
                 partials[n].append(c_oracle.execute_partial(cs.ct, as_groupby(SH[n][0]), threads))
                 if n == "q1_style":
+                    # the CPU baseline: the same call once more, now that the table-side preparation (codes re-ranked by the
+                    # dictionary's byte order) is cached -- query work only, as in the reference arm
+                    t1 = time.perf_counter()
+                    c_oracle.execute_partial(cs.ct, as_groupby(SH[n][0]), threads)
                     cpu_q1.append((time.perf_counter() - t1, tab.n_rows))
             if "by_orderkey_top10" in names:
                 k = tab.data["o_orderkey"]
