@@ -359,11 +359,42 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   st->strategy = strat;
   const uint64_t cells = plan.n_keys * (uint64_t)plan.n_slots;
 
+  // rows that pass the filter, counted exactly by a scan without keys or aggregates (cached per plan by the callers)
+  auto count_passing = [&]() -> uint64_t {
+      ScanParams c = p;
+    c.n_dims = 0;
+    c.n_aggs = 0;
+    c.n_keys = 1;
+    c.n_slots = 1;
+    c.n_hll = 0;
+    c.ignore_key_base = 1;
+    size_t smem = scan_smem_bytes(STRAT_LANE, 1, 1);
+    int grid = scan_grid_size(STRAT_LANE, smem, sm_count_);
+    unsigned long long* part = nullptr;
+    SDO_CUDA(cudaMallocAsync((void**)&part, (size_t)(grid + 1) * 8, s));
+    c.table = part;
+    launch_scan(STRAT_LANE, c, grid, smem, s);
+    launch_reduce_partials(part, grid, 1, 1, c, part + grid, s);
+    unsigned long long cnt = 0;
+    SDO_CUDA(cudaMemcpyAsync(&cnt, part + grid, 8, cudaMemcpyDeviceToHost, s));
+    SDO_CUDA(cudaStreamSynchronize(s));
+    SDO_CUDA(cudaFreeAsync(part, s));
+    SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
+    st->launches += 2;
+    st->d2h_bytes += 8;
+    return cnt;
+  };
   if (strat == STRAT_EMIT) {
     // No table: the surviving rows come out as groups of one row each, n_slots - 1 words per row, split by owner when the
     // caller (a sharded query) names the owners.  A region holds its fair share of the rows and a quarter more; keys
     // skewed beyond that raise the overflow flag and the scan is repeated with regions that hold everything.
-    const uint64_t cap_all = (uint64_t)std::max<int64_t>(plan.rows_scanned, 1);
+    uint64_t cap_all = (uint64_t)std::max<int64_t>(plan.rows_scanned, 1);
+    if (p.n_ops > 0) {
+      // a filter can shrink the output a hundredfold: size it from the exact count of passing rows (first run of the plan)
+      int64_t known = plan.passing_rows.load();
+      if (known < 0) { known = (int64_t)count_passing(); plan.passing_rows.store(known); }
+      cap_all = (uint64_t)std::max<int64_t>(known, 1);
+    }
     const int owners = std::max(1, st->emit_owners);
     const int nsr = plan.n_slots - 1;
     st->emit_cap = owners > 1 && !st->emit_full_regions ? std::min<uint64_t>(cap_all, cap_all / owners + cap_all / (4 * owners) + 65536) : cap_all;
@@ -382,33 +413,13 @@ void Engine::run_scan(QueryCtx* ctx, const Plan& plan, ScanState* st) {
   } else if (strat == STRAT_HASH) {
     // size the table from an exact count of passing rows when a filter can shrink it
     uint64_t rows_upper = (uint64_t)plan.rows_scanned;
-    const int64_t known = plan.passing_rows.v.load();
+    const int64_t known = plan.passing_rows.load();
     if (p.n_ops > 0 && known >= 0) {
       rows_upper = (uint64_t)known;  // counted by an earlier run of this cached plan
     } else if (p.n_ops > 0) {
-      ScanParams c = p;
-      c.n_dims = 0;
-      c.n_aggs = 0;
-      c.n_keys = 1;
-      c.n_slots = 1;
-      c.n_hll = 0;
-      c.ignore_key_base = 1;
-      size_t smem = scan_smem_bytes(STRAT_LANE, 1, 1);
-      int grid = scan_grid_size(STRAT_LANE, smem, sm_count_);
-      unsigned long long* part = nullptr;
-      SDO_CUDA(cudaMallocAsync((void**)&part, (size_t)(grid + 1) * 8, s));
-      c.table = part;
-      launch_scan(STRAT_LANE, c, grid, smem, s);
-      launch_reduce_partials(part, grid, 1, 1, c, part + grid, s);
-      unsigned long long cnt = 0;
-      SDO_CUDA(cudaMemcpyAsync(&cnt, part + grid, 8, cudaMemcpyDeviceToHost, s));
-      SDO_CUDA(cudaStreamSynchronize(s));
-      SDO_CUDA(cudaFreeAsync(part, s));
-      SDO_CUDA(cudaMemsetAsync(ctx->counters, 0, COUNTER_BYTES, s));
-      st->launches += 2;
-      st->d2h_bytes += 8;
+      const unsigned long long cnt = count_passing();
       rows_upper = cnt;
-      plan.passing_rows.v.store((int64_t)cnt);
+      plan.passing_rows.store((int64_t)cnt);
     }
     uint64_t groups_upper = std::min<uint64_t>(plan.n_keys, rows_upper);
     uint64_t cap = pow2_ceil(std::max<uint64_t>(1024, groups_upper + groups_upper / 2));
@@ -1722,10 +1733,23 @@ struct Engine::CommTurn {
     held = true;
     SDO_TRACE("turn %lld holds the communicator", (long long)turn);
   }
+  // The order NCCL cares about is the order its calls are ISSUED in: once a query's last collective has been queued the next
+  // turn may issue its own, while this query's stream still waits for the data and the host finishes the result.
+  void release() {
+    std::unique_lock<std::mutex> lk(e->turn_mu_);
+    if (!held || released) return;
+    released = true;
+    e->turn_busy_ = false;
+    if (turn >= 0) e->next_turn_ = turn + 1;
+    SDO_TRACE("turn %lld released", (long long)turn);
+    e->turn_cv_.notify_all();
+  }
+  bool released = false;
   ~CommTurn() {
     std::unique_lock<std::mutex> lk(e->turn_mu_);
     SDO_TRACE("turn %lld done (held %d)", (long long)turn, (int)held);
-    if (held) {
+    if (held && released) {
+    } else if (held) {
       e->turn_busy_ = false;
       if (turn >= 0) e->next_turn_ = turn + 1;
     } else if (turn >= 0 && turn >= e->next_turn_) {
@@ -1830,6 +1854,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       turn.acquire();
       nccl_all_gather_bytes(comm_, st.table, gathered, blob, s);
       SDO_TRACE("turn %lld gather queued", (long long)turn_no);
+      turn.release();
       if (comm_rank_ == root) {
         launch_merge_gathered((const unsigned long long*)gathered, comm_world_, st.dense_blob_bytes, st.dense_table_bytes, st.table_rows * (uint64_t)ns, ns, st.params, st.table, s);
         st.launches += 1;
@@ -1850,6 +1875,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       }
       if (plan->n_hll) nccl_reduce(comm_, st.hll, st.hll, plan->n_keys * (uint64_t)plan->n_hll * HLL_M, NcclType::U8, NcclOp::Max, root, s);
       nccl_group_end();
+      turn.release();
       st.launches += 2;
       if (comm_rank_ == root) {
         launch_slot_transpose(tr, st.table, plan->n_keys, ns, false, s);
@@ -1981,11 +2007,17 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
       }
       // This rank's share: rows, or (top-K) the merged table as it stands.  Keys dealt out round-robin (key mod world) leave
       // every rank a slice it can index directly -- no key storage, no probing; hashed keys go into a hash table.
-      if (emit && st.emit_regions && st.emit_interleave)
+      uint64_t rows_in = 0;
+      for (auto& g : segments) rows_in += g.n;
+      const uint64_t share_keys = (plan->n_keys + (uint64_t)W - 1) / (uint64_t)W;
+      // (a direct table only pays when the rows fill a fair part of it: a filtered query with few survivors would spend its
+      // time initialising and searching gigabytes of empty rows)
+      if (emit && st.emit_regions && st.emit_interleave && rows_in * 8 >= share_keys)
         merge_received_rows_dense(ctx, *plan, &st, segments, (uint64_t)comm_rank_, (uint64_t)W, (plan->n_keys + (uint64_t)W - 1) / (uint64_t)W, emit, /*compact=*/!want_topk);
       else
         merge_received_rows(ctx, *plan, &st, segments, emit, /*compact=*/!want_topk);
       mark_here();  // [3] merged
+      if (!want_topk) turn.release();  // the exchange was this query's last collective
       if (want_topk) {
         const int k = (int)k_want;
         unsigned long long* cand_k = (unsigned long long*)dev_alloc((size_t)k * 8 * W);
@@ -2026,6 +2058,7 @@ Result* Engine::execute_sharded(const char* json, size_t len, int root, int64_t 
         nccl_all_gather_bytes(comm_, mine_k, cand_k, (size_t)k * 8, s);
         nccl_all_gather_bytes(comm_, mine_s, cand_s, (size_t)k * ns * 8, s);
         nccl_group_end();
+        turn.release();
         if (comm_rank_ == root) {
           // the candidates replace the share: finalize orders them on the host and cuts at K
           if (st.rows_keys) SDO_CUDA(cudaFreeAsync(st.rows_keys, s));

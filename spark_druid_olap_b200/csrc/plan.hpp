@@ -55,12 +55,11 @@ struct HostLeaf {
   std::vector<uint32_t> bitset;  // BITSET payload
 };
 
-// a value several queries of one cached plan may read and set (copying a plan copies the value)
+// a value several queries of one cached plan may read and set; copies of the plan (per-query variants) share it
 struct SharedCount {
-  std::atomic<int64_t> v{-1};
-  SharedCount() = default;
-  SharedCount(const SharedCount& o) : v(o.v.load()) {}
-  SharedCount& operator=(const SharedCount& o) { v.store(o.v.load()); return *this; }
+  std::shared_ptr<std::atomic<int64_t>> p = std::make_shared<std::atomic<int64_t>>(-1);
+  int64_t load() const { return p->load(); }
+  void store(int64_t x) const { p->store(x); }
 };
 
 struct Plan {
