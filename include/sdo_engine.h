@@ -124,7 +124,8 @@ int sdo_datasource_segments(sdo_engine* e, const char* name, const char** json_o
  *   javascript filters / extraction functions / aggregations are accepted when the function is a single
  *     `return <expression>` (comparisons, string methods, arithmetic); nothing of it runs per row.
  *   context keys read: queryId, skipEmptyBuckets, gpuTimeBoundary, and the test knobs gpuStrategy,
- *     gpuJit, gpuHllPlace, gpuTicketRows, gpuShardMerge; unknown keys are ignored.
+ *     gpuJit (true: wait for the shape's specialised kernel instead of running ahead-of-time code while it compiles),
+ *     gpuHllPlace, gpuTicketRows, gpuShardMerge; gpuStrategy emit = exchange raw rows in a sharded query; unknown keys are ignored.
  *     skipEmptyBuckets defaults to TRUE here (Druid: false): the parity target is Spark running the
  *     un-rewritten plan, which has no rows for empty buckets.  An explicit false is honoured for
  *     timeseries queries (one row per granularity bucket between the datasource's first and last
@@ -251,14 +252,17 @@ int sdo_datasource_restore(sdo_engine* e, const char* name, const char* path);
  *   reduce : larger dense tables (up to 64 MB) -- the table is transposed to [slot][key] and every slot reduced to `root`
  *            with its own operator (ncclReduce int64 / float64 sum, int64 min / max), HLL registers as uint8 max, one
  *            NCCL group;
- *   sparse : hash tables and key spaces beyond that -- every rank turns its groups into (key, slots) rows, splits them
- *            by owner = mix(key) mod world, exchanges them with grouped ncclSend / ncclRecv and merges what it
- *            receives, so it owns a disjoint share of the groups.  A query that asks for the top K <= 1024 groups by
- *            one aggregate (TopN with a numeric metric, limitSpec over one aggregate column, no having) takes the top K
- *            of every share, all-gathers the K * world candidates and finishes on `root`.  Any other sparse query
- *            returns, on EVERY rank, that rank's share of the groups (*out non-NULL everywhere; the caller unions them,
- *            as Spark unions partitions); ordering / limit / having then apply per share.  Cardinality aggregations
- *            have no sparse merge (SDO_UNSUPPORTED before anything is queued).
+ *   sparse : key spaces beyond that.  Such key spaces have about as many groups as rows on every rank, so nothing is
+ *            aggregated locally: the scan writes every surviving row (key + the aggregators' inputs, count implicit)
+ *            straight into the region of the rank that owns its key -- keys are dealt round-robin (key mod world) when a
+ *            rank's share of the key space fits a direct-indexed table, by hash otherwise --, the regions are exchanged
+ *            with grouped ncclSend / ncclRecv and every rank aggregates what it owns once.  A query that asks for the top
+ *            K <= 1024 groups by one aggregate (TopN with a numeric metric, limitSpec over one aggregate column, no
+ *            having) takes the top K of every share, all-gathers the K * world candidates and finishes on `root`.  Any
+ *            other sparse query returns, on EVERY rank, that rank's share of the groups (*out non-NULL everywhere; the
+ *            caller unions them, as Spark unions partitions); ordering / limit / having then apply per share.
+ *            Cardinality aggregations have no sparse merge (SDO_UNSUPPORTED before anything is queued).
+ *            Stats of a sparse merge carry shardPhasesMs (split / exchange / merge / topk device times) and exchangeBytes.
  *
  * sdo_comm_unique_id: on one rank; hand the 128 bytes to every rank (any channel).  `nccl_library` = path of
  *   libnccl.so.2 to load if the process has none loaded yet (NULL: default search path).
