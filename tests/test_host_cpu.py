@@ -280,3 +280,68 @@ def test_persistence_error_paths(planning, tmp_path):
     (tmp_path / "junk").write_bytes(b"SDOSEG01")
     with pytest.raises(sdo.NoDevice):
         eng.restore_datasource("r", tmp_path / "junk")  # segments live in HBM: no device, no restore
+
+
+def test_filter_program_never_needs_more_than_the_device_stack(planning):
+    """and / or children are emitted deepest first: 12 leaves nested alternately (and(a, or(b, and(c, ...)))) need a
+    12-entry stack when emitted left to right, and the device evaluator holds 8 masks.  The emitted postfix program must
+    evaluate (on a host stack machine) with at most 8 live entries -- here 2 -- and compute the same boolean function."""
+    import itertools
+    eng, _, _ = planning
+    leaves = [Q.ExtractionFilterSpec("s_nation", ["PERU", "CHINA", "KENYA"]), Q.ExtractionFilterSpec("c_nation", ["FRANCE", "INDIA"]),
+              Q.ExtractionFilterSpec("l_shipmode", ["AIR", "SHIP"]), Q.ExtractionFilterSpec("p_brand", ["Brand#11", "Brand#23"]),
+              Q.RegexFilterSpec("p_type", "BRASS$"), Q.ExtractionFilterSpec("c_mktsegment", ["BUILDING", "MACHINERY"]),
+              Q.ExtractionFilterSpec("p_size", ["3", "17", "44"]), Q.ExtractionFilterSpec("l_linenumber", ["1", "5"]),
+              Q.SelectorFilterSpec("l_returnflag", "N"), Q.ExtractionFilterSpec("c_region", ["ASIA", "EUROPE"]),
+              Q.ExtractionFilterSpec("s_region", ["AFRICA", "ASIA"]), Q.SelectorFilterSpec("l_linestatus", "O")]
+    f = leaves[-1]
+    shape = ("leaf", 11)
+    for depth, i in enumerate(reversed(range(11))):
+        kind = "and" if depth % 2 else "or"
+        f = (Q.And if depth % 2 else Q.Or)(leaves[i], f)
+        shape = (kind, ("leaf", i), shape)
+    ops = eng.explain(Q.with_filter(f))["filter"]["ops"]
+    assert sum(o.startswith("leaf:") for o in ops) == 12
+
+    def run(ops, bits):
+        stack, deepest = [], 0
+        for o in ops:
+            if o.startswith("leaf:"):
+                stack.append(bits[int(o[5:])])
+            elif o == "not":
+                stack[-1] = not stack[-1]
+            else:
+                b, a = stack.pop(), stack.pop()
+                stack.append((a and b) if o == "and" else (a or b))
+            deepest = max(deepest, len(stack))
+        assert len(stack) == 1
+        return stack[0], deepest
+
+    def want(node, bits):
+        if node[0] == "leaf":
+            return bits[node[1]]
+        a, b = want(node[1], bits), want(node[2], bits)
+        return (a and b) if node[0] == "and" else (a or b)
+
+    # leaf numbers in the program are plan-side indices in order of first appearance in the spec (= ours)
+    for bits in itertools.islice(itertools.product([False, True], repeat=12), 0, 4096, 37):
+        got, deepest = run(ops, bits)
+        assert got == want(shape, bits)
+        assert deepest <= 2
+
+
+def test_empty_buckets_are_planned_only_on_request(planning):
+    """context.skipEmptyBuckets = false makes a timeseries plan one time key per granularity bucket between the datasource's
+    first and last timestamp inside the interval; the default plans only the buckets that hold rows."""
+    eng, _, tbl = planning
+    q = json.loads(Q.timeseries("P1D", False, None, ["1993-02-10T00:00:00.000Z/1993-09-20T00:00:00.000Z"]).to_json())
+    q["filter"] = json.loads(Q.And(Q.SelectorFilterSpec("s_nation", "PERU"), Q.SelectorFilterSpec("c_nation", "KENYA")).to_json())
+    a, b = orc.parse_interval(q["intervals"][0])
+    days_with_rows = len(np.unique(tbl.time[(tbl.time >= a) & (tbl.time < b)] // 86400000))
+    assert eng.explain(q)["timeKeys"] == days_with_rows
+    q["context"] = {"queryId": "zf", "skipEmptyBuckets": False}
+    assert eng.explain(q)["timeKeys"] == (b - a) // 86400000
+    import spark_druid_olap_b200 as sdo
+    q["granularity"] = "none"
+    with pytest.raises(sdo.UnsupportedQuery):
+        eng.explain(q)
